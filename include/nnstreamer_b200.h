@@ -1,0 +1,269 @@
+/*
+ * nnstreamer_b200.h -- C-ABI of the B200-native tensor_transform / tensor_converter hot path.
+ *
+ * This is the drop-in boundary: plain C types, plain pointers and
+ * sizes, no C++/GLib/torch types.  Everything above it (the GStreamer glue in
+ * nnstreamer_b200/gst/, the Python mirror in nnstreamer_b200/element.py, bench.py, tests/)
+ * talks to the GPU only through these entry points.  Each declaration cites the reference
+ * interface (file:line under the NNStreamer 2.3.0 tree) it replaces.
+ *
+ * Conventions
+ *   - every call returns 0 on success or a negative errno-style code (NNSB_E*);
+ *     nnsb_last_error() returns the thread-local message (CUDA error string included).
+ *   - there is NO CPU fallback: if no CUDA device / kernel image is usable the call fails.
+ *   - dimension order is innermost-first (dim[0] = channel for video), rank limit 8,
+ *     exactly as tensor_typedef.h:34,212.
+ */
+#ifndef NNSTREAMER_B200_H
+#define NNSTREAMER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NNSB_API __attribute__((visibility("default")))
+
+/* ---------------------------------------------------------------------------------------
+ * Types (tensor_typedef.h:34-36,133-148,163-171,232-260)
+ * ------------------------------------------------------------------------------------- */
+#define NNSB_RANK_LIMIT 8            /* NNS_TENSOR_RANK_LIMIT, tensor_typedef.h:34 */
+#define NNSB_SIZE_LIMIT 16           /* NNS_TENSOR_SIZE_LIMIT, tensor_typedef.h:36 */
+#define NNSB_META_RANK_LIMIT 16      /* NNS_TENSOR_META_RANK_LIMIT, tensor_typedef.h:45 */
+#define NNSB_TRANSPOSE_RANK_LIMIT 4  /* gsttensor_transform.c:86 */
+#define NNSB_MAX_OPS 64              /* arithmetic chain length cap (reference: unbounded GSList) */
+
+/* tensor_type, tensor_typedef.h:133-148 -- the numeric values are wire format (flex header) */
+typedef enum {
+  NNSB_INT32 = 0, NNSB_UINT32, NNSB_INT16, NNSB_UINT16, NNSB_INT8, NNSB_UINT8,
+  NNSB_FLOAT64, NNSB_FLOAT32, NNSB_INT64, NNSB_UINT64, NNSB_FLOAT16,
+  NNSB_TYPE_END
+} nnsb_tensor_type;
+
+/* tensor_format, tensor_typedef.h:186-193 */
+typedef enum {
+  NNSB_FORMAT_STATIC = 0, NNSB_FORMAT_FLEXIBLE, NNSB_FORMAT_SPARSE, NNSB_FORMAT_END
+} nnsb_tensor_format;
+
+/* tensor_transform_mode, gsttensor_transform.h:57-67 */
+typedef enum {
+  NNSB_MODE_DIMCHG = 0, NNSB_MODE_TYPECAST, NNSB_MODE_ARITHMETIC, NNSB_MODE_TRANSPOSE,
+  NNSB_MODE_STAND, NNSB_MODE_CLAMP, NNSB_MODE_UNKNOWN = -1
+} nnsb_mode;
+
+/* tensor_transform_operator, gsttensor_transform.h:69-77 */
+typedef enum {
+  NNSB_OP_TYPECAST = 0, NNSB_OP_ADD = 1, NNSB_OP_MUL = 2, NNSB_OP_DIV = 3, NNSB_OP_UNKNOWN
+} nnsb_operator;
+
+/* tensor_transform_stand_mode, gsttensor_transform.h:79-84 */
+typedef enum { NNSB_STAND_DEFAULT = 0, NNSB_STAND_DC_AVERAGE = 1, NNSB_STAND_END } nnsb_stand_mode;
+
+/* GstPadDirection as used by convert_dimension, gsttensor_transform.c:1850-1853 */
+typedef enum { NNSB_PAD_SRC = 1, NNSB_PAD_SINK = 2 } nnsb_pad_direction;
+
+/* GstTensorInfo (type + dimension), tensor_typedef.h:232-239 */
+typedef struct {
+  int32_t type;                         /* nnsb_tensor_type */
+  uint32_t dim[NNSB_RANK_LIMIT];
+} nnsb_tensor_info;
+
+/* GstTensorsConfig / GstTensorsInfo, tensor_typedef.h:245-260 */
+typedef struct {
+  uint32_t num_tensors;
+  nnsb_tensor_info info[NNSB_SIZE_LIMIT];
+  int32_t format;                       /* nnsb_tensor_format */
+  int32_t rate_n, rate_d;
+} nnsb_tensors_config;
+
+/* GstTensorMetaInfo, tensor_typedef.h:281-296 (the 128-byte flexible-tensor header) */
+typedef struct {
+  uint32_t version;
+  uint32_t type;
+  uint32_t dimension[NNSB_META_RANK_LIMIT];
+  uint32_t format;
+  uint32_t media_type;
+  uint32_t sparse_nnz;
+} nnsb_meta_info;
+
+/* tensor_transform_operator_s, gsttensor_transform.h:104-109.  The operand keeps the
+ * literal's parse class (double if it contains '.', 'e' or 'E', else int64 --
+ * gsttensor_transform.c:796-807); the cast to the working type happens at plan time. */
+typedef struct {
+  int32_t op;                           /* nnsb_operator */
+  int32_t applying_ch;                  /* -1 = every channel (:779) */
+  int32_t is_float;                     /* operand literal class */
+  int32_t cast_type;                    /* target of a leading typecast op */
+  double dval;
+  int64_t ival;
+} nnsb_arith_op;
+
+/* The data_* union of GstTensorTransform, gsttensor_transform.h:153-160, flattened. */
+typedef struct {
+  int32_t mode;                         /* nnsb_mode */
+  int32_t dimchg_from, dimchg_to;       /* tensor_transform_dimchg  (.h:89-92) */
+  int32_t typecast_to;                  /* tensor_transform_typecast (.h:97-99) */
+  int32_t arith_out_type;               /* tensor_transform_arithmetic (.h:114-118) */
+  int32_t arith_per_channel;
+  uint32_t arith_ch_dim;
+  int32_t n_ops;
+  nnsb_arith_op ops[NNSB_MAX_OPS];      /* the `operators` GSList (.h:163) */
+  uint8_t trans_order[NNSB_RANK_LIMIT]; /* tensor_transform_transpose (.h:123-125) */
+  int32_t stand_mode;                   /* tensor_transform_stand (.h:130-134) */
+  int32_t stand_out_type;
+  int32_t stand_per_channel;
+  double clamp_min, clamp_max;          /* tensor_transform_clamp (.h:139-141) */
+} nnsb_option;
+
+/* Error codes (negative errno values) */
+#define NNSB_OK 0
+#define NNSB_EINVAL (-22)
+#define NNSB_ENOMEM (-12)
+#define NNSB_ENOTSUP (-95)
+#define NNSB_ECUDA (-5)                 /* maps to GST_FLOW_ERROR in the glue */
+#define NNSB_ERANGE (-34)
+
+/* Thread-local message of the last failing call on this thread. */
+NNSB_API const char *nnsb_last_error (void);
+
+/* ---------------------------------------------------------------------------------------
+ * Host core: type / dimension helpers (nnstreamer_plugin_api_util_impl.c)
+ * ------------------------------------------------------------------------------------- */
+/* gst_tensor_get_type, util_impl.c:1098-1170 (strips blanks, case-insensitive) */
+NNSB_API int nnsb_type_from_string (const char *typestr);
+/* gst_tensor_get_type_string, util_impl.c:1175-1181; NULL for NNSB_TYPE_END */
+NNSB_API const char *nnsb_type_to_string (int type);
+/* gst_tensor_get_element_size, util_impl.c:1085-1091 */
+NNSB_API size_t nnsb_element_size (int type);
+/* gst_tensor_get_element_count, util_impl.c:1069-1080 */
+NNSB_API uint64_t nnsb_element_count (const uint32_t *dim);
+/* gst_tensor_info_get_size, util_impl.c:155-166 */
+NNSB_API size_t nnsb_info_size (const nnsb_tensor_info * info);
+/* gst_tensor_parse_dimension, util_impl.c:921-956; returns the rank (0 on error) */
+NNSB_API int nnsb_dim_parse (const char *dimstr, uint32_t *dim);
+/* gst_tensor_get_dimension_string / _rank_dimension_string, util_impl.c:964-1017.
+ * rank 0 prints all 8. Returns the string length or NNSB_EINVAL if buf is too small. */
+NNSB_API int nnsb_dim_to_string (const uint32_t *dim, unsigned int rank, char *buf, size_t buflen);
+/* gst_tensor_dimension_is_valid, util_impl.c:893-913 */
+NNSB_API int nnsb_dim_is_valid (const uint32_t *dim);
+
+/* Flexible-tensor header (util_impl.c:1213-1424).  Header size is fixed at 128 bytes (:1330). */
+#define NNSB_META_HEADER_SIZE 128
+/* gst_tensor_info_convert_to_meta, util_impl.c:1471-1495 */
+NNSB_API int nnsb_meta_from_info (const nnsb_tensor_info * info, nnsb_meta_info * meta);
+/* gst_tensor_meta_info_convert, util_impl.c:1432-1464 */
+NNSB_API int nnsb_meta_to_info (const nnsb_meta_info * meta, nnsb_tensor_info * info);
+/* gst_tensor_meta_info_update_header, util_impl.c:1374-1389 */
+NNSB_API int nnsb_meta_write_header (const nnsb_meta_info * meta, void *header);
+/* gst_tensor_meta_info_parse_header, util_impl.c:1397-1424 */
+NNSB_API int nnsb_meta_parse_header (nnsb_meta_info * meta, const void *header);
+/* gst_tensor_meta_info_get_data_size, util_impl.c:1340-1364 */
+NNSB_API size_t nnsb_meta_data_size (const nnsb_meta_info * meta);
+
+/* ---------------------------------------------------------------------------------------
+ * Host core: mode / option grammar and dimension conversion (gsttensor_transform.c)
+ * ------------------------------------------------------------------------------------- */
+/* GEnum nicks of gtt_mode_type, gsttensor_transform.c:180-204 */
+NNSB_API int nnsb_mode_from_string (const char *nick);
+NNSB_API const char *nnsb_mode_to_string (int mode);
+
+/* gst_tensor_transform_set_option_data, gsttensor_transform.c:652-958: validates `option`
+ * against the per-mode grammar (REGEX_* :70-80) and fills `out`.  Returns 0 when the
+ * reference would set `loaded = TRUE`, NNSB_EINVAL otherwise (out->mode is then UNKNOWN). */
+NNSB_API int nnsb_option_parse (int mode, const char *option, nnsb_option * out);
+
+/* gst_tensor_transform_convert_dimension, gsttensor_transform.c:1850-1959.
+ * direction SINK: in -> out; SRC: out -> in (type becomes NNSB_TYPE_END where unknowable). */
+NNSB_API int nnsb_convert_dimension (const nnsb_option * opt, int direction,
+    const nnsb_tensor_info * in_info, nnsb_tensor_info * out_info);
+
+/* ---------------------------------------------------------------------------------------
+ * Device runtime: replaces gst_allocator_alloc(NULL,...) + gst_memory_map of
+ * gsttensor_transform.c:1725,1758-1766 and tensor_allocator.c:101-128.
+ * ------------------------------------------------------------------------------------- */
+typedef struct nnsb_ctx nnsb_ctx;        /* one per (element instance, device) */
+typedef struct nnsb_stream nnsb_stream;  /* one CUDA stream; per element instance */
+typedef struct nnsb_event nnsb_event;
+
+NNSB_API int nnsb_device_count (int *count);
+NNSB_API int nnsb_ctx_create (int device_id, nnsb_ctx ** out);
+NNSB_API int nnsb_ctx_destroy (nnsb_ctx * ctx);
+NNSB_API int nnsb_ctx_device (const nnsb_ctx * ctx);
+/* number of SMs of the bound device (148 on B200) */
+NNSB_API int nnsb_ctx_sm_count (const nnsb_ctx * ctx);
+
+NNSB_API int nnsb_stream_create (nnsb_ctx * ctx, nnsb_stream ** out);
+/* wrap an existing cudaStream_t (e.g. torch's current stream); not owned */
+NNSB_API int nnsb_stream_wrap (nnsb_ctx * ctx, void *cuda_stream, nnsb_stream ** out);
+NNSB_API int nnsb_stream_sync (nnsb_stream * s);
+NNSB_API int nnsb_stream_destroy (nnsb_stream * s);
+
+NNSB_API int nnsb_event_create (nnsb_ctx * ctx, nnsb_event ** out);
+NNSB_API int nnsb_event_record (nnsb_event * e, nnsb_stream * s);
+NNSB_API int nnsb_event_sync (nnsb_event * e);
+/* make stream `s` wait for event `e` (cross-stream ordering inside one element) */
+NNSB_API int nnsb_stream_wait_event (nnsb_stream * s, nnsb_event * e);
+NNSB_API int nnsb_event_elapsed_ms (nnsb_event * start, nnsb_event * stop, float *ms);
+NNSB_API int nnsb_event_destroy (nnsb_event * e);
+
+/* Size-bucketed device pool: freed blocks are kept and reused, so steady-state streaming
+ * performs no cudaMalloc.  Blocks are 256-byte aligned. */
+NNSB_API int nnsb_dev_alloc (nnsb_ctx * ctx, size_t size, void **out);
+NNSB_API int nnsb_dev_free (nnsb_ctx * ctx, void *ptr);
+/* release cached blocks back to the driver */
+NNSB_API int nnsb_dev_trim (nnsb_ctx * ctx);
+NNSB_API int nnsb_dev_memset_async (nnsb_stream * s, void *dst, int value, size_t n);
+/* pooled page-locked host staging memory */
+NNSB_API int nnsb_pinned_alloc (nnsb_ctx * ctx, size_t size, void **out);
+NNSB_API int nnsb_pinned_free (nnsb_ctx * ctx, void *ptr);
+
+NNSB_API int nnsb_h2d_async (nnsb_stream * s, void *dst_dev, const void *src_host, size_t n);
+NNSB_API int nnsb_d2h_async (nnsb_stream * s, void *dst_host, const void *src_dev, size_t n);
+NNSB_API int nnsb_d2d_async (nnsb_stream * s, void *dst_dev, const void *src_dev, size_t n);
+/* pitched H2D: strips the video row padding for free on the copy engine
+ * (the copy gsttensor_converter.c:1087-1100 does with one memcpy per row) */
+NNSB_API int nnsb_h2d_2d_async (nnsb_stream * s, void *dst_dev, size_t dst_pitch,
+    const void *src_host, size_t src_pitch, size_t row_bytes, size_t rows);
+
+/* ---------------------------------------------------------------------------------------
+ * Plans: one parsed (mode, option) bound to one input tensor info -> the kernels.
+ * Replaces the switch of gst_tensor_transform_transform, gsttensor_transform.c:1773-1802,
+ * and the six functions it calls (:1120 dimchg, :1202 typecast, :1240 arithmetic,
+ * :1443 transpose, :1512 stand, :1632 clamp).
+ * ------------------------------------------------------------------------------------- */
+typedef struct nnsb_plan nnsb_plan;
+
+/* acceleration: the element's `acceleration` property (gsttensor_transform.c:241-243).
+ * 0 = plain C semantics (integer ops wrap); 1 = ORC semantics for the types ORC supports
+ * (saturating integer add/mul, signed-saturating narrowing; orc_supported, :462-463). */
+NNSB_API int nnsb_plan_create (nnsb_ctx * ctx, const nnsb_option * opt,
+    const nnsb_tensor_info * in_info, int acceleration, nnsb_plan ** out);
+NNSB_API int nnsb_plan_destroy (nnsb_plan * plan);
+NNSB_API int nnsb_plan_out_info (const nnsb_plan * plan, nnsb_tensor_info * out_info);
+NNSB_API size_t nnsb_plan_in_size (const nnsb_plan * plan);   /* bytes of one input tensor */
+NNSB_API size_t nnsb_plan_out_size (const nnsb_plan * plan);  /* bytes of one output tensor */
+
+/* Transform `batch` tensors laid out back to back (frame f at d_in + f*in_size ->
+ * d_out + f*out_size) with ONE set of launches.  Per-tensor semantics are preserved
+ * (stand computes its statistics per tensor), i.e. the result equals `batch` calls of the
+ * reference function.  d_in/d_out are device pointers; asynchronous on `s`. */
+NNSB_API int nnsb_plan_launch (nnsb_plan * plan, const void *d_in, void *d_out,
+    uint32_t batch, nnsb_stream * s);
+/* number of kernels the last nnsb_plan_launch on this plan enqueued */
+NNSB_API int nnsb_plan_last_launch_count (const nnsb_plan * plan);
+/* stand only: copy the per-tensor statistics of the last launch (mean[, std]) to host */
+NNSB_API int nnsb_plan_stand_stats (nnsb_plan * plan, nnsb_stream * s, uint32_t batch,
+    double *mean_out, double *std_out, size_t capacity);
+
+/* tensor_converter video row-stride strip, gsttensor_converter.c:1087-1100: copies `rows`
+ * rows of `row_bytes` from a source with pitch `src_pitch` into a dense destination.
+ * Both pointers are device memory. */
+NNSB_API int nnsb_strip_launch (nnsb_stream * s, const void *d_src, void *d_dst,
+    size_t row_bytes, size_t src_pitch, size_t rows);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NNSTREAMER_B200_H */

@@ -1,0 +1,172 @@
+"""ctypes binding of libnnstreamer_b200.so (the C-ABI of include/nnstreamer_b200.h).
+
+The library is the product: there is no Python or CPU implementation behind it.  Loading
+fails loudly if the shared object is missing (run ``python -c 'import __graft_entry__ as g;
+g.build()'``), and every compute entry point fails with NNSB_ECUDA when no B200 is visible.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libnnstreamer_b200.so")
+
+RANK_LIMIT = 8
+SIZE_LIMIT = 16
+META_RANK_LIMIT = 16
+MAX_OPS = 64
+META_HEADER_SIZE = 128
+
+# tensor_typedef.h:133-148
+TYPES = ["int32", "uint32", "int16", "uint16", "int8", "uint8", "float64", "float32",
+         "int64", "uint64", "float16"]
+TYPE_ID = {n: i for i, n in enumerate(TYPES)}
+TYPE_END = len(TYPES)
+MODES = ["dimchg", "typecast", "arithmetic", "transpose", "stand", "clamp"]
+MODE_ID = {n: i for i, n in enumerate(MODES)}
+PAD_SRC, PAD_SINK = 1, 2
+
+OK, EINVAL, ENOMEM, ENOTSUP, ECUDA, ERANGE = 0, -22, -12, -95, -5, -34
+
+
+class TensorInfo(C.Structure):
+    _fields_ = [("type", C.c_int32), ("dim", C.c_uint32 * RANK_LIMIT)]
+
+
+class TensorsConfig(C.Structure):
+    _fields_ = [("num_tensors", C.c_uint32), ("info", TensorInfo * SIZE_LIMIT),
+                ("format", C.c_int32), ("rate_n", C.c_int32), ("rate_d", C.c_int32)]
+
+
+class MetaInfo(C.Structure):
+    _fields_ = [("version", C.c_uint32), ("type", C.c_uint32),
+                ("dimension", C.c_uint32 * META_RANK_LIMIT), ("format", C.c_uint32),
+                ("media_type", C.c_uint32), ("sparse_nnz", C.c_uint32)]
+
+
+class ArithOp(C.Structure):
+    _fields_ = [("op", C.c_int32), ("applying_ch", C.c_int32), ("is_float", C.c_int32),
+                ("cast_type", C.c_int32), ("dval", C.c_double), ("ival", C.c_int64)]
+
+
+class Option(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("dimchg_from", C.c_int32), ("dimchg_to", C.c_int32),
+                ("typecast_to", C.c_int32), ("arith_out_type", C.c_int32),
+                ("arith_per_channel", C.c_int32), ("arith_ch_dim", C.c_uint32),
+                ("n_ops", C.c_int32), ("ops", ArithOp * MAX_OPS),
+                ("trans_order", C.c_uint8 * RANK_LIMIT), ("stand_mode", C.c_int32),
+                ("stand_out_type", C.c_int32), ("stand_per_channel", C.c_int32),
+                ("clamp_min", C.c_double), ("clamp_max", C.c_double)]
+
+
+class NnsbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("nnstreamer_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+
+_VP = C.c_void_p
+_PROTOS = {
+    # name: (restype, argtypes)
+    "nnsb_last_error": (C.c_char_p, []),
+    "nnsb_type_from_string": (C.c_int, [C.c_char_p]),
+    "nnsb_type_to_string": (C.c_char_p, [C.c_int]),
+    "nnsb_element_size": (C.c_size_t, [C.c_int]),
+    "nnsb_element_count": (C.c_uint64, [C.POINTER(C.c_uint32)]),
+    "nnsb_info_size": (C.c_size_t, [C.POINTER(TensorInfo)]),
+    "nnsb_dim_parse": (C.c_int, [C.c_char_p, C.POINTER(C.c_uint32)]),
+    "nnsb_dim_to_string": (C.c_int, [C.POINTER(C.c_uint32), C.c_uint, C.c_char_p, C.c_size_t]),
+    "nnsb_dim_is_valid": (C.c_int, [C.POINTER(C.c_uint32)]),
+    "nnsb_meta_from_info": (C.c_int, [C.POINTER(TensorInfo), C.POINTER(MetaInfo)]),
+    "nnsb_meta_to_info": (C.c_int, [C.POINTER(MetaInfo), C.POINTER(TensorInfo)]),
+    "nnsb_meta_write_header": (C.c_int, [C.POINTER(MetaInfo), _VP]),
+    "nnsb_meta_parse_header": (C.c_int, [C.POINTER(MetaInfo), _VP]),
+    "nnsb_meta_data_size": (C.c_size_t, [C.POINTER(MetaInfo)]),
+    "nnsb_mode_from_string": (C.c_int, [C.c_char_p]),
+    "nnsb_mode_to_string": (C.c_char_p, [C.c_int]),
+    "nnsb_option_parse": (C.c_int, [C.c_int, C.c_char_p, C.POINTER(Option)]),
+    "nnsb_convert_dimension": (C.c_int, [C.POINTER(Option), C.c_int, C.POINTER(TensorInfo),
+                                         C.POINTER(TensorInfo)]),
+    "nnsb_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "nnsb_ctx_create": (C.c_int, [C.c_int, C.POINTER(_VP)]),
+    "nnsb_ctx_destroy": (C.c_int, [_VP]),
+    "nnsb_ctx_device": (C.c_int, [_VP]),
+    "nnsb_ctx_sm_count": (C.c_int, [_VP]),
+    "nnsb_stream_create": (C.c_int, [_VP, C.POINTER(_VP)]),
+    "nnsb_stream_wrap": (C.c_int, [_VP, _VP, C.POINTER(_VP)]),
+    "nnsb_stream_sync": (C.c_int, [_VP]),
+    "nnsb_stream_destroy": (C.c_int, [_VP]),
+    "nnsb_event_create": (C.c_int, [_VP, C.POINTER(_VP)]),
+    "nnsb_event_record": (C.c_int, [_VP, _VP]),
+    "nnsb_event_sync": (C.c_int, [_VP]),
+    "nnsb_stream_wait_event": (C.c_int, [_VP, _VP]),
+    "nnsb_event_elapsed_ms": (C.c_int, [_VP, _VP, C.POINTER(C.c_float)]),
+    "nnsb_event_destroy": (C.c_int, [_VP]),
+    "nnsb_dev_alloc": (C.c_int, [_VP, C.c_size_t, C.POINTER(_VP)]),
+    "nnsb_dev_free": (C.c_int, [_VP, _VP]),
+    "nnsb_dev_trim": (C.c_int, [_VP]),
+    "nnsb_dev_memset_async": (C.c_int, [_VP, _VP, C.c_int, C.c_size_t]),
+    "nnsb_pinned_alloc": (C.c_int, [_VP, C.c_size_t, C.POINTER(_VP)]),
+    "nnsb_pinned_free": (C.c_int, [_VP, _VP]),
+    "nnsb_h2d_async": (C.c_int, [_VP, _VP, _VP, C.c_size_t]),
+    "nnsb_d2h_async": (C.c_int, [_VP, _VP, _VP, C.c_size_t]),
+    "nnsb_d2d_async": (C.c_int, [_VP, _VP, _VP, C.c_size_t]),
+    "nnsb_h2d_2d_async": (C.c_int, [_VP, _VP, C.c_size_t, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),
+    "nnsb_plan_create": (C.c_int, [_VP, C.POINTER(Option), C.POINTER(TensorInfo), C.c_int,
+                                   C.POINTER(_VP)]),
+    "nnsb_plan_destroy": (C.c_int, [_VP]),
+    "nnsb_plan_out_info": (C.c_int, [_VP, C.POINTER(TensorInfo)]),
+    "nnsb_plan_in_size": (C.c_size_t, [_VP]),
+    "nnsb_plan_out_size": (C.c_size_t, [_VP]),
+    "nnsb_plan_launch": (C.c_int, [_VP, _VP, _VP, C.c_uint32, _VP]),
+    "nnsb_plan_last_launch_count": (C.c_int, [_VP]),
+    "nnsb_plan_stand_stats": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(C.c_double),
+                                        C.POINTER(C.c_double), C.c_size_t]),
+    "nnsb_strip_launch": (C.c_int, [_VP, _VP, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),
+}
+
+
+def lib():
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise ImportError(
+                "%s is missing: the CUDA extension has not been built "
+                "(python -c 'import __graft_entry__ as g; g.build()'). There is no fallback."
+                % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in _PROTOS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def declared_symbols():
+    return sorted(_PROTOS)
+
+
+def check(code):
+    if code != OK:
+        raise NnsbError(code, lib().nnsb_last_error().decode("utf-8", "replace"))
+    return code
+
+
+def make_info(type_name, dim):
+    info = TensorInfo()
+    info.type = TYPE_ID[type_name] if isinstance(type_name, str) else int(type_name)
+    d = list(dim) + [1] * (RANK_LIMIT - len(dim))
+    for i in range(RANK_LIMIT):
+        info.dim[i] = int(d[i])
+    return info
+
+
+def parse_option(mode, option):
+    """nnsb_option_parse; returns (code, Option)."""
+    opt = Option()
+    m = MODE_ID[mode] if isinstance(mode, str) else int(mode)
+    code = lib().nnsb_option_parse(m, option.encode() if option is not None else None, C.byref(opt))
+    return code, opt

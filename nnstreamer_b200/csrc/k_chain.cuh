@@ -1,0 +1,230 @@
+/*
+ * k_chain.cuh -- K1/K2: fused typecast + arithmetic chain, one pass over HBM.
+ *
+ * Replaces gst_tensor_transform_typecast (gsttensor_transform.c:1202-1229) and
+ * gst_tensor_transform_arithmetic (:1240-1412): the reference's ORC path makes one full pass
+ * over the output per operator, its C path walks a GSList through a typed union per element.
+ * Here every element is loaded once (In), converted (C or ORC rules), run through the
+ * compiled chain in the working type Out with per-operation rounding (no FMA contraction,
+ * IEEE division) and stored once.
+ *
+ * Data movement: each thread owns V consecutive elements per step where the wider of the
+ * two element types fills a 256-bit access (u8->f32: one 8-byte load, one 32-byte store);
+ * consecutive threads own consecutive vectors, so every warp access is a dense 256/512/1024
+ * byte run.  U independent loads are issued before the first use.  Loads are
+ * ld.global.nc.L1::no_allocate, stores st.global.L1::no_allocate (read/write-once streams).
+ *
+ * Algorithmic bytes per element: sizeof(In) + sizeof(Out)  (5 for u8->f32).
+ */
+#ifndef NNSB_K_CHAIN_CUH
+#define NNSB_K_CHAIN_CUH
+
+#include "nnsb_device.cuh"
+#include "nnsb_kernels.h"
+
+namespace nnsb {
+
+struct ChainDev
+{
+  int32_t n_pos;
+  int32_t nch;                  /* 1 = not per-channel */
+  uint64_t ch_size;
+  uint64_t step_r;              /* (grid threads * V) % ch_size */
+  uint32_t step_c;              /* ((grid threads * V) / ch_size) % nch */
+  const nnsb_cell *table;       /* [n_pos][nch] when nch > 1 */
+  int32_t opcode[NNSB_MAX_OPS];
+  nnsb_cell scalar[NNSB_MAX_OPS];
+};
+
+constexpr int CHAIN_THREADS = 256;
+
+template <typename In, typename Out> struct ChainVec
+{
+  static constexpr int W = sizeof (In) > sizeof (Out) ? sizeof (In) : sizeof (Out);
+  /* at most 16 elements per thread keeps the 1-byte pairs under ~100 registers */
+  static constexpr int V = (32 / W) > 16 ? 16 : (32 / W);
+};
+
+template <typename Out> __device__ __forceinline__ Out
+chain_operand (const ChainDev &p, int pos, uint32_t ch, bool perch)
+{
+  if (perch) {
+    unsigned long long raw = __ldg ((const unsigned long long *) (p.table + (size_t) pos * p.nch + ch));
+    Out v;
+    memcpy (&v, &raw, sizeof (Out));
+    return v;
+  }
+  return cell_get<Out> (p.scalar[pos]);
+}
+
+template <typename Out, bool ORC, int V> __device__ __forceinline__ void
+chain_apply (Vec<Out, V> &y, const uint32_t (&ch)[V], const ChainDev &p, bool perch)
+{
+  for (int pos = 0; pos < p.n_pos; pos++) {
+    const int opc = p.opcode[pos];
+    if (opc == NNSB_OP_ADD) {
+#pragma unroll
+      for (int k = 0; k < V; k++)
+        y.e[k] = Arith<Out, ORC>::add (y.e[k], chain_operand<Out> (p, pos, ch[k], perch));
+    } else if (opc == NNSB_OP_MUL) {
+#pragma unroll
+      for (int k = 0; k < V; k++)
+        y.e[k] = Arith<Out, ORC>::mul (y.e[k], chain_operand<Out> (p, pos, ch[k], perch));
+    } else {
+#pragma unroll
+      for (int k = 0; k < V; k++)
+        y.e[k] = Arith<Out, ORC>::div (y.e[k], chain_operand<Out> (p, pos, ch[k], perch));
+    }
+  }
+}
+
+template <typename In, typename Out, bool ORC, int U>
+__global__ void __launch_bounds__ (CHAIN_THREADS)
+chain_kernel (const In *__restrict__ in, Out *__restrict__ out, size_t n, size_t n_vec,
+    const __grid_constant__ ChainDev p)
+{
+  constexpr int V = ChainVec<In, Out>::V;
+  const size_t tid = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t nthreads = (size_t) gridDim.x * blockDim.x;
+  const bool perch = p.nch > 1;
+
+  /* channel walker: (r, c) = position inside the channel run and channel index of the
+   * first element of this thread's current vector */
+  uint64_t r = 0;
+  uint32_t c = 0;
+  if (perch) {
+    const uint64_t e0 = (uint64_t) tid * V;
+    r = e0 % p.ch_size;
+    c = (uint32_t) ((e0 / p.ch_size) % (uint64_t) p.nch);
+  }
+
+  for (size_t v = tid; v < n_vec; v += nthreads * U) {
+    Vec<In, V> x[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const size_t vu = v + (size_t) u * nthreads;
+      if (vu < n_vec)
+        load_vec (x[u], in + vu * V);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const size_t vu = v + (size_t) u * nthreads;
+      if (vu < n_vec) {
+        Vec<Out, V> y;
+        uint32_t ch[V];
+#pragma unroll
+        for (int k = 0; k < V; k++)
+          y.e[k] = Cast<Out, In, ORC>::run (x[u].e[k]);
+        if (perch) {
+          uint64_t rr = r;
+          uint32_t cc = c;
+#pragma unroll
+          for (int k = 0; k < V; k++) {
+            ch[k] = cc;
+            if (++rr == p.ch_size) {
+              rr = 0;
+              cc = (cc + 1 == (uint32_t) p.nch) ? 0 : cc + 1;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < V; k++)
+            ch[k] = 0;
+        }
+        chain_apply<Out, ORC, V> (y, ch, p, perch);
+        store_vec (out + vu * V, y);
+      }
+      if (perch) {
+        /* advance the walker by one grid stride (nthreads * V elements) */
+        r += p.step_r;
+        uint32_t carry = 0;
+        if (r >= p.ch_size) {
+          r -= p.ch_size;
+          carry = 1;
+        }
+        c += p.step_c + carry;
+        if (c >= (uint32_t) p.nch)
+          c -= (uint32_t) p.nch;
+      }
+    }
+  }
+
+  /* scalar tail (and the whole tensor when the pointers are not vector-aligned) */
+  for (size_t e = n_vec * V + tid; e < n; e += nthreads) {
+    Vec<Out, 1> y;
+    uint32_t ch[1] = { 0 };
+    In xv;
+    ld_stream<sizeof (In)> (&xv, in + e);
+    y.e[0] = Cast<Out, In, ORC>::run (xv);
+    if (perch)
+      ch[0] = (uint32_t) (((uint64_t) e / p.ch_size) % (uint64_t) p.nch);
+    chain_apply<Out, ORC, 1> (y, ch, p, perch);
+    st_stream<sizeof (Out)> (out + e, &y.e[0]);
+  }
+}
+
+template <typename In, typename Out, bool ORC>
+int launch_chain_t (const void *in, void *out, size_t n, const ChainArgs &args,
+    const LaunchCfg &cfg, cudaStream_t stream)
+{
+  constexpr int V = ChainVec<In, Out>::V;
+  constexpr int U = 4;
+  if (n == 0)
+    return 0;
+  const bool aligned = ((uintptr_t) in % (V * sizeof (In)) == 0)
+      && ((uintptr_t) out % (V * sizeof (Out)) == 0);
+  const size_t n_vec = aligned ? n / V : 0;
+  const size_t work = n_vec ? n_vec : n;
+  const int bps = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 8;
+  size_t blocks = (work + (size_t) CHAIN_THREADS * U - 1) / ((size_t) CHAIN_THREADS * U);
+  const size_t cap = (size_t) cfg.sm_count * bps;
+  if (blocks > cap)
+    blocks = cap;
+  if (blocks == 0)
+    blocks = 1;
+
+  ChainDev p;
+  p.n_pos = args.desc.n_pos;
+  p.nch = args.desc.nch;
+  p.ch_size = args.desc.ch_size ? args.desc.ch_size : 1;
+  const uint64_t stride_elems = (uint64_t) blocks * CHAIN_THREADS * V;
+  p.step_r = stride_elems % p.ch_size;
+  p.step_c = (uint32_t) ((stride_elems / p.ch_size) % (uint64_t) (p.nch > 0 ? p.nch : 1));
+  p.table = args.table;
+  for (int i = 0; i < NNSB_MAX_OPS; i++) {
+    p.opcode[i] = args.desc.opcode[i];
+    p.scalar[i] = args.desc.scalar[i];
+  }
+  chain_kernel<In, Out, ORC, U><<<(unsigned int) blocks, CHAIN_THREADS, 0, stream>>> (
+      (const In *) in, (Out *) out, n, n_vec, p);
+  return (int) cudaGetLastError ();
+}
+
+typedef int (*chain_fn) (const void *, void *, size_t, const ChainArgs &, const LaunchCfg &,
+    cudaStream_t);
+
+/* one row (fixed In) of the dispatch table, both policies */
+template <typename In> struct ChainRow
+{
+  static chain_fn get (int out_type, bool orc)
+  {
+    constexpr bool in_orc_ok = !Is64Int<In>::v && TypeId<In>::id != NNSB_FLOAT16;
+    switch (out_type) {
+#define NNSB_CASE(T) \
+      case TypeId<T>::id: \
+        if constexpr (in_orc_ok && !Is64Int<T>::v && TypeId<T>::id != NNSB_FLOAT16) { \
+          if (orc) return &launch_chain_t<In, T, true>; \
+        } \
+        return &launch_chain_t<In, T, false>;
+      NNSB_CASE (int32_t) NNSB_CASE (uint32_t) NNSB_CASE (int16_t) NNSB_CASE (uint16_t)
+      NNSB_CASE (int8_t) NNSB_CASE (uint8_t) NNSB_CASE (double) NNSB_CASE (float)
+      NNSB_CASE (int64_t) NNSB_CASE (uint64_t) NNSB_CASE (__half)
+#undef NNSB_CASE
+      default:
+        return nullptr;
+    }
+  }
+};
+
+}  // namespace nnsb
+#endif

@@ -1,0 +1,64 @@
+/*
+ * nnsb_kernels.h -- host-callable launchers of the sm_100a kernels (internal).
+ * Every launcher enqueues on `stream`, never synchronises, never allocates, and returns the
+ * cudaError_t of the launch as int (0 = ok).
+ */
+#ifndef NNSB_KERNELS_H
+#define NNSB_KERNELS_H
+
+#include <cuda_runtime.h>
+#include "nnsb_internal.h"
+
+namespace nnsb {
+
+struct LaunchCfg
+{
+  int sm_count;                 /* SMs of the device (148 on B200) */
+  int blocks_per_sm;            /* grid = sm_count * blocks_per_sm (0 = kernel default) */
+};
+
+/* K1/K2: fused (typecast +) arithmetic chain.  typecast mode is the empty chain.
+ * Replaces gst_tensor_transform_typecast (:1202) and _arithmetic (:1240). */
+struct ChainArgs
+{
+  nnsb_chain_desc desc;
+  const nnsb_cell *table;       /* device, [n_pos][nch]; used when nch > 1 */
+};
+int launch_chain (int in_type, int out_type, bool orc, const void *in, void *out, size_t n,
+    const ChainArgs & args, const LaunchCfg & cfg, cudaStream_t stream);
+
+/* K5: clamp, gst_tensor_transform_clamp (:1632) */
+int launch_clamp (int type, const void *in, void *out, size_t n, double lo, double hi,
+    const LaunchCfg & cfg, cudaStream_t stream);
+
+/* K6/K7: stand, gst_tensor_transform_stand (:1512) + tensor_data.c:314-493.
+ * Per tensor f (of `batch`): statistics over frame_elems elements, per channel c = e % nch
+ * (nch = 1 when not per-channel).
+ *   scratch: device doubles, stand_scratch_doubles() of them, contents undefined on entry
+ *   stats:   device doubles [batch][nch][2] = {mean, std}; written by the launch */
+size_t stand_scratch_doubles (uint32_t batch, uint32_t nch, size_t frame_elems,
+    const LaunchCfg & cfg);
+int launch_stand (int in_type, int out_type, int stand_mode, const void *in, void *out,
+    size_t frame_elems, uint32_t nch, uint32_t batch, double *scratch, double *stats,
+    const LaunchCfg & cfg, cudaStream_t stream, int *n_launches);
+
+/* K3/K4: rank-N permutation copy (transpose :1443, dimchg :1120).
+ * out index (innermost first) i has extent size[i] and input stride in_stride[i] (elements
+ * of es bytes); the output is dense.  `batch` tensors of frame_elems elements each. */
+#define NNSB_PERM_MAX_RANK 8
+struct PermDesc
+{
+  int rank;
+  uint32_t size[NNSB_PERM_MAX_RANK];
+  uint64_t in_stride[NNSB_PERM_MAX_RANK];
+  int es;                       /* element bytes: 1,2,4,8,16 */
+};
+int launch_permute (const PermDesc & d, const void *in, void *out, size_t frame_elems,
+    uint32_t batch, const LaunchCfg & cfg, cudaStream_t stream);
+
+/* K8: row-stride strip, gsttensor_converter.c:1087-1100 */
+int launch_strip (const void *src, void *dst, size_t row_bytes, size_t src_pitch, size_t rows,
+    const LaunchCfg & cfg, cudaStream_t stream);
+
+}  // namespace nnsb
+#endif

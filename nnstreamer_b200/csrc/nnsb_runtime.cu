@@ -1,0 +1,817 @@
+/*
+ * nnsb_runtime.cu -- device runtime and plans behind the C-ABI (include/nnstreamer_b200.h).
+ *
+ *  ctx     : binds one element instance to one GPU; owns a size-bucketed device pool and a
+ *            pinned-host pool so steady-state streaming never calls cudaMalloc/cudaHostAlloc.
+ *            This is what replaces `gst_allocator_alloc (NULL, size, NULL)` per tensor per
+ *            buffer (gsttensor_transform.c:1758) and tensor_allocator.c:101-128.
+ *  stream  : one CUDA stream per element instance (transform() runs on the upstream
+ *            streaming thread; every entry point re-binds the device first).
+ *  plan    : parsed option + input info -> kernel selection and launch geometry; replaces
+ *            the mode switch of gst_tensor_transform_transform (:1773-1802).
+ *
+ * No CPU fallback exists: without a usable CUDA device every call fails with NNSB_ECUDA.
+ */
+#include <cuda_runtime.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "nnsb_internal.h"
+#include "nnsb_kernels.h"
+
+using namespace nnsb;
+
+/* ------------------------------------------------------------------------------------- */
+/* objects                                                                                 */
+/* ------------------------------------------------------------------------------------- */
+struct nnsb_ctx
+{
+  int device;
+  int sm_count;
+  int blocks_per_sm;            /* 0 = per-kernel default; NNSB_BLOCKS_PER_SM overrides */
+  std::mutex mu;
+  std::map<size_t, std::vector<void *> > dev_free;     /* bucket -> cached blocks */
+  std::map<void *, size_t> dev_live;                  /* block -> bucket */
+  std::map<size_t, std::vector<void *> > pin_free;
+  std::map<void *, size_t> pin_live;
+};
+
+struct nnsb_stream
+{
+  nnsb_ctx *ctx;
+  cudaStream_t s;
+  bool owned;
+};
+
+struct nnsb_event
+{
+  nnsb_ctx *ctx;
+  cudaEvent_t e;
+};
+
+struct nnsb_plan
+{
+  nnsb_ctx *ctx;
+  nnsb_option opt;
+  nnsb_tensor_info in_info, out_info;
+  size_t in_size, out_size;
+  uint64_t frame_elems;
+  int acceleration;             /* effective: orc_supported() */
+  /* arithmetic / typecast */
+  ChainArgs chain;
+  nnsb_cell *d_table;
+  /* transpose / dimchg */
+  PermDesc perm;
+  /* stand */
+  uint32_t stand_nch;
+  double *d_scratch;
+  size_t scratch_doubles;
+  double *d_stats;
+  size_t stats_doubles;
+  int last_launches;
+};
+
+#define CUDA_TRY(call) \
+  do { \
+    cudaError_t e__ = (call); \
+    if (e__ != cudaSuccess) \
+      return nnsb_set_error (NNSB_ECUDA, "%s failed: %s", #call, cudaGetErrorString (e__)); \
+  } while (0)
+
+static int
+bind (const nnsb_ctx * ctx)
+{
+  if (!ctx)
+    return nnsb_set_error (NNSB_EINVAL, "null context");
+  CUDA_TRY (cudaSetDevice (ctx->device));
+  return NNSB_OK;
+}
+
+static size_t
+bucket_of (size_t size)
+{
+  if (size < 256)
+    size = 256;
+  if (size <= (2u << 20)) {
+    size_t b = 256;
+    while (b < size)
+      b <<= 1;
+    return b;
+  }
+  const size_t g = 2u << 20;    /* 2 MiB granularity above 2 MiB */
+  return (size + g - 1) / g * g;
+}
+
+/* ------------------------------------------------------------------------------------- */
+/* context / stream / event                                                                */
+/* ------------------------------------------------------------------------------------- */
+extern "C" int
+nnsb_device_count (int *count)
+{
+  if (!count)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_device_count: null argument");
+  *count = 0;
+  CUDA_TRY (cudaGetDeviceCount (count));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_ctx_create (int device_id, nnsb_ctx ** out)
+{
+  if (!out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_ctx_create: null argument");
+  *out = nullptr;
+  int count = 0;
+  CUDA_TRY (cudaGetDeviceCount (&count));
+  if (device_id < 0 || device_id >= count)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_ctx_create: device %d of %d does not exist",
+        device_id, count);
+  CUDA_TRY (cudaSetDevice (device_id));
+  cudaDeviceProp prop;
+  CUDA_TRY (cudaGetDeviceProperties (&prop, device_id));
+  if (prop.major != 10)
+    return nnsb_set_error (NNSB_ENOTSUP,
+        "nnsb_ctx_create: device %d is sm_%d%d; this library carries sm_100a code only",
+        device_id, prop.major, prop.minor);
+  nnsb_ctx *ctx = new (std::nothrow) nnsb_ctx ();
+  if (!ctx)
+    return nnsb_set_error (NNSB_ENOMEM, "nnsb_ctx_create: out of memory");
+  ctx->device = device_id;
+  ctx->sm_count = prop.multiProcessorCount;
+  ctx->blocks_per_sm = 0;
+  const char *env = getenv ("NNSB_BLOCKS_PER_SM");
+  if (env && atoi (env) > 0)
+    ctx->blocks_per_sm = atoi (env);
+  *out = ctx;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_dev_trim (nnsb_ctx * ctx)
+{
+  int r = bind (ctx);
+  if (r)
+    return r;
+  std::lock_guard<std::mutex> lk (ctx->mu);
+  for (auto & kv : ctx->dev_free)
+    for (void *p : kv.second)
+      cudaFree (p);
+  ctx->dev_free.clear ();
+  for (auto & kv : ctx->pin_free)
+    for (void *p : kv.second)
+      cudaFreeHost (p);
+  ctx->pin_free.clear ();
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_ctx_destroy (nnsb_ctx * ctx)
+{
+  if (!ctx)
+    return NNSB_OK;
+  if (bind (ctx) == NNSB_OK) {
+    cudaDeviceSynchronize ();
+    nnsb_dev_trim (ctx);
+    for (auto & kv : ctx->dev_live)
+      cudaFree (kv.first);
+    for (auto & kv : ctx->pin_live)
+      cudaFreeHost (kv.first);
+  }
+  delete ctx;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_ctx_device (const nnsb_ctx * ctx)
+{
+  return ctx ? ctx->device : NNSB_EINVAL;
+}
+
+extern "C" int
+nnsb_ctx_sm_count (const nnsb_ctx * ctx)
+{
+  return ctx ? ctx->sm_count : NNSB_EINVAL;
+}
+
+extern "C" int
+nnsb_stream_create (nnsb_ctx * ctx, nnsb_stream ** out)
+{
+  if (!out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_stream_create: null argument");
+  *out = nullptr;
+  int r = bind (ctx);
+  if (r)
+    return r;
+  cudaStream_t s;
+  CUDA_TRY (cudaStreamCreateWithFlags (&s, cudaStreamNonBlocking));
+  nnsb_stream *st = new (std::nothrow) nnsb_stream ();
+  if (!st) {
+    cudaStreamDestroy (s);
+    return nnsb_set_error (NNSB_ENOMEM, "nnsb_stream_create: out of memory");
+  }
+  st->ctx = ctx;
+  st->s = s;
+  st->owned = true;
+  *out = st;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_stream_wrap (nnsb_ctx * ctx, void *cuda_stream, nnsb_stream ** out)
+{
+  if (!out || !ctx)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_stream_wrap: null argument");
+  nnsb_stream *st = new (std::nothrow) nnsb_stream ();
+  if (!st)
+    return nnsb_set_error (NNSB_ENOMEM, "nnsb_stream_wrap: out of memory");
+  st->ctx = ctx;
+  st->s = (cudaStream_t) cuda_stream;
+  st->owned = false;
+  *out = st;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_stream_sync (nnsb_stream * s)
+{
+  if (!s)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_stream_sync: null stream");
+  int r = bind (s->ctx);
+  if (r)
+    return r;
+  CUDA_TRY (cudaStreamSynchronize (s->s));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_stream_destroy (nnsb_stream * s)
+{
+  if (!s)
+    return NNSB_OK;
+  if (s->owned && bind (s->ctx) == NNSB_OK) {
+    cudaStreamSynchronize (s->s);
+    cudaStreamDestroy (s->s);
+  }
+  delete s;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_event_create (nnsb_ctx * ctx, nnsb_event ** out)
+{
+  if (!out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_event_create: null argument");
+  *out = nullptr;
+  int r = bind (ctx);
+  if (r)
+    return r;
+  cudaEvent_t e;
+  CUDA_TRY (cudaEventCreate (&e));
+  nnsb_event *ev = new (std::nothrow) nnsb_event ();
+  if (!ev) {
+    cudaEventDestroy (e);
+    return nnsb_set_error (NNSB_ENOMEM, "nnsb_event_create: out of memory");
+  }
+  ev->ctx = ctx;
+  ev->e = e;
+  *out = ev;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_event_record (nnsb_event * e, nnsb_stream * s)
+{
+  if (!e || !s)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_event_record: null argument");
+  int r = bind (e->ctx);
+  if (r)
+    return r;
+  CUDA_TRY (cudaEventRecord (e->e, s->s));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_event_sync (nnsb_event * e)
+{
+  if (!e)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_event_sync: null argument");
+  int r = bind (e->ctx);
+  if (r)
+    return r;
+  CUDA_TRY (cudaEventSynchronize (e->e));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_stream_wait_event (nnsb_stream * s, nnsb_event * e)
+{
+  if (!e || !s)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_stream_wait_event: null argument");
+  int r = bind (s->ctx);
+  if (r)
+    return r;
+  CUDA_TRY (cudaStreamWaitEvent (s->s, e->e, 0));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_event_elapsed_ms (nnsb_event * start, nnsb_event * stop, float *ms)
+{
+  if (!start || !stop || !ms)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_event_elapsed_ms: null argument");
+  int r = bind (start->ctx);
+  if (r)
+    return r;
+  CUDA_TRY (cudaEventElapsedTime (ms, start->e, stop->e));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_event_destroy (nnsb_event * e)
+{
+  if (!e)
+    return NNSB_OK;
+  if (bind (e->ctx) == NNSB_OK)
+    cudaEventDestroy (e->e);
+  delete e;
+  return NNSB_OK;
+}
+
+/* ------------------------------------------------------------------------------------- */
+/* memory                                                                                  */
+/* ------------------------------------------------------------------------------------- */
+extern "C" int
+nnsb_dev_alloc (nnsb_ctx * ctx, size_t size, void **out)
+{
+  if (!out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_dev_alloc: null argument");
+  *out = nullptr;
+  int r = bind (ctx);
+  if (r)
+    return r;
+  const size_t b = bucket_of (size);
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    auto it = ctx->dev_free.find (b);
+    if (it != ctx->dev_free.end () && !it->second.empty ()) {
+      void *p = it->second.back ();
+      it->second.pop_back ();
+      ctx->dev_live[p] = b;
+      *out = p;
+      return NNSB_OK;
+    }
+  }
+  void *p = nullptr;
+  cudaError_t e = cudaMalloc (&p, b);
+  if (e != cudaSuccess) {
+    /* give cached blocks back and retry once */
+    nnsb_dev_trim (ctx);
+    e = cudaMalloc (&p, b);
+    if (e != cudaSuccess) {
+      cudaGetLastError ();
+      return nnsb_set_error (NNSB_ENOMEM, "cudaMalloc (%zu) failed: %s", b, cudaGetErrorString (e));
+    }
+  }
+  std::lock_guard<std::mutex> lk (ctx->mu);
+  ctx->dev_live[p] = b;
+  *out = p;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_dev_free (nnsb_ctx * ctx, void *ptr)
+{
+  if (!ptr)
+    return NNSB_OK;
+  if (!ctx)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_dev_free: null context");
+  std::lock_guard<std::mutex> lk (ctx->mu);
+  auto it = ctx->dev_live.find (ptr);
+  if (it == ctx->dev_live.end ())
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_dev_free: %p was not allocated by this context", ptr);
+  ctx->dev_free[it->second].push_back (ptr);
+  ctx->dev_live.erase (it);
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_pinned_alloc (nnsb_ctx * ctx, size_t size, void **out)
+{
+  if (!out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_pinned_alloc: null argument");
+  *out = nullptr;
+  int r = bind (ctx);
+  if (r)
+    return r;
+  const size_t b = bucket_of (size);
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    auto it = ctx->pin_free.find (b);
+    if (it != ctx->pin_free.end () && !it->second.empty ()) {
+      void *p = it->second.back ();
+      it->second.pop_back ();
+      ctx->pin_live[p] = b;
+      *out = p;
+      return NNSB_OK;
+    }
+  }
+  void *p = nullptr;
+  cudaError_t e = cudaHostAlloc (&p, b, cudaHostAllocDefault);
+  if (e != cudaSuccess) {
+    cudaGetLastError ();
+    return nnsb_set_error (NNSB_ENOMEM, "cudaHostAlloc (%zu) failed: %s", b, cudaGetErrorString (e));
+  }
+  std::lock_guard<std::mutex> lk (ctx->mu);
+  ctx->pin_live[p] = b;
+  *out = p;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_pinned_free (nnsb_ctx * ctx, void *ptr)
+{
+  if (!ptr)
+    return NNSB_OK;
+  if (!ctx)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_pinned_free: null context");
+  std::lock_guard<std::mutex> lk (ctx->mu);
+  auto it = ctx->pin_live.find (ptr);
+  if (it == ctx->pin_live.end ())
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_pinned_free: %p was not allocated by this context", ptr);
+  ctx->pin_free[it->second].push_back (ptr);
+  ctx->pin_live.erase (it);
+  return NNSB_OK;
+}
+
+#define STREAM_PROLOGUE(name) \
+  if (!s) \
+    return nnsb_set_error (NNSB_EINVAL, name ": null stream"); \
+  { int r__ = bind (s->ctx); if (r__) return r__; }
+
+extern "C" int
+nnsb_dev_memset_async (nnsb_stream * s, void *dst, int value, size_t n)
+{
+  STREAM_PROLOGUE ("nnsb_dev_memset_async");
+  CUDA_TRY (cudaMemsetAsync (dst, value, n, s->s));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_h2d_async (nnsb_stream * s, void *dst_dev, const void *src_host, size_t n)
+{
+  STREAM_PROLOGUE ("nnsb_h2d_async");
+  if (n == 0)
+    return NNSB_OK;
+  CUDA_TRY (cudaMemcpyAsync (dst_dev, src_host, n, cudaMemcpyHostToDevice, s->s));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_d2h_async (nnsb_stream * s, void *dst_host, const void *src_dev, size_t n)
+{
+  STREAM_PROLOGUE ("nnsb_d2h_async");
+  if (n == 0)
+    return NNSB_OK;
+  CUDA_TRY (cudaMemcpyAsync (dst_host, src_dev, n, cudaMemcpyDeviceToHost, s->s));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_d2d_async (nnsb_stream * s, void *dst_dev, const void *src_dev, size_t n)
+{
+  STREAM_PROLOGUE ("nnsb_d2d_async");
+  if (n == 0)
+    return NNSB_OK;
+  CUDA_TRY (cudaMemcpyAsync (dst_dev, src_dev, n, cudaMemcpyDeviceToDevice, s->s));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_h2d_2d_async (nnsb_stream * s, void *dst_dev, size_t dst_pitch, const void *src_host,
+    size_t src_pitch, size_t row_bytes, size_t rows)
+{
+  STREAM_PROLOGUE ("nnsb_h2d_2d_async");
+  if (rows == 0 || row_bytes == 0)
+    return NNSB_OK;
+  CUDA_TRY (cudaMemcpy2DAsync (dst_dev, dst_pitch, src_host, src_pitch, row_bytes, rows,
+          cudaMemcpyHostToDevice, s->s));
+  return NNSB_OK;
+}
+
+/* ------------------------------------------------------------------------------------- */
+/* plans                                                                                   */
+/* ------------------------------------------------------------------------------------- */
+static bool
+is_64bit_int (int t)
+{
+  return t == NNSB_INT64 || t == NNSB_UINT64;
+}
+
+static LaunchCfg
+cfg_of (const nnsb_ctx * ctx)
+{
+  LaunchCfg c;
+  c.sm_count = ctx->sm_count;
+  c.blocks_per_sm = ctx->blocks_per_sm;
+  return c;
+}
+
+extern "C" int
+nnsb_plan_destroy (nnsb_plan * plan)
+{
+  if (!plan)
+    return NNSB_OK;
+  if (plan->d_table)
+    nnsb_dev_free (plan->ctx, plan->d_table);
+  if (plan->d_scratch)
+    nnsb_dev_free (plan->ctx, plan->d_scratch);
+  if (plan->d_stats)
+    nnsb_dev_free (plan->ctx, plan->d_stats);
+  delete plan;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_plan_create (nnsb_ctx * ctx, const nnsb_option * opt, const nnsb_tensor_info * in_info,
+    int acceleration, nnsb_plan ** out)
+{
+  if (!out || !opt || !in_info)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_create: null argument");
+  *out = nullptr;
+  int r = bind (ctx);
+  if (r)
+    return r;
+  if (in_info->type < 0 || in_info->type >= NNSB_TYPE_END || !nnsb_dim_is_valid (in_info->dim))
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_create: invalid input tensor info");
+
+  nnsb_plan *plan = new (std::nothrow) nnsb_plan ();
+  if (!plan)
+    return nnsb_set_error (NNSB_ENOMEM, "nnsb_plan_create: out of memory");
+  memset (plan, 0, sizeof (*plan));
+  plan->ctx = ctx;
+  plan->opt = *opt;
+  plan->in_info = *in_info;
+  r = nnsb_convert_dimension (opt, NNSB_PAD_SINK, in_info, &plan->out_info);
+  if (r) {
+    delete plan;
+    return r;
+  }
+  if (plan->out_info.type < 0 || plan->out_info.type >= NNSB_TYPE_END) {
+    delete plan;
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_create: invalid output type");
+  }
+  plan->in_size = nnsb_info_size (&plan->in_info);
+  plan->out_size = nnsb_info_size (&plan->out_info);
+  plan->frame_elems = nnsb_element_count (in_info->dim);
+  /* orc_supported (gsttensor_transform.c:462-463) */
+  plan->acceleration = acceleration && !is_64bit_int (plan->in_info.type)
+      && !is_64bit_int (plan->out_info.type);
+
+  switch (opt->mode) {
+    case NNSB_MODE_TYPECAST:
+      memset (&plan->chain, 0, sizeof (plan->chain));
+      plan->chain.desc.nch = 1;
+      plan->chain.desc.ch_size = 1;
+      break;
+    case NNSB_MODE_ARITHMETIC:
+    {
+      nnsb_cell *table = nullptr;
+      r = nnsb_chain_compile (opt, plan->out_info.type, plan->acceleration, in_info->dim,
+          &plan->chain.desc, &table);
+      if (r == NNSB_OK && table) {
+        const size_t bytes = sizeof (nnsb_cell) * plan->chain.desc.n_pos * plan->chain.desc.nch;
+        void *d = nullptr;
+        r = nnsb_dev_alloc (ctx, bytes, &d);
+        if (r == NNSB_OK) {
+          plan->d_table = (nnsb_cell *) d;
+          cudaError_t e = cudaMemcpy (d, table, bytes, cudaMemcpyHostToDevice);
+          if (e != cudaSuccess)
+            r = nnsb_set_error (NNSB_ECUDA, "cudaMemcpy (chain table) failed: %s",
+                cudaGetErrorString (e));
+        }
+        plan->chain.table = plan->d_table;
+      }
+      free (table);
+      if (r) {
+        nnsb_plan_destroy (plan);
+        return r;
+      }
+      break;
+    }
+    case NNSB_MODE_TRANSPOSE:
+    {
+      /* out dim i <- in dim order[i] (gsttensor_transform.c:1924-1928); dims 4..7 stay */
+      uint64_t in_strides[NNSB_RANK_LIMIT];
+      uint64_t s = 1;
+      for (int i = 0; i < NNSB_RANK_LIMIT; i++) {
+        in_strides[i] = s;
+        s *= in_info->dim[i];
+      }
+      plan->perm.rank = NNSB_RANK_LIMIT;
+      plan->perm.es = (int) nnsb_element_size (in_info->type);
+      for (int i = 0; i < NNSB_RANK_LIMIT; i++) {
+        const int src = i < NNSB_TRANSPOSE_RANK_LIMIT ? opt->trans_order[i] : i;
+        plan->perm.size[i] = in_info->dim[src];
+        plan->perm.in_stride[i] = in_strides[src];
+      }
+      break;
+    }
+    case NNSB_MODE_DIMCHG:
+    {
+      const int from = opt->dimchg_from, to = opt->dimchg_to;
+      if (from > to) {
+        /* gsttensor_transform.c:1179-1188: negotiates, then fails at run time */
+        nnsb_plan_destroy (plan);
+        return nnsb_set_error (NNSB_ENOTSUP,
+            "tensor-transform/dimchg operation is not permitted if from >= to.");
+      }
+      uint64_t in_strides[NNSB_RANK_LIMIT];
+      uint64_t s = 1;
+      for (int i = 0; i < NNSB_RANK_LIMIT; i++) {
+        in_strides[i] = s;
+        s *= in_info->dim[i];
+      }
+      plan->perm.rank = NNSB_RANK_LIMIT;
+      plan->perm.es = (int) nnsb_element_size (in_info->type);
+      for (int i = 0; i < NNSB_RANK_LIMIT; i++) {
+        int src;
+        if (i < from || i > to || from == to)
+          src = i;
+        else if (i == to)
+          src = from;
+        else
+          src = i + 1;
+        plan->perm.size[i] = in_info->dim[src];
+        plan->perm.in_stride[i] = in_strides[src];
+      }
+      break;
+    }
+    case NNSB_MODE_STAND:
+      if (opt->stand_mode != NNSB_STAND_DEFAULT && opt->stand_mode != NNSB_STAND_DC_AVERAGE) {
+        nnsb_plan_destroy (plan);
+        return nnsb_set_error (NNSB_EINVAL, "stand: cannot identify mode");
+      }
+      plan->stand_nch = opt->stand_per_channel ? in_info->dim[0] : 1;
+      break;
+    case NNSB_MODE_CLAMP:
+      break;
+    default:
+      nnsb_plan_destroy (plan);
+      return nnsb_set_error (NNSB_ENOTSUP, "Not supported tensor transform mode");
+  }
+  *out = plan;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_plan_out_info (const nnsb_plan * plan, nnsb_tensor_info * out_info)
+{
+  if (!plan || !out_info)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_out_info: null argument");
+  *out_info = plan->out_info;
+  return NNSB_OK;
+}
+
+extern "C" size_t
+nnsb_plan_in_size (const nnsb_plan * plan)
+{
+  return plan ? plan->in_size : 0;
+}
+
+extern "C" size_t
+nnsb_plan_out_size (const nnsb_plan * plan)
+{
+  return plan ? plan->out_size : 0;
+}
+
+extern "C" int
+nnsb_plan_last_launch_count (const nnsb_plan * plan)
+{
+  return plan ? plan->last_launches : NNSB_EINVAL;
+}
+
+static int
+grow (nnsb_ctx * ctx, double **buf, size_t * have, size_t need)
+{
+  if (*have >= need && *buf)
+    return NNSB_OK;
+  if (*buf) {
+    /* a previous launch may still be reading the old buffer */
+    cudaDeviceSynchronize ();
+    nnsb_dev_free (ctx, *buf);
+  }
+  *buf = nullptr;
+  *have = 0;
+  void *p = nullptr;
+  int r = nnsb_dev_alloc (ctx, need * sizeof (double), &p);
+  if (r)
+    return r;
+  *buf = (double *) p;
+  *have = need;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_plan_launch (nnsb_plan * plan, const void *d_in, void *d_out, uint32_t batch,
+    nnsb_stream * s)
+{
+  if (!plan || !s)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_launch: null argument");
+  int r = bind (plan->ctx);
+  if (r)
+    return r;
+  plan->last_launches = 0;
+  if (batch == 0)
+    return NNSB_OK;
+  if (!d_in || !d_out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_launch: null device pointer");
+  const LaunchCfg cfg = cfg_of (plan->ctx);
+  const size_t n = (size_t) plan->frame_elems * batch;
+  int err = 0;
+  switch (plan->opt.mode) {
+    case NNSB_MODE_TYPECAST:
+    case NNSB_MODE_ARITHMETIC:
+      err = launch_chain (plan->in_info.type, plan->out_info.type, plan->acceleration != 0, d_in,
+          d_out, n, plan->chain, cfg, s->s);
+      plan->last_launches = 1;
+      break;
+    case NNSB_MODE_CLAMP:
+      err = launch_clamp (plan->in_info.type, d_in, d_out, n, plan->opt.clamp_min,
+          plan->opt.clamp_max, cfg, s->s);
+      plan->last_launches = 1;
+      break;
+    case NNSB_MODE_TRANSPOSE:
+    case NNSB_MODE_DIMCHG:
+      err = launch_permute (plan->perm, d_in, d_out, plan->frame_elems, batch, cfg, s->s);
+      plan->last_launches = 1;
+      break;
+    case NNSB_MODE_STAND:
+    {
+      const size_t need_scratch = stand_scratch_doubles (batch, plan->stand_nch,
+          plan->frame_elems, cfg);
+      const size_t need_stats = (size_t) batch * plan->stand_nch * 2;
+      r = grow (plan->ctx, &plan->d_scratch, &plan->scratch_doubles, need_scratch);
+      if (r)
+        return r;
+      r = grow (plan->ctx, &plan->d_stats, &plan->stats_doubles, need_stats);
+      if (r)
+        return r;
+      int nl = 0;
+      err = launch_stand (plan->in_info.type, plan->out_info.type, plan->opt.stand_mode, d_in,
+          d_out, plan->frame_elems, plan->stand_nch, batch, plan->d_scratch, plan->d_stats, cfg,
+          s->s, &nl);
+      plan->last_launches = nl;
+      break;
+    }
+    default:
+      return nnsb_set_error (NNSB_ENOTSUP, "Not supported tensor transform mode");
+  }
+  if (err)
+    return nnsb_set_error (NNSB_ECUDA, "kernel launch failed: %s",
+        cudaGetErrorString ((cudaError_t) err));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_plan_stand_stats (nnsb_plan * plan, nnsb_stream * s, uint32_t batch, double *mean_out,
+    double *std_out, size_t capacity)
+{
+  if (!plan || !s || plan->opt.mode != NNSB_MODE_STAND)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_stand_stats: not a stand plan");
+  int r = bind (plan->ctx);
+  if (r)
+    return r;
+  const size_t cnt = (size_t) batch * plan->stand_nch;
+  if (cnt > capacity || cnt * 2 > plan->stats_doubles)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_stand_stats: capacity too small");
+  std::vector<double> tmp (cnt * 2);
+  CUDA_TRY (cudaMemcpyAsync (tmp.data (), plan->d_stats, cnt * 2 * sizeof (double),
+          cudaMemcpyDeviceToHost, s->s));
+  CUDA_TRY (cudaStreamSynchronize (s->s));
+  for (size_t i = 0; i < cnt; i++) {
+    if (mean_out)
+      mean_out[i] = tmp[2 * i];
+    if (std_out)
+      std_out[i] = tmp[2 * i + 1];
+  }
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_strip_launch (nnsb_stream * s, const void *d_src, void *d_dst, size_t row_bytes,
+    size_t src_pitch, size_t rows)
+{
+  STREAM_PROLOGUE ("nnsb_strip_launch");
+  if (!d_src || !d_dst)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_strip_launch: null device pointer");
+  int err = launch_strip (d_src, d_dst, row_bytes, src_pitch, rows, cfg_of (s->ctx), s->s);
+  if (err)
+    return nnsb_set_error (NNSB_ECUDA, "strip launch failed: %s",
+        cudaGetErrorString ((cudaError_t) err));
+  return NNSB_OK;
+}
