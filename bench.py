@@ -1,0 +1,393 @@
+#!/usr/bin/env python3
+"""bench.py -- tensor_transform hot path on B200: 1080p frames/s, GB/s, HBM-roofline fraction.
+
+Workload (BASELINE.json configs[1], the configuration the metric is quoted on):
+  one tensor 3:1920:1080:32 uint8 (199 065 600 B, uniform 0..255, seed 2) ->
+  tensor_transform mode=arithmetic
+     option=typecast:float32,per-channel:true@0,add:-123.675@0,add:-116.28@1,add:-103.53@2,
+            div:58.395@0,div:57.12@1,div:57.375@2                (ImageNet mean/std)
+  -> 3:1920:1080:32 float32 (796 262 400 B).  A "step" = one pass over that 32-frame batch.
+
+  value  : device-resident frames/s (inputs already in HBM), CUDA events, max over ranks.
+  e2e    : same metric through the host-buffer path: pinned host input -> H2D -> kernel ->
+           D2H into pinned host output, every step, copies inside the timed region.
+  roofline: algorithmic bytes per launch (5 B/element) / measured launch time vs the measured
+           HBM copy bandwidth of this pool (MEASURED_PEAKS.json).
+  cpu_baseline: the reference's own C code (oracle/_ref) or the C port timed on the host cores.
+
+Multi-GPU (--gpus N under torchrun): streams are independent, so each rank runs its own
+32-frame batch on its own GPU ("weak" scaling); NCCL is used only for the barrier and the
+max-over-ranks of the timings -- the data path has no collective.
+
+`--impl reference` times the reference CPU implementation of the same step on the host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+W, H, C, B = 1920, 1080, 3, 32
+DIM = [C, W, H, 1]
+FRAME_ELEMS = C * W * H
+OPTION = ("typecast:float32,per-channel:true@0,add:-123.675@0,add:-116.28@1,add:-103.53@2,"
+          "div:58.395@0,div:57.12@1,div:57.375@2")
+ORACLE_OPS = [("typecast", "float32"), ("add", -123.675, 0), ("add", -116.28, 1),
+              ("add", -103.53, 2), ("div", 58.395, 0), ("div", 57.12, 1), ("div", 57.375, 2)]
+WORKLOAD = "3:1920:1080:32 uint8 -> float32, arithmetic " + OPTION
+ALGO_BYTES_PER_ELEM = 5           # sizeof(u8) + sizeof(f32), SURVEY.md 8d
+METRIC = "tensor_transform_1080p_frames_per_sec"
+UNIT = "frames/s"
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------
+# CPU side (oracle): cpu_baseline leg and --impl reference
+# ---------------------------------------------------------------------------------------
+def cpu_checker():
+    from oracle import oracle as O
+    if O.ref_available():
+        return O.ref(), "reference"
+    return O.port(), "port"
+
+
+def cpu_run_frames(checker, frames, n_threads):
+    """Run the reference CPU arithmetic on `frames` (list of u8 arrays), one frame per task,
+    n_threads worker threads (ctypes releases the GIL).  Returns wall seconds."""
+    idx = [0]
+    lock = threading.Lock()
+
+    def worker():
+        while True:
+            with lock:
+                i = idx[0]
+                idx[0] += 1
+            if i >= len(frames):
+                return
+            checker.arithmetic(frames[i], DIM, ORACLE_OPS, True, 0)
+
+    ths = [threading.Thread(target=worker) for _ in range(n_threads)]
+    t0 = time.perf_counter()
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(sample_frames=None):
+    checker, kind = cpu_checker()
+    cores = os.cpu_count() or 1
+    rng = np.random.default_rng(2)
+    frame = rng.integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
+    t1 = cpu_run_frames(checker, [frame], 1)            # warm-up + per-frame cost
+    if sample_frames is None:
+        # ~15 s of CPU work in total, at least one frame per core
+        sample_frames = int(max(cores, min(4 * cores, 15.0 / max(t1, 1e-3))))
+    frames = [frame] * sample_frames
+    dt = cpu_run_frames(checker, frames, cores)
+    return {"value": sample_frames / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": "%d 1080p frames of the bench workload, one frame per task on %d threads "
+                      "(%.3f s single-thread per frame)" % (sample_frames, cores, t1)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    checker, kind = cpu_checker()
+    cores = os.cpu_count() or 1
+    rng = np.random.default_rng(2)
+    frame = rng.integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
+    frames = [frame] * B
+    for _ in range(args.warmup):
+        cpu_run_frames(checker, frames[:cores], cores)
+    t = 0.0
+    for _ in range(args.steps):
+        t += cpu_run_frames(checker, frames, cores)
+    value = args.steps * B / t
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch_frames": B},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": "each step = the full 32-frame batch, one frame per task on "
+                                   "%d host threads" % cores},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------
+# GPU side
+# ---------------------------------------------------------------------------------------
+def time_launches(dev, fn, steps, warmup):
+    for _ in range(warmup):
+        fn()
+    dev.sync()
+    e0, e1 = dev.event(), dev.event()
+    dev.record(e0)
+    for _ in range(steps):
+        fn()
+    dev.record(e1)
+    ms = dev.elapsed_ms(e0, e1)
+    dev.event_destroy(e0)
+    dev.event_destroy(e1)
+    return ms
+
+
+def extra_kernels(dev, peak):
+    """Device-resident GB/s of the other modes at their BASELINE configs (informational)."""
+    out = {}
+    rng = np.random.default_rng(3)
+
+    def run(name, mode, option, itype, dim, batch, bytes_per_elem, make):
+        plan = dev.plan(mode, option, itype, dim)
+        n = int(np.prod(dim)) * batch
+        host = make(n)
+        d_in = dev.upload(host)
+        d_out = dev.alloc(plan.out_size * batch)
+        ms = time_launches(dev, lambda: plan.launch(d_in, d_out, batch), 10, 3) / 10
+        gbs = n * bytes_per_elem / (ms * 1e-3) / 1e9
+        out[name] = {"ms": ms, "GB/s": gbs, "frac_of_measured_peak": gbs / peak,
+                     "launches": plan.last_launch_count}
+        dev.free(d_in)
+        dev.free(d_out)
+        plan.close()
+
+    f32 = lambda n: rng.standard_normal(n, dtype=np.float32)
+    u8 = lambda n: rng.integers(0, 256, n, dtype=np.uint8)
+    run("typecast_u8_f32_1080p_b32", "typecast", "float32", "uint8", DIM, B, 5, u8)
+    run("arith_scalar_u8_f32_1080p_b32", "arithmetic", "typecast:float32,add:-127.5,div:127.5",
+        "uint8", DIM, B, 5, u8)
+    run("transpose_hwc_chw_4k_f32", "transpose", "1:2:0:3", "float32", [3, 3840, 2160, 1], 1, 8, f32)
+    run("transpose_hwc_chw_4k_f32_b8", "transpose", "1:2:0:3", "float32", [3, 3840, 2160, 1], 8, 8, f32)
+    run("dimchg_0_2_4k_f32", "dimchg", "0:2", "float32", [3, 3840, 2160, 1], 1, 8, f32)
+    run("clamp_f32_1080p_b64", "clamp", "-33.3:77.7", "float32", DIM, 64, 8, f32)
+    run("stand_default_f32_1080p_b64_per_frame", "stand", "default", "float32", DIM, 64, 8, f32)
+    run("stand_dc_perch_f32_1080p_b64_per_frame", "stand", "dc-average,per-channel:true",
+        "float32", DIM, 64, 8, f32)
+    run("stand_default_f32_1080p_x64_one_tensor", "stand", "default", "float32",
+        [3, 1920, 1080, 64], 1, 8, f32)
+    return out
+
+
+def run_b200(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    from nnstreamer_b200 import Device
+    dev = Device(local_rank)
+    peak, peak_src = measured_peak()
+
+    rng = np.random.default_rng(2 + rank)
+    n = FRAME_ELEMS * B
+    h_in, h_in_ptr = dev.pinned(n, np.uint8)
+    h_in[:] = rng.integers(0, 256, n, dtype=np.uint8)
+    h_out, h_out_ptr = dev.pinned(4 * n, np.float32)
+    d_in = dev.alloc(n)
+    d_out = dev.alloc(4 * n)
+    dev.h2d(d_in, h_in)
+    dev.sync()
+    plan = dev.plan("arithmetic", OPTION, "uint8", DIM)
+
+    def barrier():
+        dev.sync()
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident: K launches, CUDA events on the launching stream ----
+    step = lambda: plan.launch(d_in, d_out, B)
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = dev.event(), dev.event()
+    dev.record(e0)
+    for _ in range(args.steps):
+        step()
+    dev.record(e1)
+    ms_dev = dev.elapsed_ms(e0, e1)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_dev = max_over_ranks(ms_dev)
+    launches = plan.last_launch_count * args.steps
+
+    # ---- end to end: pinned host -> H2D -> kernel -> D2H pinned, every step ----
+    def e2e_step():
+        dev.h2d(d_in, h_in)
+        plan.launch(d_in, d_out, B)
+        dev.d2h(h_out, d_out)
+
+    for _ in range(max(1, min(args.warmup, 3))):
+        e2e_step()
+    barrier()
+    dev.record(e0)
+    for _ in range(args.steps):
+        e2e_step()
+    dev.record(e1)
+    ms_e2e = dev.elapsed_ms(e0, e1)
+    barrier()
+    ms_e2e = max_over_ranks(ms_e2e)
+
+    # ---- parity spot check on the bench data (first frame, against the oracle) ----
+    parity = None
+    cpu = None
+    extras = None
+    if rank == 0:
+        from oracle import oracle as O
+        got = h_out[:FRAME_ELEMS].copy()
+        want = O.port().arithmetic(h_in[:FRAME_ELEMS], DIM, ORACLE_OPS, True, 0)
+        parity = bool(got.tobytes() == want.tobytes())
+        if world == 1:
+            cpu = cpu_baseline()
+            if not args.no_extras:
+                dev.free(d_in)
+                dev.free(d_out)
+                d_in = d_out = None
+                extras = extra_kernels(dev, peak)
+
+    if rank == 0:
+        ms_step = ms_dev / args.steps
+        algo_bytes = n * ALGO_BYTES_PER_ELEM
+        achieved = algo_bytes / (ms_step * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": world * B * args.steps / (ms_dev * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch_frames": B,
+                       "l2": "inputs larger than L2 (199 MB in + 796 MB out per step vs 126 MB L2)",
+                       "sharding": "one independent 32-frame stream per GPU, no collective"},
+            "GB/s": world * achieved,
+            "e2e": {"value": world * B * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": n, "d2h_bytes_per_step": 4 * n,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "frac_of_nominal_8TBs": achieved / 8000.0,
+                         "traffic": None, "peak_source": peak_src,
+                         "kernel": "chain_kernel<uint8,float,C,4> (k_chain.cuh)",
+                         "algorithmic_bytes_per_launch": algo_bytes},
+            "cpu_baseline": cpu,
+            "clocks": clocks,
+            "parity_vs_oracle_first_frame": parity,
+        }
+        if extras is not None:
+            line["kernels"] = extras
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    dev.close()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the informational per-kernel table")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -56,7 +56,6 @@ class Device:
         L.check(self._lib.nnsb_pinned_alloc(self.ctx, nbytes, C.byref(p)))
         buf = (C.c_uint8 * nbytes).from_address(p.value)
         arr = np.frombuffer(buf, dtype=np.uint8, count=nbytes).view(dtype)
-        arr._nnsb_ptr = p.value if hasattr(arr, "__dict__") else None
         return arr, p.value
 
     def pinned_free(self, ptr):
