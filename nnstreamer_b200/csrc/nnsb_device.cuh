@@ -183,6 +183,51 @@ __device__ __forceinline__ float u8_to_f32 (uint32_t byte)
   return __fsub_rn (__uint_as_float (0x4B000000u | byte), 8388608.0f);
 }
 
+/* float <-> float conversions the way x86 does them (cvtss2sd, cvtsd2ss, vcvtph2ps,
+ * vcvtps2ph / libgcc): round to nearest even; a NaN keeps its sign and the top payload bits
+ * and becomes quiet.  CUDA's cvt returns a canonical NaN instead, hence the explicit paths. */
+__device__ __forceinline__ float f16_to_f32 (__half h)
+{
+  const unsigned short b = __half_as_ushort (h);
+  if ((b & 0x7fffu) > 0x7c00u)
+    return __uint_as_float (((uint32_t) (b & 0x8000u) << 16) | 0x7fc00000u | ((uint32_t) (b & 0x3ffu) << 13));
+  return __half2float (h);
+}
+__device__ __forceinline__ __half f32_to_f16 (float f)
+{
+  if (f != f) {
+    const uint32_t u = __float_as_uint (f);
+    return __ushort_as_half ((unsigned short) (((u >> 16) & 0x8000u) | 0x7e00u | ((u >> 13) & 0x1ffu)));
+  }
+  return __float2half_rn (f);
+}
+__device__ __forceinline__ __half f64_to_f16 (double d)
+{
+  if (d != d) {
+    const unsigned long long u = (unsigned long long) __double_as_longlong (d);
+    return __ushort_as_half ((unsigned short) (((u >> 48) & 0x8000u) | 0x7e00u | ((u >> 42) & 0x1ffu)));
+  }
+  return __double2half (d);
+}
+__device__ __forceinline__ double f32_to_f64 (float f)
+{
+  if (f != f) {
+    const unsigned long long u = __float_as_uint (f);
+    return __longlong_as_double ((long long) (((u & 0x80000000ull) << 32) | 0x7ff8000000000000ull
+            | ((u & 0x7fffffull) << 29)));
+  }
+  return (double) f;
+}
+__device__ __forceinline__ float f64_to_f32 (double d)
+{
+  if (d != d) {
+    const unsigned long long u = (unsigned long long) __double_as_longlong (d);
+    return __uint_as_float ((uint32_t) ((u >> 32) & 0x80000000u) | 0x7fc00000u
+        | (uint32_t) ((u >> 29) & 0x3fffffu));
+  }
+  return __double2float_rn (d);
+}
+
 /* ------------------------------------------------------------------------------------- */
 /* CCast: `(To) from` as the reference's C path performs it                                */
 /* gst_tensor_data_typecast, tensor_data.c:202-279: float sources reach an unsigned target */
@@ -209,13 +254,13 @@ template <typename To, typename From> struct CCast
       }
       return (To) s;
     } else if constexpr (IsFloat<From>::v && IsFloat<To>::v) {
-      if constexpr (sizeof (From) == 2 && sizeof (To) == 2) return x;
-      else if constexpr (sizeof (From) == 2 && sizeof (To) == 4) return __half2float (x);
-      else if constexpr (sizeof (From) == 2 && sizeof (To) == 8) return (double) __half2float (x);
-      else if constexpr (sizeof (To) == 2 && sizeof (From) == 4) return __float2half_rn (x);
-      else if constexpr (sizeof (To) == 2 && sizeof (From) == 8) return __double2half (x);
-      else if constexpr (sizeof (To) == 4 && sizeof (From) == 8) return __double2float_rn (x);
-      else return (To) x;
+      if constexpr (sizeof (From) == sizeof (To)) return x;
+      else if constexpr (sizeof (From) == 2 && sizeof (To) == 4) return f16_to_f32 (x);
+      else if constexpr (sizeof (From) == 2 && sizeof (To) == 8) return f32_to_f64 (f16_to_f32 (x));
+      else if constexpr (sizeof (To) == 2 && sizeof (From) == 4) return f32_to_f16 (x);
+      else if constexpr (sizeof (To) == 2 && sizeof (From) == 8) return f64_to_f16 (x);
+      else if constexpr (sizeof (To) == 4 && sizeof (From) == 8) return f64_to_f32 (x);
+      else return f32_to_f64 (x);
     } else if constexpr (!IsFloat<From>::v && IsFloat<To>::v) {
       /* integer -> float: round to nearest even, one rounding */
       if constexpr (sizeof (To) == 2) {
@@ -331,6 +376,24 @@ template <typename T> __device__ __forceinline__ T cell_get (const nnsb_cell &c)
   return v;
 }
 
+/* x86 SSE NaN rules for a binary operation r = a op b: a NaN operand is returned quieted
+ * (the first operand wins), an invalid operation (inf-inf, 0*inf, 0/0, inf/inf) returns the
+ * default NaN, which has the SIGN BIT SET.  CUDA returns canonical 0x7fffffff instead. */
+__device__ __forceinline__ float nan_fix (float r, float a, float b)
+{
+  if (r == r) return r;
+  if (a != a) return __uint_as_float (__float_as_uint (a) | 0x00400000u);
+  if (b != b) return __uint_as_float (__float_as_uint (b) | 0x00400000u);
+  return __uint_as_float (0xffc00000u);
+}
+__device__ __forceinline__ double nan_fix (double r, double a, double b)
+{
+  if (r == r) return r;
+  if (a != a) return __longlong_as_double (__double_as_longlong (a) | 0x0008000000000000ll);
+  if (b != b) return __longlong_as_double (__double_as_longlong (b) | 0x0008000000000000ll);
+  return __longlong_as_double ((long long) 0xfff8000000000000ull);
+}
+
 /* C path: handle_operator, gsttensor_transform.c:563-582 (+=, *=, /= in the working type;
  * narrow integers are promoted to int and truncated back, i.e. modular) */
 template <typename T, bool ORC> struct Arith
@@ -338,11 +401,12 @@ template <typename T, bool ORC> struct Arith
   static __device__ __forceinline__ T add (T a, T b)
   {
     if constexpr (sizeof (T) == 2 && IsFloat<T>::v) {
-      return __float2half_rn (__fadd_rn (__half2float (a), __half2float (b)));
+      const float fa = f16_to_f32 (a), fb = f16_to_f32 (b);
+      return f32_to_f16 (nan_fix (__fadd_rn (fa, fb), fa, fb));
     } else if constexpr (sizeof (T) == 4 && IsFloat<T>::v) {
-      return __fadd_rn (a, b);
+      return nan_fix (__fadd_rn (a, b), a, b);
     } else if constexpr (sizeof (T) == 8 && IsFloat<T>::v) {
-      return __dadd_rn (a, b);
+      return nan_fix (__dadd_rn (a, b), a, b);
     } else if constexpr (ORC) {
       /* addssb/addusb/addssw/addusw/addssl/addusl: saturating */
       if constexpr (sizeof (T) == 4 && IsSigned<T>::v) {
@@ -370,11 +434,12 @@ template <typename T, bool ORC> struct Arith
   static __device__ __forceinline__ T mul (T a, T b)
   {
     if constexpr (sizeof (T) == 2 && IsFloat<T>::v) {
-      return __float2half_rn (__fmul_rn (__half2float (a), __half2float (b)));
+      const float fa = f16_to_f32 (a), fb = f16_to_f32 (b);
+      return f32_to_f16 (nan_fix (__fmul_rn (fa, fb), fa, fb));
     } else if constexpr (sizeof (T) == 4 && IsFloat<T>::v) {
-      return __fmul_rn (a, b);
+      return nan_fix (__fmul_rn (a, b), a, b);
     } else if constexpr (sizeof (T) == 8 && IsFloat<T>::v) {
-      return __dmul_rn (a, b);
+      return nan_fix (__dmul_rn (a, b), a, b);
     } else if constexpr (ORC) {
       /* mul[su]bw+conv, mul[su]wl+conv, mul[su]lq+conv: widening multiply, saturating narrow */
       if constexpr (sizeof (T) == 4 && IsSigned<T>::v) {
@@ -402,11 +467,12 @@ template <typename T, bool ORC> struct Arith
   static __device__ __forceinline__ T div (T a, T b)
   {
     if constexpr (sizeof (T) == 2 && IsFloat<T>::v) {
-      return __float2half_rn (__fdiv_rn (__half2float (a), __half2float (b)));
+      const float fa = f16_to_f32 (a), fb = f16_to_f32 (b);
+      return f32_to_f16 (nan_fix (__fdiv_rn (fa, fb), fa, fb));
     } else if constexpr (sizeof (T) == 4 && IsFloat<T>::v) {
-      return __fdiv_rn (a, b);
+      return nan_fix (__fdiv_rn (a, b), a, b);
     } else if constexpr (sizeof (T) == 8 && IsFloat<T>::v) {
-      return __ddiv_rn (a, b);
+      return nan_fix (__ddiv_rn (a, b), a, b);
     } else if constexpr (IsSigned<T>::v) {
       /* C division truncates toward zero; INT_MIN / -1 (a trap on x86) is defined here as
        * the wrapped value so the kernel cannot fault */

@@ -21,6 +21,14 @@ def rand_full(dtype, n, seed):
             sp = special.astype(dt)
         k = min(len(sp), n)
         x[:k] = sp[:k]
+        # NaNs with payloads (quiet/signalling, both signs): x86 propagates them, so must we
+        ui = {2: np.uint16, 4: np.uint32, 8: np.uint64}[dt.itemsize]
+        pats = {2: [0x7e01, 0xfe00, 0x7d55, 0xfc01, 0x7fff],
+                4: [0x7fc00001, 0xffc00000, 0x7fa55555, 0xff800001, 0x7fffffff],
+                8: [0x7ff8000000000001, 0xfff8000000000000, 0x7ff5555555555555,
+                    0xfff0000000000001, 0x7fffffffffffffff]}[dt.itemsize]
+        if n >= k + len(pats):
+            x.view(ui)[k:k + len(pats)] = np.array(pats, dtype=ui)
         return x
     info = np.iinfo(dt)
     x = rng.integers(info.min, info.max, n, dtype=dt, endpoint=True)
