@@ -263,6 +263,25 @@ NNSB_API int nnsb_plan_stand_stats (nnsb_plan * plan, nnsb_stream * s, uint32_t 
 NNSB_API int nnsb_strip_launch (nnsb_stream * s, const void *d_src, void *d_dst,
     size_t row_bytes, size_t src_pitch, size_t rows);
 
+/* No counterpart in the reference (its CPU element simply mallocs).  The same stand kernels
+ * as nnsb_plan_launch(), for callers that must not allocate while frames are flowing: a
+ * pipeline whose GPU memory is already fully reserved by an inference runtime's pool, a
+ * streaming thread that cannot tolerate the unbounded latency of cudaMalloc, or a plug-in
+ * that is handed only a CUDA stream and device pointers.  No cudaMalloc / cudaFree / pool is
+ * touched: the scratch is a fixed NNSB_NOALLOC_SCRATCH_BYTES array inside the loaded module
+ * (so every GPU that loads the library holds that much memory until exit).
+ *   d_in, d_out : `batch` tensors of shape `dim` back to back, on the CURRENT CUDA device
+ *   out_type    : NNSB_TYPE_END keeps the input type (the option's default)
+ *   cuda_stream : a cudaStream_t, NULL = default stream
+ * Fails with NNSB_ERANGE when batch x channels needs more scratch than the array holds.
+ * The first call on a device resolves the array's device address: make it before any stream
+ * capture.  All calls on a device share the array, so calls that may overlap on the GPU
+ * race with each other; keep them on one stream. */
+#define NNSB_NOALLOC_SCRATCH_BYTES (1u << 20)
+NNSB_API int nnsb_stand_launch_noalloc (const void *d_in, void *d_out, int in_type,
+    int out_type, const uint32_t *dim, int stand_mode, int per_channel, uint32_t batch,
+    void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

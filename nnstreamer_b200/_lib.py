@@ -15,6 +15,7 @@ SIZE_LIMIT = 16
 META_RANK_LIMIT = 16
 MAX_OPS = 64
 META_HEADER_SIZE = 128
+NOALLOC_SCRATCH_BYTES = 1 << 20
 
 # tensor_typedef.h:133-148
 TYPES = ["int32", "uint32", "int16", "uint16", "int8", "uint8", "float64", "float32",
@@ -124,6 +125,8 @@ _PROTOS = {
     "nnsb_plan_stand_stats": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(C.c_double),
                                         C.POINTER(C.c_double), C.c_size_t]),
     "nnsb_strip_launch": (C.c_int, [_VP, _VP, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),
+    "nnsb_stand_launch_noalloc": (C.c_int, [_VP, _VP, C.c_int, C.c_int, C.POINTER(C.c_uint32),
+                                            C.c_int, C.c_int, C.c_uint32, _VP]),
 }
 
 
