@@ -163,6 +163,157 @@ chain_kernel (const In *__restrict__ in, Out *__restrict__ out, size_t n, size_t
   }
 }
 
+/* ------------------------------------------------------------------------------------- */
+/* 1-byte inputs: the whole chain is a function of (channel, byte) -> 256 entries per        */
+/* channel.  Each block evaluates the table once with the SAME code path as the generic      */
+/* kernel (so results are identical by construction), then streams: one shared-memory        */
+/* lookup per element instead of a convert + N rounded operations (IEEE div is ~10 issue     */
+/* slots; at 5 B/element the generic u8->f32 kernel is issue-bound, not HBM-bound).           */
+/* ------------------------------------------------------------------------------------- */
+template <typename Out> struct LutVec
+{
+  static constexpr int V = (32 / sizeof (Out)) > 16 ? 16 : (32 / sizeof (Out));
+};
+
+template <typename In, typename Out, bool INVARIANT, int U>
+__device__ __forceinline__ void
+lut_stream (const In *__restrict__ in, Out *__restrict__ out, size_t n_vec, const Out *lut,
+    const ChainDev &p, size_t tid, size_t nthreads, bool perch)
+{
+  constexpr int V = LutVec<Out>::V;
+  uint64_t r = 0;
+  uint32_t c = 0;
+  if (perch) {
+    const uint64_t e0 = (uint64_t) tid * V;
+    r = e0 % p.ch_size;
+    c = (uint32_t) ((e0 / p.ch_size) % (uint64_t) p.nch);
+  }
+  /* per-lane table rows; loop-invariant when the grid stride is a multiple of the channel
+   * period (the launcher sizes the grid for that whenever it can) */
+  const Out *row[V];
+#pragma unroll
+  for (int k = 0; k < V; k++)
+    row[k] = lut;
+  if (INVARIANT && perch) {
+    uint64_t rr = r;
+    uint32_t cc = c;
+#pragma unroll
+    for (int k = 0; k < V; k++) {
+      row[k] = lut + (size_t) cc * 256;
+      if (++rr == p.ch_size) {
+        rr = 0;
+        cc = (cc + 1 == (uint32_t) p.nch) ? 0 : cc + 1;
+      }
+    }
+  }
+  for (size_t v = tid; v < n_vec; v += nthreads * U) {
+    Vec<In, V> x[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const size_t vu = v + (size_t) u * nthreads;
+      if (vu < n_vec)
+        load_vec (x[u], in + vu * V);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const size_t vu = v + (size_t) u * nthreads;
+      if (!INVARIANT && perch) {
+        uint64_t rr = r;
+        uint32_t cc = c;
+#pragma unroll
+        for (int k = 0; k < V; k++) {
+          row[k] = lut + (size_t) cc * 256;
+          if (++rr == p.ch_size) {
+            rr = 0;
+            cc = (cc + 1 == (uint32_t) p.nch) ? 0 : cc + 1;
+          }
+        }
+        r += p.step_r;
+        uint32_t carry = 0;
+        if (r >= p.ch_size) {
+          r -= p.ch_size;
+          carry = 1;
+        }
+        c += p.step_c + carry;
+        if (c >= (uint32_t) p.nch)
+          c -= (uint32_t) p.nch;
+      }
+      if (vu < n_vec) {
+        Vec<Out, V> y;
+#pragma unroll
+        for (int k = 0; k < V; k++)
+          y.e[k] = row[k][(uint8_t) x[u].e[k]];
+        store_vec (out + vu * V, y);
+      }
+    }
+  }
+}
+
+template <typename In, typename Out, bool ORC, int U>
+__global__ void __launch_bounds__ (CHAIN_THREADS)
+lut_chain_kernel (const In *__restrict__ in, Out *__restrict__ out, size_t n, size_t n_vec,
+    const __grid_constant__ ChainDev p)
+{
+  static_assert (sizeof (In) == 1, "table lookup needs a 1-byte input type");
+  constexpr int V = LutVec<Out>::V;
+  extern __shared__ __align__ (16) unsigned char lut_raw[];
+  Out *lut = reinterpret_cast<Out *> (lut_raw);
+  const bool perch = p.nch > 1;
+  const int entries = p.nch * 256;
+  for (int i = threadIdx.x; i < entries; i += CHAIN_THREADS) {
+    const uint8_t byte = (uint8_t) (i & 255);
+    In xv;
+    memcpy (&xv, &byte, 1);
+    Vec<Out, 1> y;
+    uint32_t ch[1] = { (uint32_t) (i >> 8) };
+    y.e[0] = Cast<Out, In, ORC>::run (xv);
+    chain_apply<Out, ORC, 1> (y, ch, p, perch);
+    lut[i] = y.e[0];
+  }
+  __syncthreads ();
+
+  const size_t tid = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t nthreads = (size_t) gridDim.x * blockDim.x;
+  if (p.step_r == 0 && p.step_c == 0)
+    lut_stream<In, Out, true, U> (in, out, n_vec, lut, p, tid, nthreads, perch);
+  else
+    lut_stream<In, Out, false, U> (in, out, n_vec, lut, p, tid, nthreads, perch);
+
+  for (size_t e = n_vec * V + tid; e < n; e += nthreads) {
+    In xv;
+    ld_stream<1> (&xv, in + e);
+    uint8_t byte;
+    memcpy (&byte, &xv, 1);
+    const uint32_t c = perch ? (uint32_t) (((uint64_t) e / p.ch_size) % (uint64_t) p.nch) : 0;
+    const Out y = lut[(size_t) c * 256 + byte];
+    st_stream<sizeof (Out)> (out + e, &y);
+  }
+}
+
+static inline uint64_t
+gcd_u64 (uint64_t a, uint64_t b)
+{
+  while (b) {
+    const uint64_t t = a % b;
+    a = b;
+    b = t;
+  }
+  return a;
+}
+
+/* Shrinks `blocks` so that one grid stride (blocks * threads * V elements) is a multiple of
+ * the channel period ch_size * nch; returns 0 if that would cost more than half the grid. */
+static inline size_t
+blocks_for_invariant_channels (size_t blocks, uint64_t elems_per_block, uint64_t period)
+{
+  if (period <= 1)
+    return blocks;
+  const uint64_t need = period / gcd_u64 (elems_per_block, period);
+  if (need == 0 || need > blocks / 2 + 1)
+    return 0;
+  return blocks / need * need;
+}
+
 template <typename In, typename Out, bool ORC>
 int launch_chain_t (const void *in, void *out, size_t n, const ChainArgs &args,
     const LaunchCfg &cfg, cudaStream_t stream)
@@ -185,16 +336,45 @@ int launch_chain_t (const void *in, void *out, size_t n, const ChainArgs &args,
 
   ChainDev p;
   p.n_pos = args.desc.n_pos;
-  p.nch = args.desc.nch;
+  p.nch = args.desc.nch > 0 ? args.desc.nch : 1;
   p.ch_size = args.desc.ch_size ? args.desc.ch_size : 1;
-  const uint64_t stride_elems = (uint64_t) blocks * CHAIN_THREADS * V;
-  p.step_r = stride_elems % p.ch_size;
-  p.step_c = (uint32_t) ((stride_elems / p.ch_size) % (uint64_t) (p.nch > 0 ? p.nch : 1));
   p.table = args.table;
   for (int i = 0; i < NNSB_MAX_OPS; i++) {
     p.opcode[i] = args.desc.opcode[i];
     p.scalar[i] = args.desc.scalar[i];
   }
+
+  if constexpr (sizeof (In) == 1) {
+    /* table path: a table that fits and enough elements to amortise building it (also used
+     * for a bare typecast: one lookup is no slower than the conversion and needs fewer
+     * registers, i.e. more warps in flight) */
+    constexpr int LV = LutVec<Out>::V;
+    const size_t lut_bytes = (size_t) p.nch * 256 * sizeof (Out);
+    const bool lut_aligned = ((uintptr_t) in % (LV * sizeof (In)) == 0)
+        && ((uintptr_t) out % (LV * sizeof (Out)) == 0);
+    if (lut_bytes <= 48 * 1024 && n >= 65536 && lut_aligned) {
+      const size_t l_vec = n / LV;
+      size_t lb = (l_vec + (size_t) CHAIN_THREADS * U - 1) / ((size_t) CHAIN_THREADS * U);
+      if (lb > cap)
+        lb = cap;
+      if (lb == 0)
+        lb = 1;
+      const uint64_t period = p.ch_size * (uint64_t) p.nch;
+      const size_t li = blocks_for_invariant_channels (lb, (uint64_t) CHAIN_THREADS * LV, period);
+      if (li)
+        lb = li;
+      const uint64_t stride = (uint64_t) lb * CHAIN_THREADS * LV;
+      p.step_r = stride % p.ch_size;
+      p.step_c = (uint32_t) ((stride / p.ch_size) % (uint64_t) p.nch);
+      lut_chain_kernel<In, Out, ORC, U><<<(unsigned int) lb, CHAIN_THREADS, lut_bytes, stream>>> (
+          (const In *) in, (Out *) out, n, l_vec, p);
+      return (int) cudaGetLastError ();
+    }
+  }
+
+  const uint64_t stride_elems = (uint64_t) blocks * CHAIN_THREADS * V;
+  p.step_r = stride_elems % p.ch_size;
+  p.step_c = (uint32_t) ((stride_elems / p.ch_size) % (uint64_t) p.nch);
   chain_kernel<In, Out, ORC, U><<<(unsigned int) blocks, CHAIN_THREADS, 0, stream>>> (
       (const In *) in, (Out *) out, n, n_vec, p);
   return (int) cudaGetLastError ();

@@ -160,6 +160,41 @@ def test_arith_chains_orc_path(dev, port, dtype):
         _arith_case(dev, port, x, [3, 33, 17], opt, ops, accel=True)
 
 
+@pytest.mark.parametrize("itype", ["uint8", "int8"])
+@pytest.mark.parametrize("accel", [False, True])
+def test_arith_one_byte_inputs_table_path(dev, port, itype, accel):
+    """>= 65536 one-byte elements take the shared-memory table kernel; it must equal the
+    oracle for every output type, scalar and per-channel (innermost, middle and odd channel
+    counts, i.e. both the loop-invariant and the walking channel mapping)."""
+    rng = np.random.default_rng(55)
+    info = np.iinfo(itype)
+    outs = ["float32", "uint8", "int16", "float64"] if accel else \
+        ["float32", "uint8", "int8", "int16", "uint16", "int32", "float64", "float16", "int64"]
+    for otype in outs:
+        dim = [3, 160, 144, 1]                  # 69120 elements
+        x = rng.integers(info.min, info.max, 69120, dtype=itype, endpoint=True)
+        _arith_case(dev, port, x, dim, "typecast:%s,add:-12,mul:3,div:7" % otype,
+                    [("typecast", otype), ("add", -12), ("mul", 3), ("div", 7)], accel=accel)
+        _arith_case(dev, port, x, dim,
+                    "typecast:%s,per-channel:true@0,add:-12@0,add:5@1,mul:3@2,div:7@0,div:2" % otype,
+                    [("typecast", otype), ("add", -12, 0), ("add", 5, 1), ("mul", 3, 2), ("div", 7, 0),
+                     ("div", 2)], True, 0, accel=accel)
+    # channel dimension in the middle (run length 160*3) and outermost; 7 channels (odd period)
+    for dim, ch_dim in (([3, 160, 144, 1], 1), ([3, 160, 144, 1], 2), ([7, 9877, 1, 1], 0),
+                        ([5, 7, 1999, 1], 1)):
+        n = int(np.prod(dim))
+        x = rng.integers(info.min, info.max, n, dtype=itype, endpoint=True)
+        nch = dim[ch_dim]
+        _arith_case(dev, port, x, dim,
+                    "typecast:float32,per-channel:true@%d,add:1.5@0,mul:2@%d,div:3.0" % (ch_dim, nch - 1),
+                    [("typecast", "float32"), ("add", 1.5, 0), ("mul", 2, nch - 1), ("div", 3.0)],
+                    True, ch_dim, accel=accel)
+    # no typecast: u8 -> u8 chain, batch of 2
+    x = rng.integers(info.min, info.max, 2 * 69120, dtype=itype, endpoint=True)
+    _arith_case(dev, port, x, [3, 160, 144, 1], "add:100,mul:2", [("add", 100), ("mul", 2)],
+                accel=accel, batch=2)
+
+
 def test_arith_float_chain_random_f32_bitexact(dev, port):
     """Random f32 inputs over many magnitudes incl. denormals: add/mul/div rounding per op."""
     rng = np.random.default_rng(77)
