@@ -326,7 +326,10 @@ int launch_chain_t (const void *in, void *out, size_t n, const ChainArgs &args,
       && ((uintptr_t) out % (V * sizeof (Out)) == 0);
   const size_t n_vec = aligned ? n / V : 0;
   const size_t work = n_vec ? n_vec : n;
-  const int bps = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 8;
+  /* Many more blocks than fit at once: measured on B200 (profiles/r1_blocks_per_sm_sweep.md),
+   * throughput rises monotonically from 8 to 64+ blocks per SM because the hardware block
+   * scheduler then balances the SMs dynamically; a persistent one-wave grid is ~10 % slower. */
+  const int bps = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 256;
   size_t blocks = (work + (size_t) CHAIN_THREADS * U - 1) / ((size_t) CHAIN_THREADS * U);
   const size_t cap = (size_t) cfg.sm_count * bps;
   if (blocks > cap)
@@ -354,9 +357,12 @@ int launch_chain_t (const void *in, void *out, size_t n, const ChainArgs &args,
         && ((uintptr_t) out % (LV * sizeof (Out)) == 0);
     if (lut_bytes <= 48 * 1024 && n >= 65536 && lut_aligned) {
       const size_t l_vec = n / LV;
+      /* every block rebuilds the table, so keep ~20 K elements per block */
+      const int lres = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 64;
+      const size_t lcap = (size_t) cfg.sm_count * lres;
       size_t lb = (l_vec + (size_t) CHAIN_THREADS * U - 1) / ((size_t) CHAIN_THREADS * U);
-      if (lb > cap)
-        lb = cap;
+      if (lb > lcap)
+        lb = lcap;
       if (lb == 0)
         lb = 1;
       const uint64_t period = p.ch_size * (uint64_t) p.nch;

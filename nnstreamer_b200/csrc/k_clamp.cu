@@ -69,7 +69,7 @@ launch_clamp_t (const void *in, void *out, size_t n, double lo, double hi, const
       && ((uintptr_t) out % (V * sizeof (T)) == 0);
   const size_t n_vec = aligned ? n / V : 0;
   const size_t work = n_vec ? n_vec : n;
-  const int bps = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 8;
+  const int bps = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 256;   /* see k_chain.cuh */
   size_t blocks = (work + (size_t) CLAMP_THREADS * U - 1) / ((size_t) CLAMP_THREADS * U);
   const size_t cap = (size_t) cfg.sm_count * bps;
   if (blocks > cap)

@@ -24,6 +24,8 @@
  *
  * Algorithmic bytes: 2 * es per element (permute, copy), 2 * row_bytes per row (strip).
  */
+#include <cstdlib>
+
 #include "nnsb_device.cuh"
 #include "nnsb_kernels.h"
 
@@ -170,7 +172,7 @@ launch_copy (const void *in, void *out, size_t bytes, const LaunchCfg &cfg, cuda
   const size_t n_vec = aligned ? bytes / 32 : 0;
   const size_t work = n_vec ? n_vec : bytes;
   size_t blocks = (work + (size_t) PERM_THREADS * 4 - 1) / ((size_t) PERM_THREADS * 4);
-  const size_t cap = (size_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 8);
+  const size_t cap = (size_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 256);
   if (blocks > cap)
     blocks = cap;
   if (blocks == 0)
@@ -252,6 +254,21 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
     p.o_in[p.n_outer] = dims[i].in;
     p.o_out[p.n_outer] = dims[i].out;
     p.n_outer++;
+  }
+
+  /* 3b. video-shaped cases go to the TMA pipeline (k_plane.cu) when they qualify */
+  if (p.R == 1 && !getenv ("NNSB_NO_PLANE")) {
+    int r = -1;
+    if (p.SY >= 2 && p.SY <= 4 && p.x_in_stride == p.SY)
+      /* [P][C] -> [C][P]: Y = channels (input-contiguous), X = pixels */
+      r = launch_plane (true, (int) p.SY, d0.es, p.SX, p.y_out_stride, p.n_outer, p.o_size,
+          p.o_in, p.o_out, in, out, cfg, stream);
+    else if (p.SX >= 2 && p.SX <= 4 && p.y_out_stride == p.SX)
+      /* [C][P] -> [P][C]: X = channels (output-contiguous), Y = pixels */
+      r = launch_plane (false, (int) p.SX, d0.es, p.SY, p.x_in_stride, p.n_outer, p.o_size,
+          p.o_out, p.o_in, in, out, cfg, stream);
+    if (r != -1)
+      return r;
   }
 
   /* 4. tile shape: ~8 KiB of payload, runs of >= 32 elements on both global sides */

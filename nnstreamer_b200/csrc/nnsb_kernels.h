@@ -17,6 +17,21 @@ struct LaunchCfg
   int blocks_per_sm;            /* grid = sm_count * blocks_per_sm (0 = kernel default) */
 };
 
+/* Blocks of `kernel` that are resident on one SM at the same time.  Grid-stride kernels are
+ * launched with exactly sm_count * resident blocks: one full wave, no tail wave (a launch
+ * with 1.6 waves leaves 40 % of the SMs idle during the second one). */
+template <typename K> static inline int
+resident_blocks_per_sm (K kernel, int threads, size_t dyn_smem)
+{
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor (&n, kernel, threads, dyn_smem) != cudaSuccess
+      || n < 1) {
+    cudaGetLastError ();
+    n = 1;
+  }
+  return n;
+}
+
 /* K1/K2: fused (typecast +) arithmetic chain.  typecast mode is the empty chain.
  * Replaces gst_tensor_transform_typecast (:1202) and _arithmetic (:1240). */
 struct ChainArgs
@@ -55,6 +70,12 @@ struct PermDesc
 };
 int launch_permute (const PermDesc & d, const void *in, void *out, size_t frame_elems,
     uint32_t batch, const LaunchCfg & cfg, cudaStream_t stream);
+
+/* K3 fast path (k_plane.cu): interleaved <-> planar through TMA bulk copies.
+ * Returns -1 when the problem does not qualify, else the launch status. */
+int launch_plane (bool to_planar, int channels, int es, uint64_t pixels, uint64_t plane_stride,
+    int n_outer, const uint32_t *o_size, const uint64_t *o_il, const uint64_t *o_pl,
+    const void *in, void *out, const LaunchCfg & cfg, cudaStream_t stream);
 
 /* K8: row-stride strip, gsttensor_converter.c:1087-1100 */
 int launch_strip (const void *src, void *dst, size_t row_bytes, size_t src_pitch, size_t rows,

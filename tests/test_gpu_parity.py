@@ -244,6 +244,36 @@ def test_transpose_hwc_to_chw_batched(dev, port):
     assert bits_equal(want[:n], np_want)
 
 
+@pytest.mark.parametrize("dtype", ["uint8", "uint16", "float32"])
+@pytest.mark.parametrize("channels", [2, 3, 4])
+def test_transpose_video_shapes_tma_path(dev, port, dtype, channels):
+    """Large interleaved<->planar transposes take the TMA bulk-copy pipeline (k_plane.cu):
+    full and partial tiles, batches, both directions, plus sizes that must fall back."""
+    rng = np.random.default_rng(channels)
+    for (w, h, batch) in ((640, 120, 1), (1000, 77, 1), (336, 100, 3), (333, 99, 1)):
+        dim = [channels, w, h, 1]
+        n = channels * w * h
+        x = rand_small(dtype, n * batch, seed=w)
+        # HWC -> CHW
+        plan = dev.plan("transpose", "1:2:0:3", dtype, dim)
+        got = plan.run_host(x, batch=batch)
+        plan.close()
+        want = np.concatenate([port.transpose(x[i * n:(i + 1) * n], dim, (1, 2, 0, 3))
+                               for i in range(batch)])
+        assert bits_equal(got, want), "to planar %s %s: %s" % (dtype, dim, first_mismatch(got, want))
+        # and back: CHW (W:H:C) -> HWC with 2:0:1:3
+        dim2 = [w, h, channels, 1]
+        plan = dev.plan("transpose", "2:0:1:3", dtype, dim2)
+        back = plan.run_host(got, batch=batch)
+        plan.close()
+        assert bits_equal(back, x), "round trip %s %s" % (dtype, dim)
+        # dimchg 0:2 is the same permutation as transpose 1:2:0:3
+        plan = dev.plan("dimchg", "0:2", dtype, dim)
+        got2 = plan.run_host(x, batch=batch)
+        plan.close()
+        assert bits_equal(got2, want)
+
+
 @pytest.mark.parametrize("from_to", [(0, 1), (0, 2), (0, 3), (0, 4), (1, 2), (1, 3), (2, 3),
                                      (2, 2), (0, 7)])
 def test_dimchg(dev, port, from_to):
