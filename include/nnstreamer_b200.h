@@ -251,6 +251,16 @@ NNSB_API size_t nnsb_plan_out_size (const nnsb_plan * plan);  /* bytes of one ou
  * reference function.  d_in/d_out are device pointers; asynchronous on `s`. */
 NNSB_API int nnsb_plan_launch (nnsb_plan * plan, const void *d_in, void *d_out,
     uint32_t batch, nnsb_stream * s);
+/* Element-range launch for the element-wise modes (typecast, arithmetic, clamp): transforms
+ * elements [first_elem, first_elem + n_elems) of the buffers d_in / d_out point to.  Lets the
+ * host-buffer path pipeline H2D copy, kernel and D2H copy chunk by chunk on two streams.
+ * first_elem must be a multiple of nnsb_plan_chunk_granule() (keeps the 32-byte vector
+ * alignment and, for per-channel arithmetic, the channel phase).  No reference counterpart:
+ * the reference's loops (gsttensor_transform.c:1222-1226,1375-1409) run on host memory. */
+NNSB_API int nnsb_plan_is_elementwise (const nnsb_plan * plan);
+NNSB_API uint64_t nnsb_plan_chunk_granule (const nnsb_plan * plan);
+NNSB_API int nnsb_plan_launch_elems (nnsb_plan * plan, const void *d_in, void *d_out,
+    uint64_t first_elem, uint64_t n_elems, nnsb_stream * s);
 /* number of kernels the last nnsb_plan_launch on this plan enqueued */
 NNSB_API int nnsb_plan_last_launch_count (const nnsb_plan * plan);
 /* stand only: copy the per-tensor statistics of the last launch (mean[, std]) to host */
@@ -262,6 +272,104 @@ NNSB_API int nnsb_plan_stand_stats (nnsb_plan * plan, nnsb_stream * s, uint32_t 
  * Both pointers are device memory. */
 NNSB_API int nnsb_strip_launch (nnsb_stream * s, const void *d_src, void *d_dst,
     size_t row_bytes, size_t src_pitch, size_t rows);
+
+/* ---------------------------------------------------------------------------------------
+ * Element mirrors.  GStreamer is not available in the build image, so the GObject /
+ * GstBaseTransform surface of the two elements is exposed as plain functions with the same
+ * names, property strings, caps strings and return conventions; the GStreamer glue
+ * (nnstreamer_b200/gst/) is a 1:1 wrapper around them.
+ * ------------------------------------------------------------------------------------- */
+#define NNSB_FLOW_OK 0                  /* GST_FLOW_OK */
+#define NNSB_FLOW_ERROR (-5)            /* GST_FLOW_ERROR */
+#define NNSB_FLOW_NOT_SUPPORTED (-6)    /* GST_FLOW_NOT_SUPPORTED */
+#define NNSB_ENOENT (-2)                /* property value is NULL (e.g. `option` never set) */
+
+/* One GstMemory: a block of host or device memory.  Blocks produced by the elements are
+ * `owned` (release them with nnsb_memory_release); blocks shared from the input
+ * (gst_memory_ref, gsttensor_transform.c:1716) are not. */
+typedef struct {
+  void *data;
+  size_t size;
+  int32_t on_device;                    /* 0 = host, 1 = device memory of the element's GPU */
+  int32_t owned;
+  void *owner;                          /* the context that allocated it */
+} nnsb_memory;
+
+typedef struct nnsb_transform nnsb_transform;
+
+/* gst_tensor_transform_init, gsttensor_transform.c:288-301 (silent=TRUE, mode=unknown,
+ * option=NULL, acceleration=FALSE as in a build without ORC).  The GPU context is created
+ * on the first transform, so properties and caps work on a machine without a GPU. */
+NNSB_API int nnsb_transform_new (int device_id, nnsb_transform ** out);
+NNSB_API int nnsb_transform_free (nnsb_transform * t);
+/* gst_tensor_transform_set_property, :963-1025.  Properties: "silent", "mode" (nick or
+ * number), "option", "acceleration", "apply".  An invalid option restores the previous one
+ * (:985-990) and returns NNSB_EINVAL; the reference only logs. */
+NNSB_API int nnsb_transform_set_property (nnsb_transform * t, const char *name, const char *value);
+/* gst_tensor_transform_get_property, :1030-1081 (+ "transpose-rank-limit").  Returns the
+ * string length, NNSB_ENOENT when the value is NULL, NNSB_EINVAL for unknown names. */
+NNSB_API int nnsb_transform_get_property (nnsb_transform * t, const char *name, char *buf, size_t buflen);
+/* gst_tensor_transform_transform_caps, :1971-2061.  direction: nnsb_pad_direction of `caps`;
+ * filter may be NULL.  Result written to out (caps string). */
+NNSB_API int nnsb_transform_transform_caps (nnsb_transform * t, int direction, const char *caps,
+    const char *filter, char *out, size_t outlen);
+/* gst_tensor_transform_fixate_caps, :2066-2088 */
+NNSB_API int nnsb_transform_fixate_caps (nnsb_transform * t, int direction, const char *caps,
+    const char *othercaps, char *out, size_t outlen);
+/* gst_tensor_transform_set_caps, :2093-2164; 0 = accepted */
+NNSB_API int nnsb_transform_set_caps (nnsb_transform * t, const char *incaps, const char *outcaps);
+/* gst_tensor_transform_transform_size, :2169-2186: always succeeds with *othersize = 0 */
+NNSB_API int nnsb_transform_transform_size (nnsb_transform * t, int direction, const char *caps,
+    size_t size, const char *othercaps, size_t *othersize);
+/* gst_tensor_transform_transform, :1667-1814: n_in input memories -> *n_out output memories
+ * appended to out[] (capacity NNSB_SIZE_LIMIT).  Host inputs give (pinned) host outputs with
+ * the copies pipelined against the kernels; device inputs give device outputs.  Returns an
+ * NNSB_FLOW_* code. */
+NNSB_API int nnsb_transform_transform (nnsb_transform * t, const nnsb_memory * in, uint32_t n_in,
+    nnsb_memory * out, uint32_t *n_out);
+/* the negotiated configs (filter->in_config / out_config) */
+NNSB_API int nnsb_transform_get_config (nnsb_transform * t, int direction, nnsb_tensors_config * cfg);
+/* element-owned memory helpers (the CUDA GstAllocator's alloc / free) */
+NNSB_API int nnsb_transform_alloc (nnsb_transform * t, size_t size, int on_device, nnsb_memory * out);
+NNSB_API int nnsb_memory_release (nnsb_memory * mem);
+/* kernels launched by this element so far */
+NNSB_API int nnsb_transform_kernel_launches (nnsb_transform * t, uint64_t *count);
+
+typedef struct nnsb_converter nnsb_converter;
+
+/* tensor_converter, video branch only (gsttensor_converter.c:1046-1109,1390-1519,2101-2239).
+ * Properties: "frames-per-tensor" (uint >= 1, default 1), "silent". */
+NNSB_API int nnsb_converter_new (int device_id, nnsb_converter ** out);
+NNSB_API int nnsb_converter_free (nnsb_converter * c);
+NNSB_API int nnsb_converter_set_property (nnsb_converter * c, const char *name, const char *value);
+NNSB_API int nnsb_converter_get_property (nnsb_converter * c, const char *name, char *buf, size_t buflen);
+/* gst_tensor_converter_parse_caps / parse_video: video/x-raw caps (format GRAY8, RGB, BGR,
+ * RGBx, BGRx, xRGB, xBGR, RGBA, BGRA, ARGB, ABGR) -> tensors config; out = src caps string */
+NNSB_API int nnsb_converter_set_caps (nnsb_converter * c, const char *video_caps, char *out, size_t outlen);
+NNSB_API int nnsb_converter_get_config (nnsb_converter * c, nnsb_tensors_config * cfg);
+/* 1 when rows carry padding that chain() removes (gst_tensor_converter_video_stride, :1390) */
+NNSB_API int nnsb_converter_remove_padding (nnsb_converter * c);
+NNSB_API size_t nnsb_converter_frame_size (nnsb_converter * c);   /* GST_VIDEO_INFO_SIZE */
+/* gst_tensor_converter_chain, _NNS_VIDEO case: takes one video frame (host or device).  The
+ * row padding is stripped on the way into a device-side batch buffer (pitched H2D copy for
+ * host frames, strip kernel for device frames); when frames-per-tensor frames have arrived
+ * *produced = 1 and `out` holds the batched tensor in device memory (release it). */
+NNSB_API int nnsb_converter_chain (nnsb_converter * c, const nnsb_memory * frame, nnsb_memory * out,
+    int *produced);
+
+/* ---------------------------------------------------------------------------------------
+ * Batching queue: groups frames so that one launch covers `batch` tensors (north_star).
+ * Frames are copied (H2D on a copy stream, or D2D) into one of two device batch buffers;
+ * nnsb_queue_flush launches the plan once over everything queued and hands back the device
+ * pointer of the outputs (valid until the flush after next).  Per-tensor semantics are
+ * those of nnsb_plan_launch.
+ * ------------------------------------------------------------------------------------- */
+typedef struct nnsb_queue nnsb_queue;
+NNSB_API int nnsb_queue_create (nnsb_ctx * ctx, nnsb_plan * plan, uint32_t batch, nnsb_queue ** out);
+NNSB_API int nnsb_queue_destroy (nnsb_queue * q);
+/* *full = 1 when the queue now holds `batch` frames */
+NNSB_API int nnsb_queue_push (nnsb_queue * q, const void *frame, int on_device, int *full);
+NNSB_API int nnsb_queue_flush (nnsb_queue * q, void **d_out, uint32_t *n_frames, nnsb_stream ** stream);
 
 /* No counterpart in the reference (its CPU element simply mallocs).  The same stand kernels
  * as nnsb_plan_launch(), for callers that must not allocate while frames are flowing: a

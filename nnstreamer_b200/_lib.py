@@ -59,6 +59,14 @@ class Option(C.Structure):
                 ("clamp_min", C.c_double), ("clamp_max", C.c_double)]
 
 
+class Memory(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("size", C.c_size_t), ("on_device", C.c_int32),
+                ("owned", C.c_int32), ("owner", C.c_void_p)]
+
+
+FLOW_OK, FLOW_ERROR, FLOW_NOT_SUPPORTED, ENOENT = 0, -5, -6, -2
+
+
 class NnsbError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__("nnstreamer_b200 error %d: %s" % (code, msg))
@@ -121,10 +129,43 @@ _PROTOS = {
     "nnsb_plan_in_size": (C.c_size_t, [_VP]),
     "nnsb_plan_out_size": (C.c_size_t, [_VP]),
     "nnsb_plan_launch": (C.c_int, [_VP, _VP, _VP, C.c_uint32, _VP]),
+    "nnsb_plan_is_elementwise": (C.c_int, [_VP]),
+    "nnsb_plan_chunk_granule": (C.c_uint64, [_VP]),
+    "nnsb_plan_launch_elems": (C.c_int, [_VP, _VP, _VP, C.c_uint64, C.c_uint64, _VP]),
     "nnsb_plan_last_launch_count": (C.c_int, [_VP]),
     "nnsb_plan_stand_stats": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(C.c_double),
                                         C.POINTER(C.c_double), C.c_size_t]),
     "nnsb_strip_launch": (C.c_int, [_VP, _VP, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),
+    "nnsb_transform_new": (C.c_int, [C.c_int, C.POINTER(_VP)]),
+    "nnsb_transform_free": (C.c_int, [_VP]),
+    "nnsb_transform_set_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p]),
+    "nnsb_transform_get_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "nnsb_transform_transform_caps": (C.c_int, [_VP, C.c_int, C.c_char_p, C.c_char_p, C.c_char_p,
+                                                C.c_size_t]),
+    "nnsb_transform_fixate_caps": (C.c_int, [_VP, C.c_int, C.c_char_p, C.c_char_p, C.c_char_p,
+                                             C.c_size_t]),
+    "nnsb_transform_set_caps": (C.c_int, [_VP, C.c_char_p, C.c_char_p]),
+    "nnsb_transform_transform_size": (C.c_int, [_VP, C.c_int, C.c_char_p, C.c_size_t, C.c_char_p,
+                                                C.POINTER(C.c_size_t)]),
+    "nnsb_transform_transform": (C.c_int, [_VP, C.POINTER(Memory), C.c_uint32, C.POINTER(Memory),
+                                           C.POINTER(C.c_uint32)]),
+    "nnsb_transform_get_config": (C.c_int, [_VP, C.c_int, C.POINTER(TensorsConfig)]),
+    "nnsb_transform_alloc": (C.c_int, [_VP, C.c_size_t, C.c_int, C.POINTER(Memory)]),
+    "nnsb_memory_release": (C.c_int, [C.POINTER(Memory)]),
+    "nnsb_transform_kernel_launches": (C.c_int, [_VP, C.POINTER(C.c_uint64)]),
+    "nnsb_converter_new": (C.c_int, [C.c_int, C.POINTER(_VP)]),
+    "nnsb_converter_free": (C.c_int, [_VP]),
+    "nnsb_converter_set_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p]),
+    "nnsb_converter_get_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "nnsb_converter_set_caps": (C.c_int, [_VP, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "nnsb_converter_get_config": (C.c_int, [_VP, C.POINTER(TensorsConfig)]),
+    "nnsb_converter_remove_padding": (C.c_int, [_VP]),
+    "nnsb_converter_frame_size": (C.c_size_t, [_VP]),
+    "nnsb_converter_chain": (C.c_int, [_VP, C.POINTER(Memory), C.POINTER(Memory), C.POINTER(C.c_int)]),
+    "nnsb_queue_create": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(_VP)]),
+    "nnsb_queue_destroy": (C.c_int, [_VP]),
+    "nnsb_queue_push": (C.c_int, [_VP, _VP, C.c_int, C.POINTER(C.c_int)]),
+    "nnsb_queue_flush": (C.c_int, [_VP, C.POINTER(_VP), C.POINTER(C.c_uint32), C.POINTER(_VP)]),
     "nnsb_stand_launch_noalloc": (C.c_int, [_VP, _VP, C.c_int, C.c_int, C.POINTER(C.c_uint32),
                                             C.c_int, C.c_int, C.c_uint32, _VP]),
 }

@@ -778,6 +778,67 @@ nnsb_plan_launch (nnsb_plan * plan, const void *d_in, void *d_out, uint32_t batc
 }
 
 extern "C" int
+nnsb_plan_is_elementwise (const nnsb_plan * plan)
+{
+  if (!plan)
+    return 0;
+  return plan->opt.mode == NNSB_MODE_TYPECAST || plan->opt.mode == NNSB_MODE_ARITHMETIC
+      || plan->opt.mode == NNSB_MODE_CLAMP;
+}
+
+extern "C" uint64_t
+nnsb_plan_chunk_granule (const nnsb_plan * plan)
+{
+  /* element counts that are a multiple of this keep every launch vector-aligned and, for
+   * per-channel arithmetic, start on channel 0 of a channel run */
+  if (!plan)
+    return 0;
+  uint64_t g = 256;             /* 256 elements: 32-byte aligned for every element size */
+  if (plan->opt.mode == NNSB_MODE_ARITHMETIC && plan->chain.desc.nch > 1) {
+    const uint64_t period = plan->chain.desc.ch_size * (uint64_t) plan->chain.desc.nch;
+    uint64_t a = g, b = period;
+    while (b) { const uint64_t t = a % b; a = b; b = t; }
+    g = g / a * period;
+  }
+  return g;
+}
+
+extern "C" int
+nnsb_plan_launch_elems (nnsb_plan * plan, const void *d_in, void *d_out, uint64_t first_elem,
+    uint64_t n_elems, nnsb_stream * s)
+{
+  if (!plan || !s || !d_in || !d_out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_launch_elems: null argument");
+  if (!nnsb_plan_is_elementwise (plan))
+    return nnsb_set_error (NNSB_ENOTSUP,
+        "nnsb_plan_launch_elems: only typecast, arithmetic and clamp can be split by elements");
+  if (first_elem % nnsb_plan_chunk_granule (plan))
+    return nnsb_set_error (NNSB_EINVAL,
+        "nnsb_plan_launch_elems: first element must be a multiple of nnsb_plan_chunk_granule()");
+  int r = bind (plan->ctx);
+  if (r)
+    return r;
+  plan->last_launches = 0;
+  if (n_elems == 0)
+    return NNSB_OK;
+  const LaunchCfg cfg = cfg_of (plan->ctx);
+  const char *in = (const char *) d_in + first_elem * nnsb_element_size (plan->in_info.type);
+  char *out = (char *) d_out + first_elem * nnsb_element_size (plan->out_info.type);
+  int err;
+  if (plan->opt.mode == NNSB_MODE_CLAMP)
+    err = launch_clamp (plan->in_info.type, in, out, n_elems, plan->opt.clamp_min,
+        plan->opt.clamp_max, cfg, s->s);
+  else
+    err = launch_chain (plan->in_info.type, plan->out_info.type, plan->acceleration != 0, in, out,
+        n_elems, plan->chain, cfg, s->s);
+  plan->last_launches = 1;
+  if (err)
+    return nnsb_set_error (NNSB_ECUDA, "kernel launch failed: %s",
+        cudaGetErrorString ((cudaError_t) err));
+  return NNSB_OK;
+}
+
+extern "C" int
 nnsb_plan_stand_stats (nnsb_plan * plan, nnsb_stream * s, uint32_t batch, double *mean_out,
     double *std_out, size_t capacity)
 {

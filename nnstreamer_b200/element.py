@@ -1,0 +1,286 @@
+"""Python mirror of the reference elements' interface on top of the C-ABI element functions.
+
+TensorTransform  <->  tensor_transform  (gst/nnstreamer/elements/gsttensor_transform.c)
+TensorConverter  <->  tensor_converter, video branch (gsttensor_converter.c)
+BatchQueue            the device-side batching queue
+
+Same property names and value strings, same caps strings; `chain`/`transform` take and return
+lists of numpy arrays (host memories) or DeviceMemory handles.  Nothing is computed here: every
+call goes to libnnstreamer_b200.so.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+
+_CAPS_BUF = 4096
+
+
+class DeviceMemory:
+    """A device-resident GstMemory stand-in (pointer + size), optionally owned."""
+
+    def __init__(self, mem):
+        self.mem = mem
+
+    @property
+    def ptr(self):
+        return self.mem.data
+
+    @property
+    def size(self):
+        return self.mem.size
+
+    def release(self):
+        L.lib().nnsb_memory_release(C.byref(self.mem))
+
+
+def _host_memory(arr):
+    m = L.Memory()
+    m.data = arr.ctypes.data_as(C.c_void_p)
+    m.size = arr.nbytes
+    m.on_device = 0
+    m.owned = 0
+    m.owner = None
+    return m
+
+
+def device_memory(ptr, size):
+    m = L.Memory()
+    m.data = C.c_void_p(ptr)
+    m.size = size
+    m.on_device = 1
+    m.owned = 0
+    m.owner = None
+    return DeviceMemory(m)
+
+
+class TensorTransform:
+    """gst_element_factory_make ("tensor_transform")"""
+
+    def __init__(self, device_id=0, **props):
+        self._lib = L.lib()
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_transform_new(int(device_id), C.byref(self.handle)))
+        for k, v in props.items():
+            self.set_property(k.replace("_", "-"), v)
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_transform_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- GObject properties ----------------------------------------------------------------
+    def set_property(self, name, value):
+        """Returns True when accepted.  Like g_object_set, an invalid `option` raises nothing:
+        the previous option stays in force (gsttensor_transform.c:985-990)."""
+        if isinstance(value, bool):
+            value = "true" if value else "false"
+        val = None if value is None else str(value).encode()
+        code = self._lib.nnsb_transform_set_property(self.handle, name.encode(), val)
+        if code != 0 and name != "option":
+            L.check(code)
+        return code == 0
+
+    def get_property(self, name):
+        buf = C.create_string_buffer(_CAPS_BUF)
+        code = self._lib.nnsb_transform_get_property(self.handle, name.encode(), buf, _CAPS_BUF)
+        if code == L.ENOENT:
+            return None
+        if code < 0:
+            L.check(code)
+        s = buf.value.decode()
+        if name in ("silent", "acceleration"):
+            return s == "true"
+        if name == "transpose-rank-limit":
+            return int(s)
+        return s
+
+    # -- GstBaseTransform vfuncs -----------------------------------------------------------
+    def transform_caps(self, direction, caps, filter_caps=None):
+        buf = C.create_string_buffer(_CAPS_BUF)
+        d = L.PAD_SINK if direction == "sink" else L.PAD_SRC
+        code = self._lib.nnsb_transform_transform_caps(
+            self.handle, d, caps.encode(), filter_caps.encode() if filter_caps else None, buf, _CAPS_BUF)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def fixate_caps(self, direction, caps, othercaps):
+        buf = C.create_string_buffer(_CAPS_BUF)
+        d = L.PAD_SINK if direction == "sink" else L.PAD_SRC
+        code = self._lib.nnsb_transform_fixate_caps(self.handle, d, caps.encode(), othercaps.encode(),
+                                                    buf, _CAPS_BUF)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def set_caps(self, incaps, outcaps):
+        return self._lib.nnsb_transform_set_caps(self.handle, incaps.encode(), outcaps.encode()) == 0
+
+    def negotiate(self, incaps, peer_caps="other/tensor; other/tensors"):
+        """What BaseTransform does with a fixed sink caps: transform_caps -> fixate -> set_caps.
+        Returns the fixed src caps string."""
+        out = self.fixate_caps("sink", incaps, peer_caps)
+        if not self.set_caps(incaps, out):
+            raise L.NnsbError(L.EINVAL, self._lib.nnsb_last_error().decode())
+        return out
+
+    def config(self, direction="src"):
+        cfg = L.TensorsConfig()
+        d = L.PAD_SINK if direction == "sink" else L.PAD_SRC
+        L.check(self._lib.nnsb_transform_get_config(self.handle, d, C.byref(cfg)))
+        return cfg
+
+    def transform(self, memories):
+        """gst_tensor_transform_transform: list of numpy arrays (host) or DeviceMemory ->
+        (flow_return, list of outputs).  Host outputs are numpy arrays (copied out of the
+        element's pinned buffers); device outputs are DeviceMemory."""
+        n = len(memories)
+        ins = (L.Memory * max(1, n))()
+        keep = []
+        for i, m in enumerate(memories):
+            if isinstance(m, DeviceMemory):
+                ins[i] = m.mem
+            else:
+                a = np.ascontiguousarray(m)
+                keep.append(a)
+                ins[i] = _host_memory(a)
+        outs = (L.Memory * L.SIZE_LIMIT)()
+        n_out = C.c_uint32(0)
+        flow = self._lib.nnsb_transform_transform(self.handle, ins, n, outs, C.byref(n_out))
+        results = []
+        for i in range(n_out.value):
+            m = outs[i]
+            if m.on_device:
+                results.append(DeviceMemory(m))
+            else:
+                buf = (C.c_uint8 * m.size).from_address(m.data)
+                results.append(np.frombuffer(buf, dtype=np.uint8).copy())
+                if m.owned:
+                    self._lib.nnsb_memory_release(C.byref(m))
+        return flow, results
+
+    def transform_raw(self, ins, n, outs, n_out):
+        """No-copy variant for benchmarks: ctypes Memory arrays in, Memory array out."""
+        return self._lib.nnsb_transform_transform(self.handle, ins, n, outs, C.byref(n_out))
+
+    def alloc(self, size, on_device=False):
+        m = L.Memory()
+        L.check(self._lib.nnsb_transform_alloc(self.handle, int(size), int(bool(on_device)), C.byref(m)))
+        return m
+
+    @property
+    def kernel_launches(self):
+        c = C.c_uint64(0)
+        L.check(self._lib.nnsb_transform_kernel_launches(self.handle, C.byref(c)))
+        return int(c.value)
+
+
+class TensorConverter:
+    """gst_element_factory_make ("tensor_converter"), video/x-raw input only."""
+
+    def __init__(self, device_id=0, **props):
+        self._lib = L.lib()
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_converter_new(int(device_id), C.byref(self.handle)))
+        for k, v in props.items():
+            self.set_property(k.replace("_", "-"), v)
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_converter_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_property(self, name, value):
+        if isinstance(value, bool):
+            value = "true" if value else "false"
+        L.check(self._lib.nnsb_converter_set_property(self.handle, name.encode(), str(value).encode()))
+
+    def get_property(self, name):
+        buf = C.create_string_buffer(256)
+        code = self._lib.nnsb_converter_get_property(self.handle, name.encode(), buf, 256)
+        if code < 0:
+            L.check(code)
+        s = buf.value.decode()
+        return int(s) if name == "frames-per-tensor" else (s == "true")
+
+    def set_caps(self, video_caps):
+        buf = C.create_string_buffer(_CAPS_BUF)
+        code = self._lib.nnsb_converter_set_caps(self.handle, video_caps.encode(), buf, _CAPS_BUF)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    @property
+    def remove_padding(self):
+        return bool(self._lib.nnsb_converter_remove_padding(self.handle))
+
+    @property
+    def frame_size(self):
+        return self._lib.nnsb_converter_frame_size(self.handle)
+
+    def config(self):
+        cfg = L.TensorsConfig()
+        L.check(self._lib.nnsb_converter_get_config(self.handle, C.byref(cfg)))
+        return cfg
+
+    def chain(self, frame):
+        """One video frame in (numpy uint8 array or DeviceMemory); returns (flow, DeviceMemory
+        or None): a tensor comes out every frames-per-tensor frames."""
+        if isinstance(frame, DeviceMemory):
+            m = frame.mem
+        else:
+            a = np.ascontiguousarray(frame, dtype=np.uint8)
+            m = _host_memory(a)
+        out = L.Memory()
+        produced = C.c_int(0)
+        flow = self._lib.nnsb_converter_chain(self.handle, C.byref(m), C.byref(out), C.byref(produced))
+        return flow, (DeviceMemory(out) if produced.value else None)
+
+
+class BatchQueue:
+    """nnsb_queue: groups frames so that one launch covers `batch` tensors."""
+
+    def __init__(self, dev, plan, batch):
+        self._lib = L.lib()
+        self.dev = dev
+        self.plan = plan
+        self.batch = int(batch)
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_queue_create(dev.ctx, plan.handle, self.batch, C.byref(self.handle)))
+
+    def push(self, frame):
+        full = C.c_int(0)
+        if isinstance(frame, int):
+            L.check(self._lib.nnsb_queue_push(self.handle, C.c_void_p(frame), 1, C.byref(full)))
+        else:
+            a = np.ascontiguousarray(frame)
+            self._keep = a
+            L.check(self._lib.nnsb_queue_push(self.handle, a.ctypes.data_as(C.c_void_p), 0, C.byref(full)))
+        return bool(full.value)
+
+    def flush(self):
+        """Launch over everything queued; returns (device pointer, frames, stream handle)."""
+        d_out = C.c_void_p()
+        n = C.c_uint32(0)
+        stream = C.c_void_p()
+        L.check(self._lib.nnsb_queue_flush(self.handle, C.byref(d_out), C.byref(n), C.byref(stream)))
+        return d_out.value, int(n.value), stream
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_queue_destroy(self.handle)
+            self.handle = C.c_void_p()
