@@ -6,7 +6,8 @@ this package only mirrors the reference element's interface on top of that C-ABI
 from . import _lib  # noqa: F401
 from ._lib import NnsbError, lib  # noqa: F401
 from .device import Device, Plan  # noqa: F401
-from .element import BatchQueue, DeviceMemory, TensorConverter, TensorTransform  # noqa: F401
+from .element import (BatchQueue, DeviceMemory, TensorConverter, TensorTransform,  # noqa: F401
+                      device_memory)
 
 __all__ = ["Device", "Plan", "NnsbError", "lib", "TensorTransform", "TensorConverter",
            "BatchQueue", "DeviceMemory"]
