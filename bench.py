@@ -281,12 +281,15 @@ def run_b200(args):
 
     # ---- device-resident: K launches, CUDA events on the launching stream ----
     step = lambda: plan.launch(d_in, d_out, B)
-    for _ in range(args.warmup):
-        step()
-    barrier()
+    # clocks / throttle reasons are sampled from before the warm-up until after the end-to-end
+    # region, so that the (milliseconds-long) device-resident region is covered too
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+        time.sleep(0.3)
+    for _ in range(args.warmup):
+        step()
+    barrier()
     e0, e1 = dev.event(), dev.event()
     dev.record(e0)
     for _ in range(args.steps):
@@ -294,7 +297,6 @@ def run_b200(args):
     dev.record(e1)
     ms_dev = dev.elapsed_ms(e0, e1)
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
     ms_dev = max_over_ranks(ms_dev)
     launches = plan.last_launch_count * args.steps
 
@@ -340,6 +342,7 @@ def run_b200(args):
     ms_e2e = (time.perf_counter() - t0) * 1e3
     e2e_launches = elem.kernel_launches - launches_before
     barrier()
+    clocks = sampler.stop() if rank == 0 else None
     ms_e2e = max_over_ranks(ms_e2e)
 
     # ---- parity spot check on the bench data (first frame, against the oracle) ----
