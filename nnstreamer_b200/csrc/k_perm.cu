@@ -1,20 +1,21 @@
 /*
  * k_perm.cu -- K3/K4/K8: data-movement kernels.
  *
- *  permute : rank-N permutation copy through a padded shared-memory tile.  Replaces the
- *            per-element nns_memcpy nest of gst_tensor_transform_transpose
- *            (gsttensor_transform.c:1417-1500) and the block memcpy nest of
- *            gst_tensor_transform_dimchg (:1155-1178).  Both lower to the same problem after
- *            the plan canonicalises the dimensions (drop extent-1 dims, merge dims that are
- *            adjacent on both sides):
- *               I : innermost run, contiguous in input AND output (extent R, may be 1)
- *               X : the next output-contiguous dimension (out stride R)
- *               Y : the next input-contiguous dimension  (in  stride R)
- *            A block stages an RT x TX x TY tile: global reads walk (r, y, x) so that a warp
- *            reads dense runs of the input, global writes walk (r, x, y) so that a warp
- *            writes dense runs of the output; the shared tile has an odd pitch, so the
- *            transposed access is bank-conflict free.  HWC->CHW on video (C = 3 innermost)
- *            becomes Y = C (3), X = W*H: the whole input tile is one contiguous run.
+ *  permute : rank-N permutation copy through a shared-memory tile.  Replaces the per-element
+ *            nns_memcpy nest of gst_tensor_transform_transpose (gsttensor_transform.c:1417-1500)
+ *            and the block memcpy nest of gst_tensor_transform_dimchg (:1155-1178).  Both lower
+ *            to the same problem after the dimensions are canonicalised (drop extent-1 dims,
+ *            merge dims that are adjacent on both sides).
+ *            The tile is an N-dimensional BOX chosen so that it holds a run of >= 32
+ *            contiguous elements on the input side (walking the dims by input stride) AND on
+ *            the output side (walking them by output stride), whichever dims that takes --
+ *            e.g. C:W:H -> H:W:C needs a box over all three dims.  A block reads its box in
+ *            input order (dense warp loads), parks it in shared memory, and writes it in
+ *            output order (dense warp stores).  The in-box coordinates of the <= 8 elements a
+ *            thread moves depend only on the box shape, so their global offsets and
+ *            shared-memory slots are computed once per kernel; per tile and element only an
+ *            add, a load and a store remain.  Shared memory is padded by one word every 32.
+ *            Video-shaped interleaved <-> planar cases go to the TMA pipeline in k_plane.cu.
  *  copy    : flat vector copy for permutations that canonicalise to the identity
  *            (dimchg from == to, :1133-1139; transpose 0:1:2:3, :1464-1469).
  *  strip   : tensor_converter's video row-padding removal (gsttensor_converter.c:1087-1100):
@@ -32,84 +33,248 @@
 namespace nnsb {
 
 constexpr int PERM_THREADS = 256;
-constexpr int PERM_MAX_OUTER = NNSB_PERM_MAX_RANK;
+constexpr int PERM_EPT = 8;             /* elements per thread per tile */
+constexpr int PERM_TILE_MAX = PERM_THREADS * PERM_EPT;   /* 2048 elements */
+constexpr int PERM_DIMS = NNSB_PERM_MAX_RANK + 1;        /* rank 8 + batch */
+
+/* exact q / d for q < 2^31 with one 64-bit multiply: m = ceil (2^(31+s) / d), s = ceil (log2 d) */
+struct FastDiv
+{
+  uint32_t d, m, s;
+};
+
+static FastDiv
+make_fastdiv (uint32_t d)
+{
+  FastDiv f;
+  f.d = d ? d : 1;
+  f.s = 0;
+  while ((1ull << f.s) < f.d)
+    f.s++;
+  f.m = (uint32_t) (((1ull << (31 + f.s)) + f.d - 1) / f.d);
+  return f;
+}
+
+__device__ __forceinline__ void
+divmod (uint32_t q, const FastDiv &f, uint32_t &quot, uint32_t &rem)
+{
+  quot = (uint32_t) (((uint64_t) q * f.m) >> (31 + f.s));
+  rem = q - quot * f.d;
+}
 
 struct PermDev
 {
-  /* tile dims */
-  uint32_t R, RT, nR;           /* inner run: extent, tile, tiles */
-  uint32_t SX, TX, nX;
-  uint32_t SY, TY, nY;
-  uint64_t x_in_stride;         /* input stride of X (elements) */
-  uint64_t y_out_stride;        /* output stride of Y (elements) */
-  uint32_t pitch;               /* shared pitch along x, in (y) units: odd */
-  uint32_t magic_rt, magic_ty, magic_tx;   /* ceil (2^32 / d) for the in-tile index split */
-  /* outer dims (everything except I, X, Y; the batch is one of them) */
-  int n_outer;
-  uint32_t o_size[PERM_MAX_OUTER];
-  uint64_t o_in[PERM_MAX_OUTER];
-  uint64_t o_out[PERM_MAX_OUTER];
-  uint64_t n_tiles;
+  int n;                                /* dims, in output order (out stride ascending) */
+  uint32_t size[PERM_DIMS];
+  FastDiv tile[PERM_DIMS];              /* box extent per dim */
+  FastDiv ntile[PERM_DIMS];             /* boxes per dim */
+  uint64_t in_stride[PERM_DIMS];
+  uint64_t out_stride[PERM_DIMS];
+  int in_order[PERM_DIMS];              /* dims sorted by input stride (fastest first) */
+  uint32_t lstride[PERM_DIMS];          /* stride of dim d in the load-order linear index */
+  uint32_t volume;                      /* elements per box (<= 2048) */
+  uint32_t n_tiles;                     /* < 2^31 */
 };
 
-__device__ __forceinline__ uint32_t
-fast_div (uint32_t q, uint32_t d, uint32_t magic)
+__device__ __forceinline__ uint32_t smem_slot (uint32_t linear)
 {
-  /* exact for q < 2^32 / d; q is an in-tile index (< 64 Ki) */
-  return d == 1 ? q : __umulhi (q, magic);
+  return linear + (linear >> 5);        /* one pad word every 32: breaks power-of-two strides */
 }
 
-template <typename E>
+constexpr int PERM_STAGES = 4;
+
+template <typename E> __device__ __forceinline__ void
+cp_async_elem (E *smem_dst, const E *gmem_src)
+{
+  const uint32_t d = (uint32_t) __cvta_generic_to_shared (smem_dst);
+  if constexpr (sizeof (E) == 8)
+    asm volatile ("cp.async.ca.shared.global [%0], [%1], 8;" :: "r" (d), "l" (gmem_src) : "memory");
+  else if constexpr (sizeof (E) == 4)
+    asm volatile ("cp.async.ca.shared.global [%0], [%1], 4;" :: "r" (d), "l" (gmem_src) : "memory");
+}
+
+/* ASYNC: loads are cp.async (LDGSTS) into a ring of PERM_STAGES tiles, PERM_STAGES-1 tiles of
+ * reads in flight per block (4/8-byte elements: cp.async moves 4, 8 or 16 bytes).
+ * !ASYNC: loads go through registers, one tile at a time (1/2-byte elements). */
+template <typename E, bool ASYNC>
 __global__ void __launch_bounds__ (PERM_THREADS)
 permute_kernel (const E *__restrict__ in, E *__restrict__ out, const __grid_constant__ PermDev p)
 {
   extern __shared__ __align__ (16) unsigned char smem_raw[];
-  E *tile = reinterpret_cast<E *> (smem_raw);
+  constexpr uint32_t STAGE_ELEMS = PERM_TILE_MAX + PERM_TILE_MAX / 32 + 1;
+  E *ring = reinterpret_cast<E *> (smem_raw);
 
-  for (uint64_t t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
-    /* decode tile index: r-tile fastest, then x-tile, then y-tile, then outer dims */
-    uint64_t q = t;
-    const uint32_t tr = (uint32_t) (q % p.nR); q /= p.nR;
-    const uint32_t tx = (uint32_t) (q % p.nX); q /= p.nX;
-    const uint32_t ty = (uint32_t) (q % p.nY); q /= p.nY;
-    uint64_t in_base = 0, out_base = 0;
-    for (int i = 0; i < p.n_outer; i++) {
-      const uint64_t idx = q % p.o_size[i];
-      q /= p.o_size[i];
-      in_base += idx * p.o_in[i];
-      out_base += idx * p.o_out[i];
+  /* in-box coordinates of this thread's elements: computed once per kernel */
+  uint32_t l_sm[PERM_EPT], s_sm[PERM_EPT];
+  uint64_t l_off[PERM_EPT], s_off[PERM_EPT];
+#pragma unroll
+  for (int j = 0; j < PERM_EPT; j++) {
+    const uint32_t i = threadIdx.x + j * PERM_THREADS;
+    uint32_t q = i, c;
+    uint64_t off = 0;
+    for (int k = 0; k < p.n; k++) {
+      const int d = p.in_order[k];
+      divmod (q, p.tile[d], q, c);
+      off += (uint64_t) c * p.in_stride[d];
     }
-    const uint32_t r0 = tr * p.RT, x0 = tx * p.TX, y0 = ty * p.TY;
-    const uint32_t rn = min (p.RT, p.R - r0), xn = min (p.TX, p.SX - x0), yn = min (p.TY, p.SY - y0);
-    in_base += (uint64_t) x0 * p.x_in_stride + (uint64_t) y0 * p.R + r0;
-    out_base += (uint64_t) y0 * p.y_out_stride + (uint64_t) x0 * p.R + r0;
+    l_off[j] = off;
+    l_sm[j] = smem_slot (i);
+    q = i;
+    off = 0;
+    uint32_t lin = 0;
+    for (int d = 0; d < p.n; d++) {
+      divmod (q, p.tile[d], q, c);
+      off += (uint64_t) c * p.out_stride[d];
+      lin += c * p.lstride[d];
+    }
+    s_off[j] = off;
+    s_sm[j] = smem_slot (lin);
+  }
 
-    const uint32_t count = p.RT * p.TX * p.TY;
-    /* global -> shared: (r, y, x), r fastest */
-    for (uint32_t i = threadIdx.x; i < count; i += PERM_THREADS) {
-      const uint32_t a = fast_div (i, p.RT, p.magic_rt);
-      const uint32_t r = i - a * p.RT;
-      const uint32_t x = fast_div (a, p.TY, p.magic_ty);
-      const uint32_t y = a - x * p.TY;
-      if (r < rn && y < yn && x < xn) {
-        E v;
-        ld_stream<sizeof (E)> (&v, in + in_base + (uint64_t) x * p.x_in_stride + (uint64_t) y * p.R + r);
-        tile[((size_t) x * p.pitch + y) * p.RT + r] = v;
-      }
+  uint32_t my_tiles = 0;
+  if (blockIdx.x < p.n_tiles)
+    my_tiles = (p.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+
+  /* Where a tile sits (its base offsets, whether the box lies fully inside the tensor, its
+   * origin for the edge test) is worked out by ONE thread per tile and shared through a small
+   * ring: the decode walks all dims and is far too long to be repeated by 256 threads. */
+  struct TileInfo
+  {
+    uint64_t in_base, out_base;
+    uint32_t origin[PERM_DIMS];
+    int full;
+  };
+  constexpr int INFO = PERM_STAGES + 1;
+  __shared__ TileInfo info[INFO];
+  auto locate = [&] (uint32_t k) {
+    TileInfo &ti = info[k % INFO];
+    uint32_t q = blockIdx.x + k * gridDim.x, td;
+    bool full = true;
+    uint64_t ib = 0, ob = 0;
+    for (int d = 0; d < p.n; d++) {
+      divmod (q, p.ntile[d], q, td);
+      const uint32_t o = td * p.tile[d].d;
+      ti.origin[d] = o;
+      ib += (uint64_t) o * p.in_stride[d];
+      ob += (uint64_t) o * p.out_stride[d];
+      full = full && (o + p.tile[d].d <= p.size[d]);
     }
-    __syncthreads ();
-    /* shared -> global: (r, x, y), r fastest */
-    for (uint32_t i = threadIdx.x; i < count; i += PERM_THREADS) {
-      const uint32_t a = fast_div (i, p.RT, p.magic_rt);
-      const uint32_t r = i - a * p.RT;
-      const uint32_t y = fast_div (a, p.TX, p.magic_tx);
-      const uint32_t x = a - y * p.TX;
-      if (r < rn && y < yn && x < xn) {
-        E v = tile[((size_t) x * p.pitch + y) * p.RT + r];
-        st_stream<sizeof (E)> (out + out_base + (uint64_t) y * p.y_out_stride + (uint64_t) x * p.R + r, &v);
-      }
+    ti.in_base = ib;
+    ti.out_base = ob;
+    ti.full = full ? 1 : 0;
+  };
+  auto inside = [&] (uint32_t i, const uint32_t *origin, bool load_order) {
+    uint32_t q = i, c;
+    bool ok = true;
+    for (int k = 0; k < p.n; k++) {
+      const int d = load_order ? p.in_order[k] : k;
+      divmod (q, p.tile[d], q, c);
+      ok = ok && (origin[d] + c < p.size[d]);
     }
+    return ok;
+  };
+
+  if constexpr (ASYNC) {
+    auto issue = [&] (uint32_t k) {
+      if (k < my_tiles) {
+        const TileInfo &ti = info[k % INFO];
+        E *stage = ring + (size_t) (k % PERM_STAGES) * STAGE_ELEMS;
+        const E *src = in + ti.in_base;
+        if (ti.full) {
+#pragma unroll
+          for (int j = 0; j < PERM_EPT; j++)
+            if (threadIdx.x + j * PERM_THREADS < p.volume)
+              cp_async_elem (stage + l_sm[j], src + l_off[j]);
+        } else {
+          for (int j = 0; j < PERM_EPT; j++) {
+            const uint32_t i = threadIdx.x + j * PERM_THREADS;
+            if (i < p.volume && inside (i, ti.origin, true))
+              cp_async_elem (stage + l_sm[j], src + l_off[j]);
+          }
+        }
+      }
+      asm volatile ("cp.async.commit_group;" ::: "memory");   /* possibly empty: keeps the count */
+    };
+    if (threadIdx.x == 0)
+      for (uint32_t k = 0; k < (uint32_t) PERM_STAGES && k < my_tiles; k++)
+        locate (k);
     __syncthreads ();
+    for (int s = 0; s < PERM_STAGES - 1; s++)
+      issue ((uint32_t) s);
+    for (uint32_t k = 0; k < my_tiles; k++) {
+      issue (k + PERM_STAGES - 1);
+      asm volatile ("cp.async.wait_group %0;" :: "n" (PERM_STAGES - 1) : "memory");
+      __syncthreads ();
+      if (threadIdx.x == 0 && k + PERM_STAGES < my_tiles)
+        locate (k + PERM_STAGES);       /* slot (k + S) % (S + 1): not read before the next barrier */
+      const TileInfo &ti = info[k % INFO];
+      const E *stage = ring + (size_t) (k % PERM_STAGES) * STAGE_ELEMS;
+      E *dst = out + ti.out_base;
+      if (ti.full) {
+#pragma unroll
+        for (int j = 0; j < PERM_EPT; j++)
+          if (threadIdx.x + j * PERM_THREADS < p.volume) {
+            E w = stage[s_sm[j]];
+            st_stream<sizeof (E)> (dst + s_off[j], &w);
+          }
+      } else {
+        for (int j = 0; j < PERM_EPT; j++) {
+          const uint32_t i = threadIdx.x + j * PERM_THREADS;
+          if (i < p.volume && inside (i, ti.origin, false)) {
+            E w = stage[s_sm[j]];
+            st_stream<sizeof (E)> (dst + s_off[j], &w);
+          }
+        }
+      }
+      __syncthreads ();         /* the stage is overwritten by the issue of the next iteration */
+    }
+  } else {
+    if (threadIdx.x == 0 && my_tiles > 0)
+      locate (0);
+    __syncthreads ();
+    for (uint32_t k = 0; k < my_tiles; k++) {
+      const TileInfo &ti = info[k % INFO];
+      const E *src = in + ti.in_base;
+      E *dst = out + ti.out_base;
+      E v[PERM_EPT];
+      if (ti.full) {
+#pragma unroll
+        for (int j = 0; j < PERM_EPT; j++)
+          if (threadIdx.x + j * PERM_THREADS < p.volume)
+            ld_stream<sizeof (E)> (&v[j], src + l_off[j]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < PERM_EPT; j++) {
+          const uint32_t i = threadIdx.x + j * PERM_THREADS;
+          if (i < p.volume && inside (i, ti.origin, true))
+            ld_stream<sizeof (E)> (&v[j], src + l_off[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < PERM_EPT; j++)
+        if (threadIdx.x + j * PERM_THREADS < p.volume)
+          ring[l_sm[j]] = v[j];
+      if (threadIdx.x == 0 && k + 1 < my_tiles)
+        locate (k + 1);
+      __syncthreads ();
+      if (ti.full) {
+#pragma unroll
+        for (int j = 0; j < PERM_EPT; j++)
+          if (threadIdx.x + j * PERM_THREADS < p.volume) {
+            E w = ring[s_sm[j]];
+            st_stream<sizeof (E)> (dst + s_off[j], &w);
+          }
+      } else {
+        for (int j = 0; j < PERM_EPT; j++) {
+          const uint32_t i = threadIdx.x + j * PERM_THREADS;
+          if (i < p.volume && inside (i, ti.origin, false)) {
+            E w = ring[s_sm[j]];
+            st_stream<sizeof (E)> (dst + s_off[j], &w);
+          }
+        }
+      }
+      __syncthreads ();
+    }
   }
 }
 
@@ -139,30 +304,6 @@ copy_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ o
     out[b] = in[b];
 }
 
-static uint32_t
-magic_of (uint32_t d)
-{
-  if (d <= 1)
-    return 0;
-  return (uint32_t) (((1ull << 32) + d - 1) / d);
-}
-
-struct uint128_e { uint32_t v[4]; };
-
-template <typename E> static int
-launch_permute_t (const PermDev &p, size_t smem, const void *in, void *out, unsigned int grid,
-    cudaStream_t stream)
-{
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute (permute_kernel<E>,
-        cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-    if (e != cudaSuccess)
-      return (int) e;
-  }
-  permute_kernel<E><<<grid, PERM_THREADS, smem, stream>>> ((const E *) in, (E *) out, p);
-  return (int) cudaGetLastError ();
-}
-
 static int
 launch_copy (const void *in, void *out, size_t bytes, const LaunchCfg &cfg, cudaStream_t stream)
 {
@@ -182,6 +323,32 @@ launch_copy (const void *in, void *out, size_t bytes, const LaunchCfg &cfg, cuda
   return (int) cudaGetLastError ();
 }
 
+template <typename E, bool ASYNC> static int
+launch_permute_t (const PermDev &p, const void *in, void *out, const LaunchCfg &cfg,
+    cudaStream_t stream)
+{
+  const size_t smem = (size_t) (ASYNC ? PERM_STAGES : 1) * (PERM_TILE_MAX + PERM_TILE_MAX / 32 + 1)
+      * sizeof (E);
+  static int resident = 0;
+  if (resident == 0) {
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute (permute_kernel<E, ASYNC>,
+          cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+      if (e != cudaSuccess)
+        return (int) e;
+    }
+    resident = resident_blocks_per_sm (permute_kernel<E, ASYNC>, PERM_THREADS, smem);
+  }
+  /* persistent: every block amortises its coordinate set-up over many tiles */
+  uint64_t grid = p.n_tiles;
+  const uint64_t cap = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : resident);
+  if (grid > cap)
+    grid = cap;
+  permute_kernel<E, ASYNC><<<(unsigned int) grid, PERM_THREADS, smem, stream>>> ((const E *) in,
+      (E *) out, p);
+  return (int) cudaGetLastError ();
+}
+
 int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_elems,
     uint32_t batch, const LaunchCfg &cfg, cudaStream_t stream)
 {
@@ -189,7 +356,7 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
     return 0;
   /* 1. collect (size, in_stride, out_stride), drop extent-1 dims, append the batch */
   struct Dim { uint64_t size, in, out; };
-  Dim dims[NNSB_PERM_MAX_RANK + 1];
+  Dim dims[PERM_DIMS];
   int n = 0;
   uint64_t ostride = 1;
   for (int i = 0; i < d0.rank; i++) {
@@ -221,103 +388,133 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
   const size_t total = (size_t) frame_elems * batch;
   if (n == 0 || (n == 1 && dims[0].in == 1))
     return launch_copy (in, out, total * d0.es, cfg, stream);
+  for (int i = 0; i < n; i++)
+    if (dims[i].size > 0xffffffffull)
+      return (int) cudaErrorInvalidValue;
 
-  /* 3. pick I, X, Y */
+  /* 3. video-shaped [P][C] <-> [C][P] (2..4 channels): the TMA pipeline (k_plane.cu) */
+  if (!getenv ("NNSB_NO_PLANE")) {
+    /* find X (out stride 1) and Y (in stride 1); everything else is an outer dim */
+    int ix = -1, iy = -1;
+    for (int i = 0; i < n; i++) {
+      if (dims[i].out == 1) ix = i;
+      if (dims[i].in == 1) iy = i;
+    }
+    if (ix >= 0 && iy >= 0 && ix != iy) {
+      uint32_t o_size[PERM_DIMS];
+      uint64_t o_in[PERM_DIMS], o_out[PERM_DIMS];
+      int no = 0;
+      for (int i = 0; i < n; i++)
+        if (i != ix && i != iy) {
+          o_size[no] = (uint32_t) dims[i].size;
+          o_in[no] = dims[i].in;
+          o_out[no] = dims[i].out;
+          no++;
+        }
+      int r = -1;
+      if (dims[iy].size >= 2 && dims[iy].size <= 4 && dims[ix].in == dims[iy].size)
+        r = launch_plane (true, (int) dims[iy].size, d0.es, dims[ix].size, dims[iy].out, no, o_size,
+            o_in, o_out, in, out, cfg, stream);
+      else if (dims[ix].size >= 2 && dims[ix].size <= 4 && dims[iy].out == dims[ix].size)
+        r = launch_plane (false, (int) dims[ix].size, d0.es, dims[iy].size, dims[ix].in, no, o_size,
+            o_out, o_in, in, out, cfg, stream);
+      if (r != -1)
+        return r;
+    }
+  }
+
+  /* 4. the box: >= 32-element runs on both sides, then grown to ~2048 elements */
   PermDev p;
   memset (&p, 0, sizeof (p));
-  int ix = -1, iy = -1, ii = -1;
-  uint64_t R = 1;
-  if (dims[0].in == 1) {
-    ii = 0;
-    R = dims[0].size;
+  p.n = n;
+  int in_order[PERM_DIMS];
+  for (int i = 0; i < n; i++)
+    in_order[i] = i;
+  for (int i = 1; i < n; i++)           /* insertion sort by input stride */
+    for (int j = i; j > 0 && dims[in_order[j]].in < dims[in_order[j - 1]].in; j--) {
+      const int t = in_order[j];
+      in_order[j] = in_order[j - 1];
+      in_order[j - 1] = t;
+    }
+  uint64_t T[PERM_DIMS];
+  for (int i = 0; i < n; i++)
+    T[i] = 1;
+  const uint64_t RUN = getenv ("NNSB_PERM_RUN") ? (uint64_t) atoi (getenv ("NNSB_PERM_RUN")) : 32;
+  {
+    uint64_t prod = 1;
+    for (int k = 0; k < n && prod < RUN; k++) {
+      const int d = in_order[k];
+      uint64_t want = (RUN + prod - 1) / prod;
+      if (want > dims[d].size) want = dims[d].size;
+      if (T[d] < want) T[d] = want;
+      prod *= want;
+    }
+    prod = 1;
+    for (int d = 0; d < n && prod < RUN; d++) {
+      uint64_t want = (RUN + prod - 1) / prod;
+      if (want > dims[d].size) want = dims[d].size;
+      if (T[d] < want) T[d] = want;
+      prod *= want;
+    }
   }
+  auto volume = [&] () { uint64_t v = 1; for (int i = 0; i < n; i++) v *= T[i]; return v; };
+  /* too large (both runs needed many dims): shrink the largest extents */
+  while (volume () > (uint64_t) PERM_TILE_MAX) {
+    int big = 0;
+    for (int i = 1; i < n; i++)
+      if (T[i] > T[big]) big = i;
+    T[big] = (T[big] + 1) / 2;
+  }
+  /* grow: alternately lengthen the output run and the input run */
+  for (int round = 0; round < 64; round++) {
+    bool grew = false;
+    for (int side = 0; side < 2; side++) {
+      for (int k = 0; k < n; k++) {
+        const int d = side == 0 ? k : in_order[k];
+        if (T[d] < dims[d].size) {
+          uint64_t nt = T[d] * 2;
+          if (nt > dims[d].size) nt = dims[d].size;
+          if (volume () / T[d] * nt <= (uint64_t) PERM_TILE_MAX) {
+            T[d] = nt;
+            grew = true;
+          }
+          break;                /* only the first non-full dim of each side */
+        }
+      }
+    }
+    if (!grew)
+      break;
+  }
+  uint64_t tiles = 1;
   for (int i = 0; i < n; i++) {
-    if (i == ii)
-      continue;
-    if (ix < 0 && dims[i].out == R)
-      ix = i;
-    if (iy < 0 && dims[i].in == R)
-      iy = i;
+    p.size[i] = (uint32_t) dims[i].size;
+    p.tile[i] = make_fastdiv ((uint32_t) T[i]);
+    p.ntile[i] = make_fastdiv ((uint32_t) ((dims[i].size + T[i] - 1) / T[i]));
+    p.in_stride[i] = dims[i].in;
+    p.out_stride[i] = dims[i].out;
+    p.in_order[i] = in_order[i];
+    tiles *= p.ntile[i].d;
   }
-  if (ix < 0 || iy < 0 || ix == iy || R > 0xffffffffull || dims[ix].size > 0xffffffffull
-      || dims[iy].size > 0xffffffffull)
-    return (int) cudaErrorInvalidValue;   /* cannot happen for a canonical permutation */
-  p.R = (uint32_t) R;
-  p.SX = (uint32_t) dims[ix].size;
-  p.SY = (uint32_t) dims[iy].size;
-  p.x_in_stride = dims[ix].in;
-  p.y_out_stride = dims[iy].out;
-  for (int i = 0; i < n; i++) {
-    if (i == ii || i == ix || i == iy)
-      continue;
-    p.o_size[p.n_outer] = (uint32_t) dims[i].size;
-    p.o_in[p.n_outer] = dims[i].in;
-    p.o_out[p.n_outer] = dims[i].out;
-    p.n_outer++;
+  {
+    uint32_t ls = 1;
+    for (int k = 0; k < n; k++) {
+      p.lstride[in_order[k]] = ls;
+      ls *= p.tile[in_order[k]].d;
+    }
   }
+  p.volume = (uint32_t) volume ();
+  if (tiles >= (1ull << 31))
+    return (int) cudaErrorInvalidValue;
+  p.n_tiles = (uint32_t) tiles;
 
-  /* 3b. video-shaped cases go to the TMA pipeline (k_plane.cu) when they qualify */
-  if (p.R == 1 && !getenv ("NNSB_NO_PLANE")) {
-    int r = -1;
-    if (p.SY >= 2 && p.SY <= 4 && p.x_in_stride == p.SY)
-      /* [P][C] -> [C][P]: Y = channels (input-contiguous), X = pixels */
-      r = launch_plane (true, (int) p.SY, d0.es, p.SX, p.y_out_stride, p.n_outer, p.o_size,
-          p.o_in, p.o_out, in, out, cfg, stream);
-    else if (p.SX >= 2 && p.SX <= 4 && p.y_out_stride == p.SX)
-      /* [C][P] -> [P][C]: X = channels (output-contiguous), Y = pixels */
-      r = launch_plane (false, (int) p.SX, d0.es, p.SY, p.x_in_stride, p.n_outer, p.o_size,
-          p.o_out, p.o_in, in, out, cfg, stream);
-    if (r != -1)
-      return r;
-  }
-
-  /* 4. tile shape: ~8 KiB of payload, runs of >= 32 elements on both global sides */
-  const uint32_t budget = (uint32_t) (d0.es <= 4 ? 2048 : 8192 / d0.es);
-  p.RT = p.R < budget ? p.R : budget;
-  uint32_t rem = budget / p.RT;
-  if (rem < 1)
-    rem = 1;
-  const uint32_t run = (32 + p.RT - 1) / p.RT;       /* tiles of the other dims per 32-element run */
-  p.TY = p.SY < run ? p.SY : run;
-  if (p.TY > rem)
-    p.TY = rem;
-  if (p.TY < 1)
-    p.TY = 1;
-  uint32_t tx = rem / p.TY;
-  if (tx < 1)
-    tx = 1;
-  if (tx > 32)
-    tx = (tx / 32) * 32;
-  p.TX = p.SX < tx ? p.SX : tx;
-  /* give unused budget back to Y (e.g. small X) */
-  if ((uint64_t) p.RT * p.TX * p.TY * 2 <= budget) {
-    uint32_t ty = budget / (p.RT * p.TX);
-    p.TY = p.SY < ty ? p.SY : ty;
-  }
-  p.nR = (p.R + p.RT - 1) / p.RT;
-  p.nX = (p.SX + p.TX - 1) / p.TX;
-  p.nY = (p.SY + p.TY - 1) / p.TY;
-  p.pitch = p.TY | 1u;
-  p.magic_rt = magic_of (p.RT);
-  p.magic_ty = magic_of (p.TY);
-  p.magic_tx = magic_of (p.TX);
-  uint64_t tiles = (uint64_t) p.nR * p.nX * p.nY;
-  for (int i = 0; i < p.n_outer; i++)
-    tiles *= p.o_size[i];
-  p.n_tiles = tiles;
-  const size_t smem = (size_t) p.TX * p.pitch * p.RT * d0.es;
-
-  uint64_t grid = tiles;
-  const uint64_t cap = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 16);
-  if (grid > cap)
-    grid = cap;
-
+  const bool sync_only = getenv ("NNSB_PERM_SYNC") != nullptr;
   switch (d0.es) {
-    case 1: return launch_permute_t<uint8_t> (p, smem, in, out, (unsigned int) grid, stream);
-    case 2: return launch_permute_t<uint16_t> (p, smem, in, out, (unsigned int) grid, stream);
-    case 4: return launch_permute_t<uint32_t> (p, smem, in, out, (unsigned int) grid, stream);
-    case 8: return launch_permute_t<Bytes<8> > (p, smem, in, out, (unsigned int) grid, stream);
-    case 16: return launch_permute_t<Bytes<16> > (p, smem, in, out, (unsigned int) grid, stream);
+    case 1: return launch_permute_t<uint8_t, false> (p, in, out, cfg, stream);
+    case 2: return launch_permute_t<uint16_t, false> (p, in, out, cfg, stream);
+    case 4: return sync_only ? launch_permute_t<uint32_t, false> (p, in, out, cfg, stream)
+        : launch_permute_t<uint32_t, true> (p, in, out, cfg, stream);
+    case 8: return sync_only ? launch_permute_t<uint64_t, false> (p, in, out, cfg, stream)
+        : launch_permute_t<uint64_t, true> (p, in, out, cfg, stream);
     default: return (int) cudaErrorInvalidValue;
   }
 }

@@ -56,6 +56,10 @@ __device__ __forceinline__ void mbar_expect_tx (uint64_t *bar, uint32_t bytes)
   asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
       :: "r" (smem_u32 (bar)), "r" (bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive (uint64_t *bar)
+{
+  asm volatile ("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r" (smem_u32 (bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait (uint64_t *bar, uint32_t parity)
 {
   const uint32_t addr = smem_u32 (bar);
@@ -109,7 +113,7 @@ template <int C, int ES> struct PlaneGeom
   static constexpr int TP = PLANE_THREADS * G;            /* pixels per tile */
   static constexpr int TILE_BYTES = TP * C * ES;          /* 256 * 16 * C */
   static constexpr int PLANE_BYTES = TP * ES;             /* 4096 */
-  static constexpr size_t SMEM = (size_t) PLANE_STAGES * 2 * TILE_BYTES + 64;
+  static constexpr size_t SMEM = (size_t) PLANE_STAGES * 2 * TILE_BYTES + 3 * PLANE_STAGES * 8 + 32;
 };
 
 /* element i (ES bytes wide) of a little-endian array of 32-bit words; i is a compile-time
@@ -138,15 +142,28 @@ plane_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ 
   extern __shared__ __align__ (128) unsigned char smem[];
   unsigned char *in_buf = smem;                                          /* [STAGES][TILE_BYTES] */
   unsigned char *out_buf = smem + (size_t) PLANE_STAGES * Gm::TILE_BYTES;   /* [STAGES][TILE_BYTES] */
+  /* per stage: full  = the input tile has landed (1 arrival + transaction bytes)
+   *            empty = the previous bulk store out of out_buf[s] has drained (thread 0 arrives)
+   *            done  = all 256 threads have re-ordered the tile (each arrives once)
+   * No CTA-wide barrier sits in the steady-state loop: only thread 0 ever waits for the other
+   * threads, so the remaining warps run ahead to the next tile as soon as its data is there. */
   uint64_t *full = reinterpret_cast<uint64_t *> (smem + (size_t) PLANE_STAGES * 2 * Gm::TILE_BYTES);
+  uint64_t *empty = full + PLANE_STAGES;
+  uint64_t *done = empty + PLANE_STAGES;
 
   const int t = threadIdx.x;
   if (t == 0) {
-    for (int s = 0; s < PLANE_STAGES; s++)
+    for (int s = 0; s < PLANE_STAGES; s++) {
       mbar_init (&full[s], 1);
+      mbar_init (&empty[s], 1);
+      mbar_init (&done[s], PLANE_THREADS);
+    }
     asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads ();
+  if (t == 0)
+    for (int s = 0; s < PLANE_STAGES; s++)
+      mbar_arrive (&empty[s]);          /* every output buffer starts out free (phase 0) */
 
   /* tile k of this CTA is global tile blockIdx.x + k * gridDim.x */
   auto tile_of = [&] (uint64_t k) { return (uint64_t) blockIdx.x + k * gridDim.x; };
@@ -210,11 +227,8 @@ plane_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ 
   for (uint64_t k = 0; k < my_tiles; k++) {
     const int s = (int) (k % PLANE_STAGES);
     const uint32_t parity = (uint32_t) ((k / PLANE_STAGES) & 1);
-    /* the bulk store that last read out_buf[s] (tile k - STAGES) must have drained */
-    if (t == 0)
-      bulk_wait_read<PLANE_STAGES - 1> ();
     mbar_wait (&full[s], parity);
-    __syncthreads ();
+    mbar_wait (&empty[s], parity);      /* the store that last read out_buf[s] has drained */
 
     const unsigned char *src = in_buf + (size_t) s * Gm::TILE_BYTES;
     unsigned char *dst = out_buf + (size_t) s * Gm::TILE_BYTES;
@@ -258,11 +272,17 @@ plane_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ 
             make_uint4 (il[4 * j + 0], il[4 * j + 1], il[4 * j + 2], il[4 * j + 3]);
     }
     fence_async_smem ();        /* generic-proxy writes -> visible to the bulk store */
-    __syncthreads ();
+    mbar_arrive (&done[s]);
     if (t == 0) {
+      mbar_wait (&done[s], parity);     /* everyone has read in_buf[s] and written out_buf[s] */
       issue_store (tile_of (k), s);
       if (k + PLANE_STAGES < my_tiles)
-        issue_load (tile_of (k + PLANE_STAGES), s);   /* in_buf[s] has been consumed by everyone */
+        issue_load (tile_of (k + PLANE_STAGES), s);
+      /* stores complete in order: once all but the newest STAGES-1 are done, the buffer of
+       * tile k-STAGES+1 -- the one iteration k+1 writes -- is free */
+      bulk_wait_read<PLANE_STAGES - 1> ();
+      if (k + 1 >= (uint64_t) PLANE_STAGES)
+        mbar_arrive (&empty[(k + 1) % PLANE_STAGES]);
     }
   }
   if (t == 0)
@@ -344,7 +364,7 @@ int launch_plane (bool to_planar, int channels, int es, uint64_t pixels, uint64_
     p.n_tiles *= o_size[i];
   }
   /* tiny problems are not worth a pipeline */
-  if (pixels * channels * es < 64 * 1024)
+  if (p.n_tiles * (uint64_t) PLANE_THREADS * 16 * channels < 64 * 1024)
     return -1;
   switch (channels) {
     case 2: return launch_plane_es<2> (es, to_planar, p, in, out, cfg, stream);

@@ -453,3 +453,46 @@ def test_stride_strip_unaligned_pointers(dev, port):
     assert bits_equal(got, port.stride_strip(src, c, w, h))
     dev.free(d_src)
     dev.free(d_dst)
+
+
+# ---------------------------------------------------------------------------------------
+# against the committed outputs of the reference's own code (tests/golden/ref_golden.npz)
+# ---------------------------------------------------------------------------------------
+def test_gpu_matches_reference_golden_fixture(dev):
+    import os
+    from test_oracle_golden import ARITH_CASES
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_golden.npz"))
+    for it in TYPES:
+        x = gold["typecast/%s/in" % it]
+        for ot in TYPES:
+            plan = dev.plan("typecast", ot, it, [x.size])
+            got = plan.run_host(x)
+            plan.close()
+            assert bits_equal(got, gold["typecast/%s/%s" % (it, ot)]), (it, ot)
+    for name, it, dim, opt, ops, pc, cd in ARITH_CASES:
+        plan = dev.plan("arithmetic", opt, it, dim)
+        got = plan.run_host(gold["arith/%s/in" % name])
+        plan.close()
+        assert bits_equal(got, gold["arith/%s/out" % name]), name
+    x = gold["transpose/in"]
+    for order in ORDERS:
+        plan = dev.plan("transpose", "%d:%d:%d:3" % order[:3], "float32", [20, 10, 3, 2])
+        assert bits_equal(plan.run_host(x), gold["transpose/%d%d%d" % order[:3]])
+        plan.close()
+    for to in (1, 2, 3):
+        plan = dev.plan("dimchg", "0:%d" % to, "uint8", [3, 16, 16, 1])
+        assert bits_equal(plan.run_host(gold["dimchg/in"]), gold["dimchg/0_%d" % to])
+        plan.close()
+    for it, lo, hi, opt in (("int8", -50, 50, "-50:50"), ("uint32", 20, 80, "20:80"),
+                            ("float32", -33.3, 77.7, "-33.3:77.7"), ("float64", -1e3, 1e3, "-1e3:1e3"),
+                            ("int64", -1e18, 1e18, "-1e18:1e18")):
+        x = gold["clamp/%s/in" % it]
+        plan = dev.plan("clamp", opt, it, [x.size])
+        assert bits_equal(plan.run_host(x), gold["clamp/%s/out" % it]), it
+        plan.close()
+    xs = gold["stand/in"]
+    for mode in ("default", "dc-average"):
+        for pc in (False, True):
+            plan = dev.plan("stand", mode + (",per-channel:true" if pc else ""), "float32", [50, 100, 1, 1])
+            _stand_close(plan.run_host(xs), gold["stand/%s/%d" % (mode, int(pc))], 10.0 if mode == "dc-average" else 1.0)
+            plan.close()
