@@ -332,6 +332,11 @@ NNSB_API int nnsb_transform_get_config (nnsb_transform * t, int direction, nnsb_
 /* element-owned memory helpers (the CUDA GstAllocator's alloc / free) */
 NNSB_API int nnsb_transform_alloc (nnsb_transform * t, size_t size, int on_device, nnsb_memory * out);
 NNSB_API int nnsb_memory_release (nnsb_memory * mem);
+/* synchronous copies between a device memory of this element and host memory: what the CUDA
+ * GstAllocator's mem_map / mem_unmap do for peers that are not CUDA-aware (gst_memory_map,
+ * gsttensor_transform.c:1725,1761) */
+NNSB_API int nnsb_transform_download (nnsb_transform * t, void *host_dst, const nnsb_memory * dev_src);
+NNSB_API int nnsb_transform_upload (nnsb_transform * t, const nnsb_memory * dev_dst, const void *host_src);
 /* kernels launched by this element so far */
 NNSB_API int nnsb_transform_kernel_launches (nnsb_transform * t, uint64_t *count);
 

@@ -152,6 +152,8 @@ _PROTOS = {
     "nnsb_transform_get_config": (C.c_int, [_VP, C.c_int, C.POINTER(TensorsConfig)]),
     "nnsb_transform_alloc": (C.c_int, [_VP, C.c_size_t, C.c_int, C.POINTER(Memory)]),
     "nnsb_memory_release": (C.c_int, [C.POINTER(Memory)]),
+    "nnsb_transform_download": (C.c_int, [_VP, _VP, C.POINTER(Memory)]),
+    "nnsb_transform_upload": (C.c_int, [_VP, C.POINTER(Memory), _VP]),
     "nnsb_transform_kernel_launches": (C.c_int, [_VP, C.POINTER(C.c_uint64)]),
     "nnsb_converter_new": (C.c_int, [C.c_int, C.POINTER(_VP)]),
     "nnsb_converter_free": (C.c_int, [_VP]),

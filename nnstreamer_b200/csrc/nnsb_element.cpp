@@ -444,6 +444,32 @@ nnsb_memory_release (nnsb_memory * mem)
 }
 
 extern "C" int
+nnsb_transform_download (nnsb_transform * t, void *host_dst, const nnsb_memory * dev_src)
+{
+  if (!t || !host_dst || !dev_src || !dev_src->on_device)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_transform_download: invalid argument");
+  int r = ensure_device (t);
+  if (!r)
+    r = nnsb_d2h_async (t->stream[0], host_dst, dev_src->data, dev_src->size);
+  if (!r)
+    r = nnsb_stream_sync (t->stream[0]);
+  return r;
+}
+
+extern "C" int
+nnsb_transform_upload (nnsb_transform * t, const nnsb_memory * dev_dst, const void *host_src)
+{
+  if (!t || !host_src || !dev_dst || !dev_dst->on_device)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_transform_upload: invalid argument");
+  int r = ensure_device (t);
+  if (!r)
+    r = nnsb_h2d_async (t->stream[0], dev_dst->data, host_src, dev_dst->size);
+  if (!r)
+    r = nnsb_stream_sync (t->stream[0]);
+  return r;
+}
+
+extern "C" int
 nnsb_transform_kernel_launches (nnsb_transform * t, uint64_t * count)
 {
   if (!t || !count)

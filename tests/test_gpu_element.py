@@ -243,6 +243,20 @@ def test_device_memory_in_device_memory_out(dev, port):
     t2.close()
 
 
+def test_element_memory_upload_download_round_trip():
+    """The CUDA GstAllocator's mem_map / mem_unmap path: device memory <-> host bytes."""
+    import ctypes as C
+    t = TensorTransform(mode="typecast", option="float32")
+    m = t.alloc(4096, on_device=True)
+    src = np.arange(4096, dtype=np.uint8)
+    assert L.lib().nnsb_transform_upload(t.handle, C.byref(m), src.ctypes.data_as(C.c_void_p)) == 0
+    dst = np.zeros(4096, dtype=np.uint8)
+    assert L.lib().nnsb_transform_download(t.handle, dst.ctypes.data_as(C.c_void_p), C.byref(m)) == 0
+    assert bits_equal(src, dst)
+    L.lib().nnsb_memory_release(C.byref(m))
+    t.close()
+
+
 # ---- tensor_converter ----------------------------------------------------------------------
 @pytest.mark.parametrize("fmt,c,w,h", [("RGB", 3, 642, 480), ("GRAY8", 1, 642, 480), ("RGB", 3, 640, 480),
                                        ("BGRx", 4, 642, 480), ("RGB", 3, 1918, 64)])
