@@ -245,6 +245,67 @@ def extra_kernels(dev, peak):
     return out
 
 
+def multi_stream_chain(device_id, n_streams=8, frames_per_stream=40):
+    """BASELINE configs[4] on ONE GPU: `n_streams` concurrent 1080p pipelines, each
+    tensor_converter -> tensor_transform typecast:float32 -> arithmetic add:-127.5,div:127.5 ->
+    transpose 1:2:0:3, one host thread and one set of elements (own CUDA streams) per pipeline.
+    Returns frames/s device-resident (frames pre-staged in HBM) and with the H2D of every
+    frame inside the timed region (the float CHW result stays on the device for the consumer)."""
+    from nnstreamer_b200 import Device, TensorConverter, TensorTransform, device_memory
+    caps = ("video/x-raw, format=(string)RGB, width=(int)%d, height=(int)%d, framerate=(fraction)30/1" % (W, H))
+    out = {}
+    for mode in ("device_resident", "h2d_per_frame"):
+        dev = Device(device_id)
+        pipes = []
+        for sidx in range(n_streams):
+            conv = TensorConverter(device_id=device_id)
+            c1 = conv.set_caps(caps)
+            t1 = TensorTransform(device_id=device_id, mode="typecast", option="float32")
+            c2 = t1.negotiate(c1)
+            t2 = TensorTransform(device_id=device_id, mode="arithmetic", option="add:-127.5,div:127.5")
+            c3 = t2.negotiate(c2)
+            t3 = TensorTransform(device_id=device_id, mode="transpose", option="1:2:0:3")
+            t3.negotiate(c3)
+            rng = np.random.default_rng(sidx)
+            if mode == "device_resident":
+                frame = device_memory(dev.upload(rng.integers(0, 256, FRAME_ELEMS, dtype=np.uint8)), FRAME_ELEMS)
+            else:
+                arr, _ptr = dev.pinned(FRAME_ELEMS, np.uint8)
+                arr[:] = rng.integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
+                frame = arr
+            pipes.append((conv, t1, t2, t3, frame))
+
+        def run(pipe, n):
+            conv, t1, t2, t3, frame = pipe
+            for _ in range(n):
+                flow, m0 = conv.chain(frame)
+                flow, (m1,) = t1.transform([m0])
+                flow, (m2,) = t2.transform([m1])
+                flow, (m3,) = t3.transform([m2])
+                for m in (m0, m1, m2, m3):
+                    m.release()
+
+        for p in pipes:
+            run(p, 3)
+        ths = [threading.Thread(target=run, args=(p, frames_per_stream)) for p in pipes]
+        t0 = time.perf_counter()
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        dt = time.perf_counter() - t0
+        fps = n_streams * frames_per_stream / dt
+        # algorithmic bytes per element along the chain: converter 0 (+1 when uploaded),
+        # typecast 5, arithmetic 8, transpose 8 (SURVEY.md 8d)
+        out[mode] = {"frames/s": fps, "GB/s": fps * FRAME_ELEMS * 21 / 1e9,
+                     "streams": n_streams, "frames_per_stream": frames_per_stream}
+        for conv, t1, t2, t3, frame in pipes:
+            for e in (conv, t1, t2, t3):
+                e.close()
+        dev.close()
+    return out
+
+
 def run_b200(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -362,6 +423,8 @@ def run_b200(args):
                 dev.free(d_out)
                 d_in = d_out = None
                 extras = extra_kernels(dev, peak)
+                extras["chain_8_streams_1080p_converter_typecast_arith_transpose"] = \
+                    multi_stream_chain(local_rank)
 
     if rank == 0:
         ms_step = ms_dev / args.steps
