@@ -105,17 +105,18 @@ permute_kernel (const E *__restrict__ in, E *__restrict__ out, const __grid_cons
   E *ring = reinterpret_cast<E *> (smem_raw);
 
   /* in-box coordinates of this thread's elements: computed once per kernel */
+  /* (in-box offsets fit 32 bits: the launcher checks the box span) */
   uint32_t l_sm[PERM_EPT], s_sm[PERM_EPT];
-  uint64_t l_off[PERM_EPT], s_off[PERM_EPT];
+  uint32_t l_off[PERM_EPT], s_off[PERM_EPT];
 #pragma unroll
   for (int j = 0; j < PERM_EPT; j++) {
     const uint32_t i = threadIdx.x + j * PERM_THREADS;
     uint32_t q = i, c;
-    uint64_t off = 0;
+    uint32_t off = 0;
     for (int k = 0; k < p.n; k++) {
       const int d = p.in_order[k];
       divmod (q, p.tile[d], q, c);
-      off += (uint64_t) c * p.in_stride[d];
+      off += c * (uint32_t) p.in_stride[d];
     }
     l_off[j] = off;
     l_sm[j] = smem_slot (i);
@@ -124,12 +125,13 @@ permute_kernel (const E *__restrict__ in, E *__restrict__ out, const __grid_cons
     uint32_t lin = 0;
     for (int d = 0; d < p.n; d++) {
       divmod (q, p.tile[d], q, c);
-      off += (uint64_t) c * p.out_stride[d];
+      off += c * (uint32_t) p.out_stride[d];
       lin += c * p.lstride[d];
     }
     s_off[j] = off;
     s_sm[j] = smem_slot (lin);
   }
+  const bool whole = (p.volume == (uint32_t) PERM_TILE_MAX);   /* every thread owns 8 elements */
 
   uint32_t my_tiles = 0;
   if (blockIdx.x < p.n_tiles)
@@ -180,7 +182,11 @@ permute_kernel (const E *__restrict__ in, E *__restrict__ out, const __grid_cons
         const TileInfo &ti = info[k % INFO];
         E *stage = ring + (size_t) (k % PERM_STAGES) * STAGE_ELEMS;
         const E *src = in + ti.in_base;
-        if (ti.full) {
+        if (ti.full && whole) {
+#pragma unroll
+          for (int j = 0; j < PERM_EPT; j++)
+            cp_async_elem (stage + l_sm[j], src + l_off[j]);
+        } else if (ti.full) {
 #pragma unroll
           for (int j = 0; j < PERM_EPT; j++)
             if (threadIdx.x + j * PERM_THREADS < p.volume)
@@ -210,7 +216,15 @@ permute_kernel (const E *__restrict__ in, E *__restrict__ out, const __grid_cons
       const TileInfo &ti = info[k % INFO];
       const E *stage = ring + (size_t) (k % PERM_STAGES) * STAGE_ELEMS;
       E *dst = out + ti.out_base;
-      if (ti.full) {
+      if (ti.full && whole) {
+        E w[PERM_EPT];
+#pragma unroll
+        for (int j = 0; j < PERM_EPT; j++)
+          w[j] = stage[s_sm[j]];
+#pragma unroll
+        for (int j = 0; j < PERM_EPT; j++)
+          st_stream<sizeof (E)> (dst + s_off[j], &w[j]);
+      } else if (ti.full) {
 #pragma unroll
         for (int j = 0; j < PERM_EPT; j++)
           if (threadIdx.x + j * PERM_THREADS < p.volume) {
@@ -505,6 +519,16 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
   p.volume = (uint32_t) volume ();
   if (tiles >= (1ull << 31))
     return (int) cudaErrorInvalidValue;
+  {
+    /* in-box offsets are kept in 32 bits: shrink boxes whose span would not fit (huge strides) */
+    uint64_t span_in = 0, span_out = 0;
+    for (int i = 0; i < n; i++) {
+      span_in += (uint64_t) (T[i] - 1) * dims[i].in;
+      span_out += (uint64_t) (T[i] - 1) * dims[i].out;
+    }
+    if (span_in >= (1ull << 32) || span_out >= (1ull << 32))
+      return (int) cudaErrorInvalidValue;
+  }
   p.n_tiles = (uint32_t) tiles;
 
   const bool sync_only = getenv ("NNSB_PERM_SYNC") != nullptr;
