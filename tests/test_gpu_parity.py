@@ -496,3 +496,58 @@ def test_gpu_matches_reference_golden_fixture(dev):
             plan = dev.plan("stand", mode + (",per-channel:true" if pc else ""), "float32", [50, 100, 1, 1])
             _stand_close(plan.run_host(xs), gold["stand/%s/%d" % (mode, int(pc))], 10.0 if mode == "dc-average" else 1.0)
             plan.close()
+
+
+# ---------------------------------------------------------------------------------------
+# guard bands: no kernel may write outside its output (compute-sanitizer is closed on this pool)
+# ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", [
+    ("typecast", "float32", "uint8", [10007], 1),
+    ("arithmetic", "typecast:float32,add:-127.5,div:127.5", "uint8", [3, 211, 157, 1], 2),
+    ("arithmetic", "per-channel:true@0,mul:2@1", "int8", [3, 160, 144, 1], 1),
+    ("clamp", "-5:5", "int16", [9001], 1),
+    ("transpose", "1:2:0:3", "float32", [3, 1000, 77, 1], 1),      # TMA path, partial last tile
+    ("transpose", "2:0:1:3", "uint8", [336, 100, 3, 1], 3),        # TMA path, planar -> interleaved
+    ("transpose", "2:1:0:3", "float32", [33, 65, 17, 2], 1),       # box tiles sticking out
+    ("transpose", "1:0:2:3", "uint16", [61, 37, 5, 1], 1),
+    ("dimchg", "0:3", "float64", [3, 10, 10, 4, 5], 1),
+    ("stand", "default,per-channel:true", "float32", [3, 61, 37, 1], 3),
+    ("stand", "dc-average", "uint8", [1000, 7, 1, 1], 1),
+], ids=lambda c: "%s-%s-%s" % (c[0], c[1], "x".join(str(d) for d in c[3])))
+def test_no_writes_outside_the_output(dev, case):
+    mode, option, itype, dim, batch = case
+    GUARD = 512
+    n = int(np.prod(dim)) * batch
+    x = rand_small(itype, n, seed=99)
+    plan = dev.plan(mode, option, itype, dim)
+    out_bytes = plan.out_size * batch
+    d_in = dev.upload(x)
+    d_buf = dev.alloc(out_bytes + 2 * GUARD)
+    fill = np.full(out_bytes + 2 * GUARD, 0xAB, dtype=np.uint8)
+    dev.h2d(d_buf, fill)
+    dev.sync()
+    plan.launch(d_in, d_buf + GUARD, batch)
+    got = dev.download(d_buf, out_bytes + 2 * GUARD, np.uint8)
+    assert (got[:GUARD] == 0xAB).all(), "wrote before the output"
+    assert (got[GUARD + out_bytes:] == 0xAB).all(), "wrote past the output"
+    dev.free(d_in)
+    dev.free(d_buf)
+    plan.close()
+
+
+def test_strip_does_not_write_outside_the_output(dev):
+    for c, w, h in ((3, 642, 480), (1, 1918, 7), (3, 5, 3)):
+        row, pitch = c * w, (c * w + 3) // 4 * 4
+        rng = np.random.default_rng(w)
+        src = rng.integers(0, 256, pitch * (h - 1) + row, dtype=np.uint8)     # last row unpadded
+        d_src = dev.upload(src)
+        d_buf = dev.alloc(row * h + 1024)
+        dev.h2d(d_buf, np.full(row * h + 1024, 0xAB, dtype=np.uint8))
+        dev.sync()
+        dev.strip(d_src, d_buf + 512, row, pitch, h)
+        got = dev.download(d_buf, row * h + 1024, np.uint8)
+        assert (got[:512] == 0xAB).all() and (got[512 + row * h:] == 0xAB).all()
+        want = np.concatenate([src[r * pitch:r * pitch + row] for r in range(h)])
+        assert bits_equal(got[512:512 + row * h], want)
+        dev.free(d_src)
+        dev.free(d_buf)
