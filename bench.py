@@ -44,6 +44,7 @@ ORACLE_OPS = [("typecast", "float32"), ("add", -123.675, 0), ("add", -116.28, 1)
               ("add", -103.53, 2), ("div", 58.395, 0), ("div", 57.12, 1), ("div", 57.375, 2)]
 WORKLOAD = "3:1920:1080:32 uint8 -> float32, arithmetic " + OPTION
 ALGO_BYTES_PER_ELEM = 5           # sizeof(u8) + sizeof(f32), SURVEY.md 8d
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 938.4e6   # measured once with ncu, see profiles/
 METRIC = "tensor_transform_1080p_frames_per_sec"
 UNIT = "frames/s"
 
@@ -119,6 +120,11 @@ def cpu_checker():
     if O.ref_available():
         return O.ref(), "reference"
     return O.port(), "port"
+
+
+def cpu_checker_port():
+    from oracle import oracle as O
+    return O.port()
 
 
 def cpu_run_frames(checker, frames, n_threads):
@@ -209,14 +215,17 @@ def time_launches(dev, fn, steps, warmup):
     return ms
 
 
-def extra_kernels(dev, peak):
-    """Device-resident GB/s of the other modes at their BASELINE configs (informational)."""
+def extra_kernels(dev, peak, with_cpu=True):
+    """Device-resident GB/s of the other modes at their BASELINE configs, each with the
+    reference CPU function timed beside it on ONE frame, one host thread (informational)."""
     out = {}
     rng = np.random.default_rng(3)
+    checker = cpu_checker()[0] if with_cpu else None
 
-    def run(name, mode, option, itype, dim, batch, bytes_per_elem, make):
+    def run(name, mode, option, itype, dim, batch, bytes_per_elem, make, cpu=None):
         plan = dev.plan(mode, option, itype, dim)
-        n = int(np.prod(dim)) * batch
+        frame_n = int(np.prod(dim))
+        n = frame_n * batch
         host = make(n)
         d_in = dev.upload(host)
         d_out = dev.alloc(plan.out_size * batch)
@@ -227,21 +236,62 @@ def extra_kernels(dev, peak):
         dev.free(d_in)
         dev.free(d_out)
         plan.close()
+        if cpu is not None and checker is not None:
+            # bound the CPU sample to one 1080p-sized frame (the reference takes 0.06-0.4 s for it)
+            sample = min(frame_n, FRAME_ELEMS)
+            sdim = dim if sample == frame_n else [C, W, H, 1]
+            xs = host[:sample]
+            t0 = time.perf_counter()
+            cpu(checker, xs, sdim)
+            dt = time.perf_counter() - t0
+            out[name]["cpu_reference_1_thread_GB/s"] = sample * bytes_per_elem / dt / 1e9
+            out[name]["cpu_sample_elements"] = sample
 
     f32 = lambda n: rng.standard_normal(n, dtype=np.float32)
     u8 = lambda n: rng.integers(0, 256, n, dtype=np.uint8)
-    run("typecast_u8_f32_1080p_b32", "typecast", "float32", "uint8", DIM, B, 5, u8)
+    scalar_ops = [("typecast", "float32"), ("add", -127.5), ("div", 127.5)]
+    run("typecast_u8_f32_1080p_b32", "typecast", "float32", "uint8", DIM, B, 5, u8,
+        lambda c, x, d: c.typecast(x, "float32"))
     run("arith_scalar_u8_f32_1080p_b32", "arithmetic", "typecast:float32,add:-127.5,div:127.5",
-        "uint8", DIM, B, 5, u8)
-    run("transpose_hwc_chw_4k_f32", "transpose", "1:2:0:3", "float32", [3, 3840, 2160, 1], 1, 8, f32)
+        "uint8", DIM, B, 5, u8, lambda c, x, d: c.arithmetic(x, d, scalar_ops))
+    # configs[0]: MobileNet pre-processing, 224x224 RGB, 256 frames per launch
+    run("arith_mobilenet_224_b256", "arithmetic", "typecast:float32,add:-127.5,div:127.5",
+        "uint8", [3, 224, 224, 1], 256, 5, u8, lambda c, x, d: c.arithmetic(x, d, scalar_ops))
+    run("transpose_hwc_chw_4k_f32", "transpose", "1:2:0:3", "float32", [3, 3840, 2160, 1], 1, 8, f32,
+        lambda c, x, d: c.transpose(x, d, (1, 2, 0, 3)))
     run("transpose_hwc_chw_4k_f32_b8", "transpose", "1:2:0:3", "float32", [3, 3840, 2160, 1], 8, 8, f32)
-    run("dimchg_0_2_4k_f32", "dimchg", "0:2", "float32", [3, 3840, 2160, 1], 1, 8, f32)
-    run("clamp_f32_1080p_b64", "clamp", "-33.3:77.7", "float32", DIM, 64, 8, f32)
-    run("stand_default_f32_1080p_b64_per_frame", "stand", "default", "float32", DIM, 64, 8, f32)
+    run("transpose_2_0_1_4k_f32", "transpose", "2:0:1:3", "float32", [3, 3840, 2160, 1], 1, 8, f32,
+        lambda c, x, d: c.transpose(x, d, (2, 0, 1, 3)))
+    run("transpose_1_0_2_4k_f32", "transpose", "1:0:2:3", "float32", [3, 3840, 2160, 1], 1, 8, f32)
+    run("transpose_0_2_1_4k_f32", "transpose", "0:2:1:3", "float32", [3, 3840, 2160, 1], 1, 8, f32)
+    run("transpose_2_1_0_4k_f32", "transpose", "2:1:0:3", "float32", [3, 3840, 2160, 1], 1, 8, f32)
+    run("dimchg_0_2_4k_f32", "dimchg", "0:2", "float32", [3, 3840, 2160, 1], 1, 8, f32,
+        lambda c, x, d: c.dimchg(x, d, 0, 2))
+    run("clamp_f32_1080p_b64", "clamp", "-33.3:77.7", "float32", DIM, 64, 8, f32,
+        lambda c, x, d: c.clamp(x, -33.3, 77.7))
+    run("stand_default_f32_1080p_b64_per_frame", "stand", "default", "float32", DIM, 64, 8, f32,
+        lambda c, x, d: c.stand(x, d, "default"))
     run("stand_dc_perch_f32_1080p_b64_per_frame", "stand", "dc-average,per-channel:true",
-        "float32", DIM, 64, 8, f32)
+        "float32", DIM, 64, 8, f32, lambda c, x, d: c.stand(x, d, "dc-average", None, True))
     run("stand_default_f32_1080p_x64_one_tensor", "stand", "default", "float32",
         [3, 1920, 1080, 64], 1, 8, f32)
+    # converter stride strip (K8): 1918x1080 RGB frames, rows padded to a multiple of 4 bytes
+    w = 1918
+    row, pitch, rows = 3 * w, (3 * w + 3) // 4 * 4, 1080 * 32
+    src = u8(pitch * rows)
+    d_src = dev.upload(src)
+    d_dst = dev.alloc(row * rows)
+    ms = time_launches(dev, lambda: dev.strip(d_src, d_dst, row, pitch, rows), 10, 3) / 10
+    gbs = 2 * row * rows / (ms * 1e-3) / 1e9
+    out["stride_strip_1918x1080_rgb_b32"] = {"ms": ms, "GB/s": gbs, "frac_of_measured_peak": gbs / peak,
+                                             "launches": 1}
+    if checker is not None:
+        t0 = time.perf_counter()
+        cpu_checker_port().stride_strip(src[:pitch * 1080], 3, w, 1080)
+        dt = time.perf_counter() - t0
+        out["stride_strip_1918x1080_rgb_b32"]["cpu_reference_1_thread_GB/s"] = 2 * row * 1080 / dt / 1e9
+    dev.free(d_src)
+    dev.free(d_dst)
     return out
 
 
@@ -422,7 +472,7 @@ def run_b200(args):
                 dev.free(d_in)
                 dev.free(d_out)
                 d_in = d_out = None
-                extras = extra_kernels(dev, peak)
+                extras = extra_kernels(dev, peak, with_cpu=not args.no_cpu_baseline)
                 extras["chain_8_streams_1080p_converter_typecast_arith_transpose"] = \
                     multi_stream_chain(local_rank)
 
@@ -448,7 +498,9 @@ def run_b200(args):
             "gpu_launches_detail": {"device_resident": launches, "e2e": e2e_launches},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8TBs": achieved / 8000.0,
-                         "traffic": None, "peak_source": peak_src,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
+                         # (profiles/r1_lut_chain_u8_f32_summary.md): 199.1 MB + 739.3 MB
+                         "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH, "peak_source": peak_src,
                          "kernel": "lut_chain_kernel<uint8,float,false,4> (k_chain.cuh)",
                          "algorithmic_bytes_per_launch": algo_bytes},
             "cpu_baseline": cpu,

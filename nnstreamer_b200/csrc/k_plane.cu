@@ -302,7 +302,7 @@ launch_plane_t (const PlaneDev &p, const void *in, void *out, const LaunchCfg &c
       return (int) e;
     resident = resident_blocks_per_sm (plane_kernel<C, ES, TO_PLANAR>, PLANE_THREADS, Gm::SMEM);
   }
-  uint64_t grid = (uint64_t) cfg.sm_count * resident;
+  uint64_t grid = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : resident);
   if (grid > p.n_tiles)
     grid = p.n_tiles;
   if (grid == 0)
