@@ -263,6 +263,10 @@ NNSB_API int nnsb_plan_launch_elems (nnsb_plan * plan, const void *d_in, void *d
     uint64_t first_elem, uint64_t n_elems, nnsb_stream * s);
 /* number of kernels the last nnsb_plan_launch on this plan enqueued */
 NNSB_API int nnsb_plan_last_launch_count (const nnsb_plan * plan);
+/* One line naming the kernel path the plan compiled to (e.g. "permute: vector table, box
+ * 64x64, swizzle 6"), for logs and tests.  Returns the string length or NNSB_EINVAL.  No
+ * reference counterpart (the reference has a single code path per mode). */
+NNSB_API int nnsb_plan_describe (const nnsb_plan * plan, char *buf, size_t buflen);
 /* stand only: copy the per-tensor statistics of the last launch (mean[, std]) to host */
 NNSB_API int nnsb_plan_stand_stats (nnsb_plan * plan, nnsb_stream * s, uint32_t batch,
     double *mean_out, double *std_out, size_t capacity);

@@ -133,6 +133,7 @@ _PROTOS = {
     "nnsb_plan_chunk_granule": (C.c_uint64, [_VP]),
     "nnsb_plan_launch_elems": (C.c_int, [_VP, _VP, _VP, C.c_uint64, C.c_uint64, _VP]),
     "nnsb_plan_last_launch_count": (C.c_int, [_VP]),
+    "nnsb_plan_describe": (C.c_int, [_VP, C.c_char_p, C.c_size_t]),
     "nnsb_plan_stand_stats": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(C.c_double),
                                         C.POINTER(C.c_double), C.c_size_t]),
     "nnsb_strip_launch": (C.c_int, [_VP, _VP, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),

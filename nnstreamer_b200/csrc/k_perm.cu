@@ -29,6 +29,7 @@
 
 #include "nnsb_device.cuh"
 #include "nnsb_kernels.h"
+#include "k_perm_common.cuh"
 
 namespace nnsb {
 
@@ -36,31 +37,6 @@ constexpr int PERM_THREADS = 256;
 constexpr int PERM_EPT = 8;             /* elements per thread per tile */
 constexpr int PERM_TILE_MAX = PERM_THREADS * PERM_EPT;   /* 2048 elements */
 constexpr int PERM_DIMS = NNSB_PERM_MAX_RANK + 1;        /* rank 8 + batch */
-
-/* exact q / d for q < 2^31 with one 64-bit multiply: m = ceil (2^(31+s) / d), s = ceil (log2 d) */
-struct FastDiv
-{
-  uint32_t d, m, s;
-};
-
-static FastDiv
-make_fastdiv (uint32_t d)
-{
-  FastDiv f;
-  f.d = d ? d : 1;
-  f.s = 0;
-  while ((1ull << f.s) < f.d)
-    f.s++;
-  f.m = (uint32_t) (((1ull << (31 + f.s)) + f.d - 1) / f.d);
-  return f;
-}
-
-__device__ __forceinline__ void
-divmod (uint32_t q, const FastDiv &f, uint32_t &quot, uint32_t &rem)
-{
-  quot = (uint32_t) (((uint64_t) q * f.m) >> (31 + f.s));
-  rem = q - quot * f.d;
-}
 
 struct PermDev
 {
@@ -364,7 +340,8 @@ launch_permute_t (const PermDev &p, const void *in, void *out, const LaunchCfg &
 }
 
 int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_elems,
-    uint32_t batch, const LaunchCfg &cfg, cudaStream_t stream)
+    uint32_t batch, const LaunchCfg &cfg, cudaStream_t stream, const PermVecPlan *vec,
+    const void *d_table)
 {
   if (batch == 0 || frame_elems == 0)
     return 0;
@@ -437,7 +414,14 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
     }
   }
 
-  /* 4. the box: >= 32-element runs on both sides, then grown to ~2048 elements */
+  /* 4. the table-driven 16-byte vector kernel (k_perm_vec.cu), when the plan qualified */
+  if (vec && vec->valid) {
+    const int r = launch_permute_vec (*vec, d_table, in, out, frame_elems, batch, cfg, stream);
+    if (r != -1)
+      return r;
+  }
+
+  /* 5. the box: >= 32-element runs on both sides, then grown to ~2048 elements */
   PermDev p;
   memset (&p, 0, sizeof (p));
   p.n = n;

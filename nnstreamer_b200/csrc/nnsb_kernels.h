@@ -68,8 +68,36 @@ struct PermDesc
   uint64_t in_stride[NNSB_PERM_MAX_RANK];
   int es;                       /* element bytes: 1,2,4,8,16 */
 };
+/* K3/K4 vector path (k_perm_vec.cu): 16-byte accesses on both sides, driven by a table that
+ * the host builds once per plan (per-vector global offsets and swizzled shared-memory slots
+ * for one box) and the plan keeps in device memory.  4- and 8-byte elements.
+ *   perm_vec_build : 0 = eligible, *host_table is malloc()ed (table_bytes long); -1 = not
+ *   launch_permute_vec : -1 when this call does not qualify (unaligned pointers, too many
+ *                        tiles), else the launch status */
+struct PermVecPlan
+{
+  int valid;
+  int es;
+  int n;                                        /* canonical dims, output order, no batch */
+  uint32_t size[NNSB_PERM_MAX_RANK];
+  uint32_t tile[NNSB_PERM_MAX_RANK];            /* box extent per dim */
+  uint64_t in_stride[NNSB_PERM_MAX_RANK];       /* elements */
+  uint64_t out_stride[NNSB_PERM_MAX_RANK];
+  int box_slot[NNSB_PERM_MAX_RANK];             /* field of the packed coordinates, -1 = extent 1 */
+  uint64_t limits_init;                         /* packed limits of the unused fields (1 each) */
+  uint32_t n_vec;                               /* 16-byte vectors per box */
+  uint64_t tiles_per_frame;
+  size_t table_bytes;
+  int swizzle_shift;                            /* chosen shared-memory swizzle (-1 = none) */
+};
+int perm_vec_build (const PermDesc & d, size_t frame_elems, PermVecPlan * plan, void **host_table);
+int launch_permute_vec (const PermVecPlan & plan, const void *d_table, const void *in, void *out,
+    size_t frame_elems, uint32_t batch, const LaunchCfg & cfg, cudaStream_t stream);
+
+/* vec/d_table: optional vector plan, tried after the interleaved<->planar fast path */
 int launch_permute (const PermDesc & d, const void *in, void *out, size_t frame_elems,
-    uint32_t batch, const LaunchCfg & cfg, cudaStream_t stream);
+    uint32_t batch, const LaunchCfg & cfg, cudaStream_t stream,
+    const PermVecPlan * vec = nullptr, const void *d_table = nullptr);
 
 /* K3 fast path (k_plane.cu): interleaved <-> planar through TMA bulk copies.
  * Returns -1 when the problem does not qualify, else the launch status. */

@@ -12,6 +12,7 @@
  *
  * No CPU fallback exists: without a usable CUDA device every call fails with NNSB_ECUDA.
  */
+#include <cstdio>
 #include <cuda_runtime.h>
 
 #include <cstdlib>
@@ -67,6 +68,8 @@ struct nnsb_plan
   nnsb_cell *d_table;
   /* transpose / dimchg */
   PermDesc perm;
+  PermVecPlan perm_vec;         /* 16-byte vector path, when the box qualifies */
+  void *d_perm_table;
   /* stand */
   uint32_t stand_nch;
   double *d_scratch;
@@ -528,6 +531,8 @@ nnsb_plan_destroy (nnsb_plan * plan)
     return NNSB_OK;
   if (plan->d_table)
     nnsb_dev_free (plan->ctx, plan->d_table);
+  if (plan->d_perm_table)
+    nnsb_dev_free (plan->ctx, plan->d_perm_table);
   if (plan->d_scratch)
     nnsb_dev_free (plan->ctx, plan->d_scratch);
   if (plan->d_stats)
@@ -664,6 +669,27 @@ nnsb_plan_create (nnsb_ctx * ctx, const nnsb_option * opt, const nnsb_tensor_inf
       nnsb_plan_destroy (plan);
       return nnsb_set_error (NNSB_ENOTSUP, "Not supported tensor transform mode");
   }
+  if (opt->mode == NNSB_MODE_TRANSPOSE || opt->mode == NNSB_MODE_DIMCHG) {
+    /* per-box table of the vector kernel: built and verified on the host, kept in HBM */
+    void *host_table = nullptr;
+    if (perm_vec_build (plan->perm, plan->frame_elems, &plan->perm_vec, &host_table) == 0) {
+      void *d = nullptr;
+      r = nnsb_dev_alloc (ctx, plan->perm_vec.table_bytes, &d);
+      if (r == NNSB_OK) {
+        plan->d_perm_table = d;
+        cudaError_t e = cudaMemcpy (d, host_table, plan->perm_vec.table_bytes,
+            cudaMemcpyHostToDevice);
+        if (e != cudaSuccess)
+          r = nnsb_set_error (NNSB_ECUDA, "cudaMemcpy (permute table) failed: %s",
+              cudaGetErrorString (e));
+      }
+      free (host_table);
+      if (r) {
+        nnsb_plan_destroy (plan);
+        return r;
+      }
+    }
+  }
   *out = plan;
   return NNSB_OK;
 }
@@ -693,6 +719,45 @@ extern "C" int
 nnsb_plan_last_launch_count (const nnsb_plan * plan)
 {
   return plan ? plan->last_launches : NNSB_EINVAL;
+}
+
+extern "C" int
+nnsb_plan_describe (const nnsb_plan * plan, char *buf, size_t buflen)
+{
+  if (!plan || !buf || buflen == 0)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_describe: null argument");
+  int len = 0;
+  switch (plan->opt.mode) {
+    case NNSB_MODE_TRANSPOSE:
+    case NNSB_MODE_DIMCHG:
+      if (plan->perm_vec.valid) {
+        char box[128];
+        int o = 0;
+        for (int i = 0; i < plan->perm_vec.n && o < (int) sizeof (box) - 12; i++)
+          o += snprintf (box + o, sizeof (box) - o, "%s%u", i ? "x" : "", plan->perm_vec.tile[i]);
+        len = snprintf (buf, buflen, "permute: vector table, box %s, %u vectors, swizzle %d", box,
+            plan->perm_vec.n_vec, plan->perm_vec.swizzle_shift);
+      } else {
+        len = snprintf (buf, buflen, "permute: scalar box kernel");
+      }
+      break;
+    case NNSB_MODE_TYPECAST:
+    case NNSB_MODE_ARITHMETIC:
+      len = snprintf (buf, buflen, "chain: %d position(s), %d channel(s)", (int) plan->chain.desc.n_pos,
+          (int) plan->chain.desc.nch);
+      break;
+    case NNSB_MODE_STAND:
+      len = snprintf (buf, buflen, "stand: %u channel(s)", plan->stand_nch);
+      break;
+    case NNSB_MODE_CLAMP:
+      len = snprintf (buf, buflen, "clamp");
+      break;
+    default:
+      return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_describe: unknown mode");
+  }
+  if (len < 0 || (size_t) len >= buflen)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_describe: buffer too small");
+  return len;
 }
 
 static int
@@ -747,7 +812,8 @@ nnsb_plan_launch (nnsb_plan * plan, const void *d_in, void *d_out, uint32_t batc
       break;
     case NNSB_MODE_TRANSPOSE:
     case NNSB_MODE_DIMCHG:
-      err = launch_permute (plan->perm, d_in, d_out, plan->frame_elems, batch, cfg, s->s);
+      err = launch_permute (plan->perm, d_in, d_out, plan->frame_elems, batch, cfg, s->s,
+          &plan->perm_vec, plan->d_perm_table);
       plan->last_launches = 1;
       break;
     case NNSB_MODE_STAND:

@@ -145,6 +145,14 @@ class Plan:
     def last_launch_count(self):
         return self._lib.nnsb_plan_last_launch_count(self.handle)
 
+    def describe(self):
+        """One line naming the kernel path the plan compiled to."""
+        buf = C.create_string_buffer(256)
+        n = self._lib.nnsb_plan_describe(self.handle, buf, len(buf))
+        if n < 0:
+            L.check(n)
+        return buf.value.decode()
+
     def stand_stats(self, batch, nch):
         n = int(batch) * int(nch)
         mean = (C.c_double * n)()

@@ -34,6 +34,7 @@ def main():
         x = rng.integers(max(info.min, -1000), min(info.max, 1000), n, endpoint=True).astype(dt)
     with Device(0) as dev:
         plan = dev.plan(a.mode, a.option, a.in_type, dim)
+        print("plan:", plan.describe())
         d_in = dev.upload(x)
         d_out = dev.alloc(plan.out_size * a.batch)
         e0, e1 = dev.event(), dev.event()

@@ -274,6 +274,56 @@ def test_transpose_video_shapes_tma_path(dev, port, dtype, channels):
         assert bits_equal(got2, want)
 
 
+VEC_CASES = [
+    # dtype, dim, batch: every box edge case of the table-driven 16-byte vector kernel
+    ("float32", [3, 128, 96, 1], 1),      # whole boxes only
+    ("float32", [3, 132, 100, 1], 2),     # partial boxes on both sides, batch
+    ("float32", [4, 36, 20, 1], 3),       # tensor smaller than one full box
+    ("float32", [8, 12, 52, 1], 1),
+    ("float64", [3, 130, 98, 1], 2),      # 2-element vectors
+    ("int64", [6, 34, 18, 1], 1),
+    ("int32", [64, 64, 64, 1], 1),
+    ("uint32", [5, 7, 9, 1], 4),          # odd sizes: must fall back to the scalar kernel
+]
+
+
+@pytest.mark.parametrize("order", [(0, 2, 1, 3), (1, 0, 2, 3), (2, 0, 1, 3), (2, 1, 0, 3),
+                                   (1, 2, 0, 3)])
+@pytest.mark.parametrize("case", VEC_CASES, ids=lambda c: "%s-%s-b%d" % (c[0], "x".join(map(str, c[1])), c[2]))
+def test_transpose_vector_path(dev, port, order, case):
+    """k_perm_vec.cu against the oracle (gsttensor_transform.c:1417-1500), bit-exact; the plan
+    must report the vector table for the aligned shapes and the scalar kernel for the odd one."""
+    dtype, dim, batch = case
+    n = int(np.prod(dim))
+    x = rand_small(dtype, n * batch, seed=n + batch)
+    opt = "%d:%d:%d:3" % order[:3]
+    plan = dev.plan("transpose", opt, dtype, dim)
+    desc = plan.describe()
+    got = plan.run_host(x, batch=batch)
+    plan.close()
+    want = np.concatenate([port.transpose(x[i * n:(i + 1) * n], dim, order) for i in range(batch)])
+    assert bits_equal(got, want), "%s %s %s [%s]: %s" % (dtype, dim, opt, desc,
+                                                          first_mismatch(got, want))
+    if dim == [5, 7, 9, 1]:
+        assert "scalar" in desc, desc
+    elif dim in ([3, 128, 96, 1], [64, 64, 64, 1], [3, 132, 100, 1]):
+        assert "vector table" in desc, desc
+
+
+def test_dimchg_vector_path(dev, port):
+    for dtype, dim, f, t in (("float32", [4, 20, 36, 8], 0, 3), ("float32", [16, 12, 40, 1], 1, 2),
+                             ("float64", [6, 10, 34, 2], 0, 2), ("float32", [32, 3, 50, 4], 0, 1)):
+        n = int(np.prod(dim))
+        x = rand_small(dtype, n, seed=n)
+        plan = dev.plan("dimchg", "%d:%d" % (f, t), dtype, dim)
+        desc = plan.describe()
+        got = plan.run_host(x)
+        plan.close()
+        want = port.dimchg(x, dim, f, t)
+        assert bits_equal(got, want), "%s %s %d:%d [%s] %s" % (dtype, dim, f, t, desc,
+                                                                first_mismatch(got, want))
+
+
 @pytest.mark.parametrize("from_to", [(0, 1), (0, 2), (0, 3), (0, 4), (1, 2), (1, 3), (2, 3),
                                      (2, 2), (0, 7)])
 def test_dimchg(dev, port, from_to):
