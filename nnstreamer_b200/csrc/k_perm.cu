@@ -345,37 +345,15 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
 {
   if (batch == 0 || frame_elems == 0)
     return 0;
-  /* 1. collect (size, in_stride, out_stride), drop extent-1 dims, append the batch */
-  struct Dim { uint64_t size, in, out; };
-  Dim dims[PERM_DIMS];
-  int n = 0;
-  uint64_t ostride = 1;
-  for (int i = 0; i < d0.rank; i++) {
-    if (d0.size[i] != 1) {
-      dims[n].size = d0.size[i];
-      dims[n].in = d0.in_stride[i];
-      dims[n].out = ostride;
-      n++;
-    }
-    ostride *= d0.size[i];
-  }
-  if (batch > 1) {
-    dims[n].size = batch;
-    dims[n].in = frame_elems;
-    dims[n].out = frame_elems;
-    n++;
-  }
-  /* 2. merge neighbours that are adjacent on both sides */
-  int m = 0;
-  for (int i = 0; i < n; i++) {
-    if (m > 0 && dims[m - 1].in * dims[m - 1].size == dims[i].in
-        && dims[m - 1].out * dims[m - 1].size == dims[i].out) {
-      dims[m - 1].size *= dims[i].size;
-    } else {
-      dims[m++] = dims[i];
-    }
-  }
-  n = m;
+  /* 1. canonical form: extent-1 dims dropped, batch appended, neighbours merged, an innermost
+   *    block common to both sides folded into the element (RGBA bytes move as one word) */
+  CDim dims[PERM_DIMS];
+  int es = d0.es;
+  uint64_t alignment = (uint64_t) (uintptr_t) in | (uint64_t) (uintptr_t) out;
+  if (batch > 1)
+    alignment |= (uint64_t) frame_elems * d0.es;
+  int n = canonicalise_perm (d0.size, d0.in_stride, d0.rank, frame_elems, batch, 8, alignment, dims,
+      &es);
   const size_t total = (size_t) frame_elems * batch;
   if (n == 0 || (n == 1 && dims[0].in == 1))
     return launch_copy (in, out, total * d0.es, cfg, stream);
@@ -383,7 +361,15 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
     if (dims[i].size > 0xffffffffull)
       return (int) cudaErrorInvalidValue;
 
-  /* 3. video-shaped [P][C] <-> [C][P] (2..4 channels): the TMA pipeline (k_plane.cu) */
+  /* 3. 4-byte and wider elements: the table-driven 16-byte vector kernel (k_perm_vec.cu), when
+   *    the plan qualified (measured faster than the TMA pipeline below at these widths) */
+  if (vec && vec->valid) {
+    const int r = launch_permute_vec (*vec, d_table, in, out, frame_elems, batch, cfg, stream);
+    if (r != -1)
+      return r;
+  }
+
+  /* 4. video-shaped [P][C] <-> [C][P] (2..4 channels): the TMA pipeline (k_plane.cu) */
   if (!getenv ("NNSB_NO_PLANE")) {
     /* find X (out stride 1) and Y (in stride 1); everything else is an outer dim */
     int ix = -1, iy = -1;
@@ -404,21 +390,14 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
         }
       int r = -1;
       if (dims[iy].size >= 2 && dims[iy].size <= 4 && dims[ix].in == dims[iy].size)
-        r = launch_plane (true, (int) dims[iy].size, d0.es, dims[ix].size, dims[iy].out, no, o_size,
+        r = launch_plane (true, (int) dims[iy].size, es, dims[ix].size, dims[iy].out, no, o_size,
             o_in, o_out, in, out, cfg, stream);
       else if (dims[ix].size >= 2 && dims[ix].size <= 4 && dims[iy].out == dims[ix].size)
-        r = launch_plane (false, (int) dims[ix].size, d0.es, dims[iy].size, dims[ix].in, no, o_size,
+        r = launch_plane (false, (int) dims[ix].size, es, dims[iy].size, dims[ix].in, no, o_size,
             o_out, o_in, in, out, cfg, stream);
       if (r != -1)
         return r;
     }
-  }
-
-  /* 4. the table-driven 16-byte vector kernel (k_perm_vec.cu), when the plan qualified */
-  if (vec && vec->valid) {
-    const int r = launch_permute_vec (*vec, d_table, in, out, frame_elems, batch, cfg, stream);
-    if (r != -1)
-      return r;
   }
 
   /* 5. the box: >= 32-element runs on both sides, then grown to ~2048 elements */
@@ -516,7 +495,7 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
   p.n_tiles = (uint32_t) tiles;
 
   const bool sync_only = getenv ("NNSB_PERM_SYNC") != nullptr;
-  switch (d0.es) {
+  switch (es) {
     case 1: return launch_permute_t<uint8_t, false> (p, in, out, cfg, stream);
     case 2: return launch_permute_t<uint16_t, false> (p, in, out, cfg, stream);
     case 4: return sync_only ? launch_permute_t<uint32_t, false> (p, in, out, cfg, stream)

@@ -33,5 +33,71 @@ divmod (uint32_t q, const FastDiv &f, uint32_t &quot, uint32_t &rem)
   rem = q - quot * f.d;
 }
 
+/* One dimension of a canonical permutation problem: extent, input stride, output stride
+ * (strides in elements; the output is dense, dims are listed in output order). */
+struct CDim
+{
+  uint64_t size, in, out;
+};
+
+/* Canonical form of a permutation: extent-1 dims dropped, the batch appended (batch > 1),
+ * dims that are adjacent on both sides merged.  If the innermost dim is the same on both
+ * sides (a pixel / a channel group that moves as a block), a power-of-two part of it is folded
+ * into the element: es grows up to max_es as far as `alignment` (OR of the base addresses and
+ * the frame size in bytes) allows, and all strides shrink accordingly.
+ * Returns the dim count; *es_io is updated. */
+static inline int
+canonicalise_perm (const uint32_t *size, const uint64_t *in_stride, int rank, uint64_t frame_elems,
+    uint32_t batch, int max_es, uint64_t alignment, CDim *dims, int *es_io)
+{
+  int n = 0;
+  uint64_t ostride = 1;
+  for (int i = 0; i < rank; i++) {
+    if (size[i] != 1) {
+      dims[n].size = size[i];
+      dims[n].in = in_stride[i];
+      dims[n].out = ostride;
+      n++;
+    }
+    ostride *= size[i];
+  }
+  if (batch > 1) {
+    dims[n].size = batch;
+    dims[n].in = frame_elems;
+    dims[n].out = frame_elems;
+    n++;
+  }
+  int m = 0;
+  for (int i = 0; i < n; i++) {
+    if (m > 0 && dims[m - 1].in * dims[m - 1].size == dims[i].in
+        && dims[m - 1].out * dims[m - 1].size == dims[i].out)
+      dims[m - 1].size *= dims[i].size;
+    else
+      dims[m++] = dims[i];
+  }
+  n = m;
+  if (n >= 2 && dims[0].in == 1 && dims[0].out == 1) {
+    int es = *es_io;
+    uint64_t f = 1;
+    while (dims[0].size % (2 * f) == 0 && (int) (2 * f) * es <= max_es
+        && alignment % (2 * f * es) == 0)
+      f *= 2;
+    if (f > 1) {
+      dims[0].size /= f;
+      for (int i = 1; i < n; i++) {
+        dims[i].in /= f;
+        dims[i].out /= f;
+      }
+      *es_io = es * (int) f;
+      if (dims[0].size == 1) {
+        for (int i = 1; i < n; i++)
+          dims[i - 1] = dims[i];
+        n--;
+      }
+    }
+  }
+  return n;
+}
+
 }  // namespace nnsb
 #endif

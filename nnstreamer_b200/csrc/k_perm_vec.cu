@@ -1,6 +1,7 @@
 /*
  * k_perm_vec.cu -- K3/K4 vector path: rank-N permutation copy with 16-byte global accesses on
- * both sides, for 4- and 8-byte elements.
+ * both sides, for 4-, 8- and 16-byte elements (an innermost block that is common to both
+ * sides -- RGBA bytes, a float4 -- is folded into the element first).
  *
  * Same job as permute_kernel (k_perm.cu): the per-element nns_memcpy nest of
  * gst_tensor_transform_transpose (gsttensor_transform.c:1417-1500) and the block memcpy nest
@@ -70,6 +71,27 @@ cp_async_16 (uint32_t smem_dst, const void *gmem_src)
   asm volatile ("cp.async.cg.shared.global [%0], [%1], 16;" :: "r" (smem_dst), "l" (gmem_src) : "memory");
 }
 
+__device__ __forceinline__ void
+cp_async_16_if (bool on, uint32_t smem_dst, const void *gmem_src)
+{
+  asm volatile ("{\n"
+      ".reg .pred p;\n"
+      "setp.ne.u32 p, %2, 0;\n"
+      "@p cp.async.cg.shared.global [%0], [%1], 16;\n"
+      "}\n" :: "r" (smem_dst), "l" (gmem_src), "r" ((uint32_t) on) : "memory");
+}
+
+__device__ __forceinline__ void
+st_stream_16_if (bool on, void *dst, const uint32_t *w)
+{
+  asm volatile ("{\n"
+      ".reg .pred p;\n"
+      "setp.ne.u32 p, %5, 0;\n"
+      "@p st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};\n"
+      "}\n" :: "l" (dst), "r" (w[0]), "r" (w[1]), "r" (w[2]), "r" (w[3]), "r" ((uint32_t) on)
+      : "memory");
+}
+
 /* all four 16-bit fields of c below the matching field of lim */
 __device__ __forceinline__ bool
 inside4 (uint64_t c, uint64_t lim)
@@ -88,11 +110,14 @@ gather (uint32_t stage_addr, const uint32_t *slot, uint32_t *w)
 #pragma unroll
     for (int e = 0; e < 4; e++)
       asm volatile ("ld.shared.u32 %0, [%1];" : "=r" (w[e]) : "r" (stage_addr + slot[e]));
-  } else {
+  } else if constexpr (ES == 8) {
 #pragma unroll
     for (int e = 0; e < 2; e++)
       asm volatile ("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r" (w[2 * e]), "=r" (w[2 * e + 1])
           : "r" (stage_addr + slot[e]));
+  } else {
+    asm volatile ("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r" (w[0]), "=r" (w[1]),
+        "=r" (w[2]), "=r" (w[3]) : "r" (stage_addr + slot[0]));
   }
 }
 
@@ -124,10 +149,12 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
         st_slot[j][1] = s.x >> 16;
         st_slot[j][2] = s.y & 0xffffu;
         st_slot[j][3] = s.y >> 16;
-      } else {
+      } else if constexpr (VE == 2) {
         const uint32_t s = *reinterpret_cast<const uint32_t *> (t_st_slot + (size_t) i * 2);
         st_slot[j][0] = s & 0xffffu;
         st_slot[j][1] = s >> 16;
+      } else {
+        st_slot[j][0] = t_st_slot[i];
       }
     }
   }
@@ -171,7 +198,15 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
     ti.full = full ? 1 : 0;
   };
 
-  /* S / NEXT are compile-time ring slots: shared-memory addresses become register + immediate */
+  /* bit j: vector j of this thread exists in the box (always, when the box fills the stage) */
+  uint32_t present = 0;
+#pragma unroll
+  for (int j = 0; j < PV_VPT; j++)
+    present |= (ld_off[j] != PV_INVALID ? 1u : 0u) << j;
+
+  /* stage_off is a compile-time ring slot: shared-memory addresses are register + immediate.
+   * Vectors that are absent, or outside the tensor in an edge box, are predicated off (their
+   * offsets / slots are still valid numbers, so the address arithmetic needs no branch). */
   auto issue = [&] (uint32_t k, uint32_t stage_off) {
     if (k < my_tiles) {
       const TileInfo &ti = info[k % INFO];
@@ -183,14 +218,14 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
       } else if (ti.full) {
 #pragma unroll
         for (int j = 0; j < PV_VPT; j++)
-          if (ld_off[j] != PV_INVALID)
-            cp_async_16 (ld_slot[j] + stage_off, src + ld_off[j]);
+          cp_async_16_if ((present >> j) & 1u, ld_slot[j] + stage_off, src + ld_off[j]);
       } else {
         const uint64_t lim = ti.limits;
 #pragma unroll
         for (int j = 0; j < PV_VPT; j++)
-          if (ld_off[j] != PV_INVALID && inside4 (t_ld_coord[threadIdx.x + j * PV_THREADS], lim))
-            cp_async_16 (ld_slot[j] + stage_off, src + ld_off[j]);
+          cp_async_16_if (((present >> j) & 1u)
+              && inside4 (t_ld_coord[threadIdx.x + j * PV_THREADS], lim),
+              ld_slot[j] + stage_off, src + ld_off[j]);
       }
     }
     asm volatile ("cp.async.commit_group;" ::: "memory");     /* possibly empty: keeps the count */
@@ -199,35 +234,35 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
     const TileInfo &ti = info[k % INFO];
     unsigned char *dst = ti.dst;
     const uint32_t stage_addr = ring_addr + stage_off;
-    if (ti.full && whole) {
-      uint32_t w[PV_VPT][4];
+    uint32_t w[PV_VPT][4];
 #pragma unroll
-      for (int j = 0; j < PV_VPT; j++)
-        gather<ES> (stage_addr, st_slot[j], w[j]);
+    for (int j = 0; j < PV_VPT; j++)
+      gather<ES> (stage_addr, st_slot[j], w[j]);
+    if (ti.full && whole) {
 #pragma unroll
       for (int j = 0; j < PV_VPT; j++)
         st_stream<16> (dst + st_off[j], w[j]);
+    } else if (ti.full) {
+#pragma unroll
+      for (int j = 0; j < PV_VPT; j++)
+        st_stream_16_if ((present >> j) & 1u, dst + st_off[j], w[j]);
     } else {
-      const bool full = ti.full != 0;
       const uint64_t lim = ti.limits;
 #pragma unroll
       for (int j = 0; j < PV_VPT; j++)
-        if (st_off[j] != PV_INVALID
-            && (full || inside4 (t_st_coord[threadIdx.x + j * PV_THREADS], lim))) {
-          uint32_t w[4];
-          gather<ES> (stage_addr, st_slot[j], w);
-          st_stream<16> (dst + st_off[j], w);
-        }
+        st_stream_16_if (((present >> j) & 1u)
+            && inside4 (t_st_coord[threadIdx.x + j * PV_THREADS], lim), dst + st_off[j], w[j]);
     }
   };
-  auto step = [&] (uint32_t k, uint32_t stage_off, uint32_t next_off) {
-    issue (k + PV_STAGES - 1, next_off);
-    asm volatile ("cp.async.wait_group %0;" :: "n" (PV_STAGES - 1) : "memory");
+  /* One barrier per tile: past it, every thread's part of tile k has landed AND every thread
+   * has finished draining tile k-1, whose ring slot the next issue overwrites. */
+  auto step = [&] (uint32_t k, uint32_t stage_off, uint32_t refill_off) {
+    asm volatile ("cp.async.wait_group %0;" :: "n" (PV_STAGES - 2) : "memory");
     __syncthreads ();
     if (threadIdx.x == 0 && k + PV_STAGES < my_tiles)
-      locate (k + PV_STAGES);   /* slot (k + S) % (S + 1): not read before the next barrier */
+      locate (k + PV_STAGES);   /* slot (k - 1) % (S + 1): last read while draining tile k-1 */
+    issue (k + PV_STAGES - 1, refill_off);
     drain (k, stage_off);
-    __syncthreads ();           /* the stage is overwritten by the issue of the next step */
   };
 
   if (threadIdx.x == 0)
@@ -250,37 +285,6 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
 /* host: box selection, table, verification                                               */
 /* ------------------------------------------------------------------------------------- */
 namespace {
-
-struct CDim
-{
-  uint64_t size, in, out;       /* extent, input stride, output stride (elements) */
-};
-
-/* drop extent-1 dims, merge dims adjacent on both sides; returns the dim count */
-int
-canonicalise (const PermDesc &d0, CDim *dims)
-{
-  int n = 0;
-  uint64_t ostride = 1;
-  for (int i = 0; i < d0.rank; i++) {
-    if (d0.size[i] != 1) {
-      dims[n].size = d0.size[i];
-      dims[n].in = d0.in_stride[i];
-      dims[n].out = ostride;
-      n++;
-    }
-    ostride *= d0.size[i];
-  }
-  int m = 0;
-  for (int i = 0; i < n; i++) {
-    if (m > 0 && dims[m - 1].in * dims[m - 1].size == dims[i].in
-        && dims[m - 1].out * dims[m - 1].size == dims[i].out)
-      dims[m - 1].size *= dims[i].size;
-    else
-      dims[m++] = dims[i];
-  }
-  return m;
-}
 
 uint64_t
 gcd_u64 (uint64_t a, uint64_t b)
@@ -325,47 +329,171 @@ ensure_run (const CDim *dims, int n, const int *order, uint64_t run, uint64_t ve
   }
 }
 
-/* wavefronts of the gather (one LDS per element of every output vector) for a swizzle */
+/* shared-memory swizzle of 16-byte chunk q: XOR of its low three bits with bits picked higher
+ * up (s1, s2 < 0 = unused).  With s < 3 the source overlaps the target bits; the builder only
+ * keeps candidates that are permutations of the stage's chunks. */
+struct Swizzle
+{
+  int s1, s2;
+  uint32_t operator () (uint32_t q) const
+  {
+    uint32_t x = 0;
+    if (s1 >= 0)
+      x ^= q >> s1;
+    if (s2 >= 0)
+      x ^= q >> s2;
+    return q ^ (x & 7u);
+  }
+  bool is_permutation () const
+  {
+    bool seen[PV_NVT];
+    memset (seen, 0, sizeof (seen));
+    for (uint32_t q = 0; q < (uint32_t) PV_NVT; q++) {
+      const uint32_t r = (*this) (q);
+      if (r >= (uint32_t) PV_NVT || seen[r])
+        return false;
+      seen[r] = true;
+    }
+    return true;
+  }
+};
+
+/* wavefronts of the gather (one LDS per element of every output vector) under a swizzle:
+ * 32-bit accesses are served a warp at a time over 32 banks, 64/128-bit ones a half/quarter
+ * warp at a time over groups of 2/4 banks */
 uint64_t
-gather_cost (const uint32_t *lin, uint32_t n_vec, int ve, int es, int shift)
+gather_cost (const uint32_t *lin, uint32_t n_vec, int ve, int es, const Swizzle &sw)
 {
   uint64_t cost = 0;
-  const int lanes = es == 8 ? 16 : 32;          /* 64-bit accesses go half a warp at a time */
-  const int banks = es == 8 ? 16 : 32;          /* ... over 16 bank pairs */
-  for (uint32_t base = 0; base < (uint32_t) PV_NVT; base += lanes) {
+  const int lanes = 128 / es, banks = 128 / es;
+  for (uint32_t base = 0; base < n_vec; base += lanes) {
     for (int e = 0; e < ve; e++) {
-      uint32_t words[32];
-      int nw = 0;
-      for (int l = 0; l < lanes; l++) {
-        const uint32_t i = base + l;
-        if (i >= n_vec)
-          continue;
-        const uint32_t li = lin[(size_t) i * ve + e];
-        uint32_t q = li / ve;
-        if (shift >= 0)
-          q ^= (q >> shift) & 7u;
-        words[nw++] = q * ve + li % ve;         /* element-sized word index */
-      }
+      uint32_t words[32][32];
+      int count[32];
+      memset (count, 0, sizeof (count));
       int worst = 0;
-      for (int b = 0; b < banks; b++) {
-        uint32_t seen[32];
-        int ns = 0;
-        for (int k = 0; k < nw; k++)
-          if ((int) (words[k] % banks) == b) {
-            bool dup = false;
-            for (int s = 0; s < ns; s++)
-              dup = dup || seen[s] == words[k];
-            if (!dup)
-              seen[ns++] = words[k];
-          }
-        if (ns > worst)
-          worst = ns;
+      for (int l = 0; l < lanes && base + l < n_vec; l++) {
+        const uint32_t li = lin[(size_t) (base + l) * ve + e];
+        const uint32_t w = sw (li / ve) * ve + li % ve;         /* element-sized word index */
+        const int b = (int) (w % banks);
+        bool dup = false;
+        for (int k = 0; k < count[b]; k++)
+          dup = dup || words[b][k] == w;
+        if (!dup)
+          words[b][count[b]++] = w;
+        if (count[b] > worst)
+          worst = count[b];
       }
       cost += worst;
     }
   }
   return cost;
 }
+
+/* One permutation problem in canonical form, and the checks / table for a candidate box */
+struct Builder
+{
+  CDim dims[PV_DIMS];
+  int n, es;
+  uint64_t VE, TILE_MAX;
+  int in_order[PV_DIMS], out_order[PV_DIMS];
+
+  /* Static conditions + brute-force verification of box T.  With tab != null also fills the
+   * offsets / coordinates of the table and st_lin (load-order index of every output element). */
+  bool check (const uint64_t *T, int *box_slot, unsigned char *tab, uint32_t *st_lin) const
+  {
+    const uint64_t volume = box_volume (T, n);
+    if (volume % VE || volume > TILE_MAX)
+      return false;
+    const uint32_t n_vec = (uint32_t) (volume / VE);
+    uint64_t span_in = 0, span_out = 0, tiles = 1;
+    int n_boxed = 0, slot[PV_DIMS];
+    for (int i = 0; i < n; i++) {
+      /* box origins 16-byte aligned on both sides */
+      if (T[i] < dims[i].size && ((T[i] * dims[i].in * es) % 16 || (T[i] * dims[i].out * es) % 16))
+        return false;
+      span_in += (T[i] - 1) * dims[i].in * es;
+      span_out += (T[i] - 1) * dims[i].out * es;
+      tiles *= (dims[i].size + T[i] - 1) / T[i];
+      slot[i] = -1;
+      if (T[i] > 1) {
+        if (n_boxed == PV_BOXED || T[i] > 0xffff)
+          return false;
+        slot[i] = n_boxed++;
+      }
+    }
+    if (span_in >= (1ull << 32) - 16 || span_out >= (1ull << 32) - 16 || tiles >= (1ull << 31))
+      return false;
+    uint32_t lstride[PV_DIMS];
+    uint32_t ls = 1;
+    for (int k = 0; k < n; k++) {
+      lstride[in_order[k]] = ls;
+      ls *= (uint32_t) T[in_order[k]];
+    }
+    uint64_t rem[PV_DIMS];              /* extent of the last, partial box (0 = none) */
+    for (int i = 0; i < n; i++)
+      rem[i] = dims[i].size % T[i];
+
+    uint32_t *t_ld_off = tab ? (uint32_t *) (tab + PV_T_LD_OFF) : nullptr;
+    uint32_t *t_st_off = tab ? (uint32_t *) (tab + PV_T_ST_OFF) : nullptr;
+    uint64_t *t_ld_coord = tab ? (uint64_t *) (tab + PV_T_LD_COORD) : nullptr;
+    uint64_t *t_st_coord = tab ? (uint64_t *) (tab + PV_T_ST_COORD) : nullptr;
+    for (int side = 0; side < 2; side++) {
+      const int *order = side == 0 ? in_order : out_order;
+      for (uint32_t v = 0; v < n_vec; v++) {
+        uint64_t off0 = 0, coord0 = 0;
+        bool cut0[PV_DIMS];
+        for (uint64_t e = 0; e < VE; e++) {
+          uint64_t q = (uint64_t) v * VE + e, off = 0, coord = 0, lin = 0;
+          bool cut[PV_DIMS];
+          for (int k = 0; k < n; k++) {
+            const int d = order[k];
+            const uint64_t c = q % T[d];
+            q /= T[d];
+            off += c * (side == 0 ? dims[d].in : dims[d].out);
+            lin += c * lstride[d];
+            if (slot[d] >= 0)
+              coord |= c << (16 * slot[d]);
+            cut[d] = rem[d] != 0 && c >= rem[d];
+          }
+          if (e == 0) {
+            off0 = off;
+            coord0 = coord;
+            for (int d = 0; d < n; d++)
+              cut0[d] = cut[d];
+          } else {
+            if (off != off0 + e)
+              return false;             /* not contiguous in global memory */
+            for (int d = 0; d < n; d++)
+              if (cut[d] != cut0[d])
+                return false;           /* an edge would cut through the vector */
+          }
+          if (side == 1 && st_lin)
+            st_lin[(size_t) v * VE + e] = (uint32_t) lin;
+        }
+        if ((off0 * es) % 16)
+          return false;
+        if (tab) {
+          if (side == 0) {
+            t_ld_off[v] = (uint32_t) (off0 * es);
+            t_ld_coord[v] = coord0;
+          } else {
+            t_st_off[v] = (uint32_t) (off0 * es);
+            t_st_coord[v] = coord0;
+          }
+        }
+      }
+    }
+    if (box_slot)
+      for (int i = 0; i < n; i++)
+        box_slot[i] = slot[i];
+    return true;
+  }
+  bool ok (const uint64_t *T) const
+  {
+    return check (T, nullptr, nullptr, nullptr);
+  }
+};
 
 }  // namespace
 
@@ -376,22 +504,24 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
   *host_table = nullptr;
   if (getenv ("NNSB_PERM_NO_VEC"))
     return -1;
-  const int es = d0.es;
-  if (es != 4 && es != 8)
+  if (((uint64_t) frame_elems * d0.es) % 16)
     return -1;
-  const uint64_t VE = 16 / es;
-  const uint64_t TILE_MAX = PV_STAGE_BYTES / es;
-  if (((uint64_t) frame_elems * es) % 16)
-    return -1;
-  CDim dims[PV_DIMS];
-  const int n = canonicalise (d0, dims);
+  /* launches require 16-byte aligned bases, so an innermost block may fold up to 16 bytes */
+  Builder B;
+  B.es = d0.es;
+  B.n = canonicalise_perm (d0.size, d0.in_stride, d0.rank, frame_elems, 0, 16, 16, B.dims, &B.es);
+  const int n = B.n, es = B.es;
   if (n < 2)
     return -1;                  /* identity: the flat copy */
+  if (es != 4 && es != 8 && es != 16)
+    return -1;
+  const uint64_t VE = B.VE = 16 / es;
+  const uint64_t TILE_MAX = B.TILE_MAX = PV_STAGE_BYTES / es;
+  const CDim *dims = B.dims;
   for (int i = 0; i < n; i++)
     if (dims[i].size > 0xffffffffull)
       return -1;
-
-  int in_order[PV_DIMS], out_order[PV_DIMS];
+  int *in_order = B.in_order, *out_order = B.out_order;
   for (int i = 0; i < n; i++)
     in_order[i] = out_order[i] = i;
   for (int i = 1; i < n; i++)
@@ -401,25 +531,31 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
       in_order[j - 1] = t;
     }
 
-  /* 1. the box: runs of >= RUN bytes on both sides, then grown to <= 16 KiB */
+  /* 1. the box.  Start from runs of >= RUN bytes on both sides, made of whole 32-byte sectors
+   *    where the sizes allow (16-byte multiples otherwise) ... */
   const char *env_run = getenv ("NNSB_PERM_VEC_RUN");
   const uint64_t RUN = (env_run ? (uint64_t) atoi (env_run) : 128) / es;
   uint64_t T[PV_DIMS];
-  for (int i = 0; i < n; i++)
-    T[i] = 1;
-  ensure_run (dims, n, in_order, RUN, VE, T);
-  ensure_run (dims, n, out_order, RUN, VE, T);
-  for (int guard = 0; box_volume (T, n) > TILE_MAX && guard < 64; guard++) {
-    int big = -1;
+  bool have = false;
+  for (uint64_t gran = 2 * VE; gran >= VE && !have; gran /= 2) {
     for (int i = 0; i < n; i++)
-      if (T[i] > VE && (big < 0 || T[i] > T[big]))
-        big = i;
-    if (big < 0)
-      return -1;
-    T[big] = ((T[big] + 1) / 2 + VE - 1) / VE * VE;
+      T[i] = 1;
+    ensure_run (dims, n, in_order, RUN, gran, T);
+    ensure_run (dims, n, out_order, RUN, gran, T);
+    for (int guard = 0; box_volume (T, n) > TILE_MAX && guard < 64; guard++) {
+      int big = -1;
+      for (int i = 0; i < n; i++)
+        if (T[i] > gran && (big < 0 || T[i] > T[big]))
+          big = i;
+      if (big < 0)
+        break;
+      T[big] = ((T[big] + 1) / 2 + gran - 1) / gran * gran;
+    }
+    have = B.ok (T);
   }
-  if (box_volume (T, n) > TILE_MAX)
+  if (!have)
     return -1;
+  /* ... double the two runs in turn while the box fits 16 KiB (keeps them balanced) ... */
   for (int round = 0; round < 64; round++) {
     bool grew = false;
     for (int side = 0; side < 2; side++) {
@@ -427,13 +563,12 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
       for (int k = 0; k < n; k++) {
         const int d = order[k];
         if (T[d] < dims[d].size) {
-          uint64_t nt = T[d] * 2;
-          if (nt > dims[d].size)
-            nt = dims[d].size;
-          if (box_volume (T, n) / T[d] * nt <= TILE_MAX) {
-            T[d] = nt;
+          const uint64_t old = T[d];
+          T[d] = old * 2 > dims[d].size ? dims[d].size : old * 2;
+          if (box_volume (T, n) <= TILE_MAX && B.ok (T))
             grew = true;
-          }
+          else
+            T[d] = old;
           break;                /* only the first non-full dim of each side */
         }
       }
@@ -441,48 +576,36 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
     if (!grew)
       break;
   }
+  /* ... then fill what is left of the stage in smaller power-of-two quanta */
+  for (int side = 0; side < 2; side++) {
+    const int *order = side == 0 ? out_order : in_order;
+    for (int k = 0; k < n; k++) {
+      const int d = order[k];
+      if (T[d] == dims[d].size)
+        continue;
+      const uint64_t old = T[d];
+      uint64_t most = TILE_MAX / (box_volume (T, n) / old);
+      if (most > dims[d].size)
+        most = dims[d].size;
+      uint64_t quantum = old & (~old + 1);      /* largest power of two dividing the extent */
+      bool grown = false;
+      for (; quantum >= 1 && !grown; quantum /= 2) {
+        const uint64_t nt = most / quantum * quantum;
+        if (nt <= old)
+          continue;
+        T[d] = nt;
+        if (B.ok (T))
+          grown = true;
+        else
+          T[d] = old;
+      }
+      break;
+    }
+  }
   const uint64_t volume = box_volume (T, n);
-  if (volume % VE || volume > TILE_MAX)
-    return -1;
   const uint32_t n_vec = (uint32_t) (volume / VE);
 
-  /* 2. static conditions: box origins 16-byte aligned on both sides, offsets fit 32 bits,
-   *    at most PV_BOXED dims with an extent > 1 */
-  uint64_t span_in = 0, span_out = 0, tiles = 1;
-  int n_boxed = 0;
-  for (int i = 0; i < n; i++) {
-    if ((T[i] * dims[i].in * es) % 16 || (T[i] * dims[i].out * es) % 16)
-      if (T[i] < dims[i].size)
-        return -1;
-    span_in += (T[i] - 1) * dims[i].in * es;
-    span_out += (T[i] - 1) * dims[i].out * es;
-    tiles *= (dims[i].size + T[i] - 1) / T[i];
-    pl->box_slot[i] = -1;
-    if (T[i] > 1) {
-      if (n_boxed == PV_BOXED || T[i] > 0xffff)
-        return -1;
-      pl->box_slot[i] = n_boxed++;
-    }
-  }
-  if (span_in >= (1ull << 32) - 16 || span_out >= (1ull << 32) - 16 || tiles >= (1ull << 31))
-    return -1;
-  uint64_t limits_init = 0;
-  for (int b = n_boxed; b < PV_BOXED; b++)
-    limits_init |= 1ull << (16 * b);
-
-  uint32_t lstride[PV_DIMS];
-  {
-    uint32_t ls = 1;
-    for (int k = 0; k < n; k++) {
-      lstride[in_order[k]] = ls;
-      ls *= (uint32_t) T[in_order[k]];
-    }
-  }
-  uint64_t rem[PV_DIMS];                /* extent of the last, partial box (0 = none) */
-  for (int i = 0; i < n; i++)
-    rem[i] = dims[i].size % T[i];
-
-  /* 3. the table, verified element by element */
+  /* 2. the table, verified element by element */
   const size_t table_bytes = PV_T_ST_SLOT + (size_t) PV_NVT * VE * 2;
   unsigned char *tab = (unsigned char *) calloc (1, table_bytes);
   uint32_t *st_lin = (uint32_t *) malloc (sizeof (uint32_t) * volume);
@@ -494,82 +617,61 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
   uint32_t *t_ld_off = (uint32_t *) (tab + PV_T_LD_OFF);
   uint32_t *t_ld_slot = (uint32_t *) (tab + PV_T_LD_SLOT);
   uint32_t *t_st_off = (uint32_t *) (tab + PV_T_ST_OFF);
-  uint64_t *t_ld_coord = (uint64_t *) (tab + PV_T_LD_COORD);
-  uint64_t *t_st_coord = (uint64_t *) (tab + PV_T_ST_COORD);
   uint16_t *t_st_slot = (uint16_t *) (tab + PV_T_ST_SLOT);
   for (int i = 0; i < PV_NVT; i++)
     t_ld_off[i] = t_st_off[i] = PV_INVALID;
-
-  bool ok = true;
-  for (int side = 0; side < 2 && ok; side++) {
-    const int *order = side == 0 ? in_order : out_order;
-    for (uint32_t v = 0; v < n_vec && ok; v++) {
-      uint64_t off0 = 0, coord0 = 0;
-      bool cut0[PV_DIMS];
-      for (uint64_t e = 0; e < VE; e++) {
-        uint64_t q = (uint64_t) v * VE + e, off = 0, coord = 0, lin = 0;
-        bool cut[PV_DIMS];
-        for (int k = 0; k < n; k++) {
-          const int d = order[k];
-          const uint64_t c = q % T[d];
-          q /= T[d];
-          off += c * (side == 0 ? dims[d].in : dims[d].out);
-          lin += c * lstride[d];
-          if (pl->box_slot[d] >= 0)
-            coord |= c << (16 * pl->box_slot[d]);
-          cut[d] = rem[d] != 0 && c >= rem[d];
-        }
-        if (e == 0) {
-          off0 = off;
-          coord0 = coord;
-          memcpy (cut0, cut, sizeof (cut));
-        } else {
-          ok = ok && off == off0 + e;   /* contiguous in global memory */
-          for (int d = 0; d < n; d++)
-            ok = ok && cut[d] == cut0[d];       /* an edge never cuts through a vector */
-        }
-        if (side == 1)
-          st_lin[(size_t) v * VE + e] = (uint32_t) lin;
-      }
-      ok = ok && (off0 * es) % 16 == 0;
-      if (side == 0) {
-        t_ld_off[v] = (uint32_t) (off0 * es);
-        t_ld_coord[v] = coord0;
-      } else {
-        t_st_off[v] = (uint32_t) (off0 * es);
-        t_st_coord[v] = coord0;
-      }
-    }
-  }
-  if (!ok) {
+  if (!B.check (T, pl->box_slot, tab, st_lin)) {
     free (tab);
     free (st_lin);
     return -1;
   }
+  int n_boxed = 0;
+  for (int i = 0; i < n; i++)
+    if (pl->box_slot[i] >= 0)
+      n_boxed++;
+  uint64_t limits_init = 0;
+  for (int b = n_boxed; b < PV_BOXED; b++)
+    limits_init |= 1ull << (16 * b);
+  uint64_t tiles = 1;
+  for (int i = 0; i < n; i++)
+    tiles *= (dims[i].size + T[i] - 1) / T[i];
 
-  /* 4. shared-memory swizzle: the candidate with the fewest gather wavefronts */
-  int best_shift = -1;
+  /* 3. shared-memory swizzle: the candidate with the fewest gather wavefronts */
+  Swizzle best_sw = { -1, -1 };
   {
     const char *env_sw = getenv ("NNSB_PERM_VEC_SWIZZLE");
     if (env_sw) {
-      best_shift = atoi (env_sw);
+      best_sw.s1 = atoi (env_sw);          /* "s1" or "s1,s2" */
+      if (strchr (env_sw, ','))
+        best_sw.s2 = atoi (strchr (env_sw, ',') + 1);
+      if (!best_sw.is_permutation ())
+        best_sw.s1 = best_sw.s2 = -1;
+      pl->gather_wavefronts = gather_cost (st_lin, n_vec, (int) VE, es, best_sw);
     } else {
-      uint64_t best = gather_cost (st_lin, n_vec, (int) VE, es, -1);
-      for (int s = 3; s <= 9; s++) {
-        const uint64_t c = gather_cost (st_lin, n_vec, (int) VE, es, s);
-        if (c < best) {
-          best = c;
-          best_shift = s;
+      uint64_t best = gather_cost (st_lin, n_vec, (int) VE, es, best_sw);
+      /* s1 = 1 is left out: same simulated gather cost, but measured 8 % slower (the
+       * cp.async writes seem to dislike chunk pairs being swapped) */
+      for (int s1 = 2; s1 <= 9; s1++)
+        for (int s2 = -1; s2 <= 9; s2++) {
+          if (s2 >= 0 && s2 <= s1)
+            continue;
+          const Swizzle sw = { s1, s2 };
+          if (!sw.is_permutation ())
+            continue;
+          const uint64_t c = gather_cost (st_lin, n_vec, (int) VE, es, sw);
+          if (c < best) {
+            best = c;
+            best_sw = sw;
+          }
         }
-      }
+      pl->gather_wavefronts = best;
     }
   }
-  auto swz = [&] (uint32_t q) { return best_shift >= 0 ? q ^ ((q >> best_shift) & 7u) : q; };
   for (uint32_t v = 0; v < n_vec; v++) {
-    t_ld_slot[v] = swz (v) * 16;
+    t_ld_slot[v] = best_sw (v) * 16;
     for (uint64_t e = 0; e < VE; e++) {
       const uint32_t li = st_lin[(size_t) v * VE + e];
-      t_st_slot[(size_t) v * VE + e] = (uint16_t) (swz (li / (uint32_t) VE) * 16 + (li % VE) * es);
+      t_st_slot[(size_t) v * VE + e] = (uint16_t) (best_sw (li / (uint32_t) VE) * 16 + (li % VE) * es);
     }
   }
   free (st_lin);
@@ -587,7 +689,9 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
   pl->n_vec = n_vec;
   pl->tiles_per_frame = tiles;
   pl->table_bytes = table_bytes;
-  pl->swizzle_shift = best_shift;
+  pl->frame_bytes = (uint64_t) frame_elems * d0.es;
+  pl->swizzle_shift = best_sw.s1;
+  pl->swizzle_shift2 = best_sw.s2;
   *host_table = tab;
   return 0;
 }
@@ -640,8 +744,8 @@ launch_permute_vec (const PermVecPlan &pl, const void *d_table, const void *in, 
     p.tile[n] = 1;
     p.size[n] = batch;
     p.ntile[n] = make_fastdiv (batch);
-    p.in_stride_b[n] = (uint64_t) frame_elems * pl.es;
-    p.out_stride_b[n] = (uint64_t) frame_elems * pl.es;
+    p.in_stride_b[n] = pl.frame_bytes;
+    p.out_stride_b[n] = pl.frame_bytes;
     p.box_slot[n] = -1;
     n++;
   }
@@ -649,8 +753,12 @@ launch_permute_vec (const PermVecPlan &pl, const void *d_table, const void *in, 
   p.limits_init = pl.limits_init;
   p.n_vec = pl.n_vec;
   p.n_tiles = (uint32_t) tiles;
-  return pl.es == 4 ? launch_permute_vec_t<4> (p, d_table, in, out, cfg, stream)
-      : launch_permute_vec_t<8> (p, d_table, in, out, cfg, stream);
+  switch (pl.es) {
+    case 4: return launch_permute_vec_t<4> (p, d_table, in, out, cfg, stream);
+    case 8: return launch_permute_vec_t<8> (p, d_table, in, out, cfg, stream);
+    case 16: return launch_permute_vec_t<16> (p, d_table, in, out, cfg, stream);
+    default: return -1;
+  }
 }
 
 }  // namespace nnsb

@@ -70,14 +70,16 @@ struct PermDesc
 };
 /* K3/K4 vector path (k_perm_vec.cu): 16-byte accesses on both sides, driven by a table that
  * the host builds once per plan (per-vector global offsets and swizzled shared-memory slots
- * for one box) and the plan keeps in device memory.  4- and 8-byte elements.
+ * for one box) and the plan keeps in device memory.  4-, 8- and 16-byte elements (after an
+ * innermost block common to both sides has been folded into the element).
  *   perm_vec_build : 0 = eligible, *host_table is malloc()ed (table_bytes long); -1 = not
  *   launch_permute_vec : -1 when this call does not qualify (unaligned pointers, too many
  *                        tiles), else the launch status */
 struct PermVecPlan
 {
   int valid;
-  int es;
+  int es;                                       /* element bytes after folding (4, 8, 16) */
+  uint64_t frame_bytes;
   int n;                                        /* canonical dims, output order, no batch */
   uint32_t size[NNSB_PERM_MAX_RANK];
   uint32_t tile[NNSB_PERM_MAX_RANK];            /* box extent per dim */
@@ -88,7 +90,9 @@ struct PermVecPlan
   uint32_t n_vec;                               /* 16-byte vectors per box */
   uint64_t tiles_per_frame;
   size_t table_bytes;
-  int swizzle_shift;                            /* chosen shared-memory swizzle (-1 = none) */
+  int swizzle_shift, swizzle_shift2;            /* chosen shared-memory swizzle (-1 = none) */
+  uint64_t gather_wavefronts;                   /* simulated LDS wavefronts per box (ideal:
+                                                 * one per 128 bytes gathered) */
 };
 int perm_vec_build (const PermDesc & d, size_t frame_elems, PermVecPlan * plan, void **host_table);
 int launch_permute_vec (const PermVecPlan & plan, const void *d_table, const void *in, void *out,

@@ -310,6 +310,27 @@ def test_transpose_vector_path(dev, port, order, case):
         assert "vector table" in desc, desc
 
 
+@pytest.mark.parametrize("order", [(0, 2, 1, 3), (0, 1, 2, 3)])
+def test_transpose_innermost_block_folds_into_element(dev, port, order):
+    """A block that is innermost on both sides (RGBA bytes, a float4) moves as one wide element."""
+    for dtype, dim, batch in (("uint8", [4, 68, 36, 1], 2), ("uint8", [16, 20, 12, 1], 1),
+                              ("uint8", [32, 20, 12, 1], 1), ("uint8", [6, 20, 12, 1], 1),
+                              ("uint16", [2, 36, 24, 1], 3), ("uint16", [8, 12, 20, 1], 1),
+                              ("float32", [4, 36, 20, 1], 2), ("float32", [2, 132, 36, 1], 1),
+                              ("float64", [2, 36, 20, 1], 1), ("uint8", [4, 5, 3, 1], 3)):
+        n = int(np.prod(dim))
+        x = rand_small(dtype, n * batch, seed=n)
+        opt = "%d:%d:%d:3" % order[:3]
+        plan = dev.plan("transpose", opt, dtype, dim)
+        desc = plan.describe()
+        got = plan.run_host(x, batch=batch)
+        plan.close()
+        want = np.concatenate([port.transpose(x[i * n:(i + 1) * n], dim, order)
+                               for i in range(batch)])
+        assert bits_equal(got, want), "%s %s %s [%s]: %s" % (dtype, dim, opt, desc,
+                                                              first_mismatch(got, want))
+
+
 def test_dimchg_vector_path(dev, port):
     for dtype, dim, f, t in (("float32", [4, 20, 36, 8], 0, 3), ("float32", [16, 12, 40, 1], 1, 2),
                              ("float64", [6, 10, 34, 2], 0, 2), ("float32", [32, 3, 50, 4], 0, 1)):
