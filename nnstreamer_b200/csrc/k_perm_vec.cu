@@ -34,8 +34,12 @@
 
 namespace nnsb {
 
-constexpr int PV_THREADS = 256;
-constexpr int PV_VPT = 4;                                 /* vectors per thread per tile */
+#ifndef NNSB_PV_THREADS
+#define NNSB_PV_THREADS 256
+#define NNSB_PV_MIN_BLOCKS 4
+#endif
+constexpr int PV_THREADS = NNSB_PV_THREADS;
+constexpr int PV_VPT = 1024 / PV_THREADS;                 /* vectors per thread per tile */
 constexpr int PV_NVT = PV_THREADS * PV_VPT;               /* vector slots per stage: 1024 */
 constexpr int PV_STAGE_BYTES = PV_NVT * 16;               /* 16 KiB */
 constexpr int PV_STAGES = 3;
@@ -122,7 +126,7 @@ gather (uint32_t stage_addr, const uint32_t *slot, uint32_t *w)
 }
 
 template <int ES>
-__global__ void __launch_bounds__ (PV_THREADS, 4)
+__global__ void __launch_bounds__ (PV_THREADS, NNSB_PV_MIN_BLOCKS)
 permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
     const unsigned char *__restrict__ table, const __grid_constant__ PermVecDev p)
 {
