@@ -265,6 +265,9 @@ def extra_kernels(dev, peak, with_cpu=True):
     run("transpose_1_0_2_4k_f32", "transpose", "1:0:2:3", "float32", [3, 3840, 2160, 1], 1, 8, f32)
     run("transpose_0_2_1_4k_f32", "transpose", "0:2:1:3", "float32", [3, 3840, 2160, 1], 1, 8, f32)
     run("transpose_2_1_0_4k_f32", "transpose", "2:1:0:3", "float32", [3, 3840, 2160, 1], 1, 8, f32)
+    for o in ("2:0:1:3", "1:0:2:3", "0:2:1:3", "2:1:0:3"):
+        run("transpose_%s_4k_f32_b8" % o[:5].replace(":", "_"), "transpose", o, "float32",
+            [3, 3840, 2160, 1], 8, 8, f32)
     run("dimchg_0_2_4k_f32", "dimchg", "0:2", "float32", [3, 3840, 2160, 1], 1, 8, f32,
         lambda c, x, d: c.dimchg(x, d, 0, 2))
     run("clamp_f32_1080p_b64", "clamp", "-33.3:77.7", "float32", DIM, 64, 8, f32,
