@@ -271,6 +271,14 @@ NNSB_API int nnsb_plan_describe (const nnsb_plan * plan, char *buf, size_t bufle
 NNSB_API int nnsb_plan_stand_stats (nnsb_plan * plan, nnsb_stream * s, uint32_t batch,
     double *mean_out, double *std_out, size_t capacity);
 
+/* Plan for a raw strided copy: `rank` output dims (innermost first) of extent size[i], whose
+ * elements (es bytes each: 1, 2, 4 or 8) are read from the input at stride in_stride[i]
+ * (elements); the output is dense.  Runs on the same kernels as transpose / dimchg and is
+ * launched with nnsb_plan_launch.  Used by the aggregator for the concatenation along an inner
+ * axis (gsttensor_aggregator.c:768-787, a block interleave of frames_out frames). */
+NNSB_API int nnsb_plan_create_permute (nnsb_ctx * ctx, int es, int rank, const uint32_t *size,
+    const uint64_t *in_stride, nnsb_plan ** out);
+
 /* tensor_converter video row-stride strip, gsttensor_converter.c:1087-1100: copies `rows`
  * rows of `row_bytes` from a source with pitch `src_pitch` into a dense destination.
  * Both pointers are device memory. */
@@ -379,6 +387,41 @@ NNSB_API int nnsb_queue_destroy (nnsb_queue * q);
 /* *full = 1 when the queue now holds `batch` frames */
 NNSB_API int nnsb_queue_push (nnsb_queue * q, const void *frame, int on_device, int *full);
 NNSB_API int nnsb_queue_flush (nnsb_queue * q, void **d_out, uint32_t *n_frames, nnsb_stream ** stream);
+
+/* ---------------------------------------------------------------------------------------
+ * tensor_aggregator mirror: GstTensorAggregator,
+ * gst/nnstreamer/elements/gsttensor_aggregator.c.  The GstAdapter becomes a byte range of one
+ * device buffer; the concatenation along an inner axis (:768-787) is one permutation launch.
+ * Properties (:170-240): frames-in, frames-out, frames-flush, frames-dim, concat, silent.
+ * ------------------------------------------------------------------------------------- */
+typedef struct nnsb_aggregator nnsb_aggregator;
+#define NNSB_CLOCK_TIME_NONE 0xffffffffffffffffull      /* GST_CLOCK_TIME_NONE */
+typedef struct
+{
+  uint64_t pts, dts, duration;  /* GST_BUFFER_PTS / _DTS / _DURATION, nanoseconds */
+} nnsb_buffer_time;
+NNSB_API int nnsb_aggregator_new (int device_id, nnsb_aggregator ** out);
+NNSB_API int nnsb_aggregator_free (nnsb_aggregator * a);
+/* gst_tensor_aggregator_set_property / _get_property, :313-382 */
+NNSB_API int nnsb_aggregator_set_property (nnsb_aggregator * a, const char *name, const char *value);
+NNSB_API int nnsb_aggregator_get_property (nnsb_aggregator * a, const char *name, char *buf,
+    size_t buflen);
+/* gst_tensor_aggregator_parse_caps, :1026-1081: sink caps in, source caps out */
+NNSB_API int nnsb_aggregator_set_caps (nnsb_aggregator * a, const char *incaps, char *outcaps,
+    size_t outlen);
+NNSB_API int nnsb_aggregator_get_config (nnsb_aggregator * a, int direction, nnsb_tensors_config * cfg);
+/* gst_tensor_aggregator_reset, :979-990 (READY->PAUSED :958, flush-stop :420-422) */
+NNSB_API int nnsb_aggregator_reset (nnsb_aggregator * a);
+/* number of output buffers the next chain call with in_size bytes will produce */
+NNSB_API int nnsb_aggregator_outputs_for (nnsb_aggregator * a, size_t in_size);
+/* gst_tensor_aggregator_chain, :835-941.  `in` is host or device memory and may be reused on
+ * return.  Every output is a device memory (owned, release with nnsb_memory_release; when
+ * frames-in == frames-out and nothing is concatenated a device input is passed on unowned).
+ * t_in / t_outs may be NULL.  Returns a NNSB_FLOW_* code. */
+NNSB_API int nnsb_aggregator_chain (nnsb_aggregator * a, const nnsb_memory * in,
+    const nnsb_buffer_time * t_in, nnsb_memory * outs, nnsb_buffer_time * t_outs, uint32_t max_out,
+    uint32_t *n_out);
+NNSB_API int nnsb_aggregator_kernel_launches (nnsb_aggregator * a, uint64_t *count);
 
 /* No counterpart in the reference (its CPU element simply mallocs).  The same stand kernels
  * as nnsb_plan_launch(), for callers that must not allocate while frames are flowing: a

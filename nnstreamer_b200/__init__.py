@@ -1,4 +1,4 @@
-"""nnstreamer_b200 -- B200-native tensor_transform / tensor_converter hot path.
+"""nnstreamer_b200 -- B200-native tensor_transform / tensor_converter hot path (+ tensor_aggregator).
 
 Everything computes on the GPU through libnnstreamer_b200.so (see include/nnstreamer_b200.h);
 this package only mirrors the reference element's interface on top of that C-ABI.
@@ -6,8 +6,8 @@ this package only mirrors the reference element's interface on top of that C-ABI
 from . import _lib  # noqa: F401
 from ._lib import NnsbError, lib  # noqa: F401
 from .device import Device, Plan  # noqa: F401
-from .element import (BatchQueue, DeviceMemory, TensorConverter, TensorTransform,  # noqa: F401
-                      device_memory)
+from .element import (BatchQueue, DeviceMemory, TensorAggregator, TensorConverter,  # noqa: F401
+                      TensorTransform, device_memory)
 
 __all__ = ["Device", "Plan", "NnsbError", "lib", "TensorTransform", "TensorConverter",
-           "BatchQueue", "DeviceMemory"]
+           "TensorAggregator", "BatchQueue", "DeviceMemory"]

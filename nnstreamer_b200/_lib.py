@@ -64,6 +64,11 @@ class Memory(C.Structure):
                 ("owned", C.c_int32), ("owner", C.c_void_p)]
 
 
+class BufferTime(C.Structure):
+    _fields_ = [("pts", C.c_uint64), ("dts", C.c_uint64), ("duration", C.c_uint64)]
+
+
+CLOCK_TIME_NONE = 0xffffffffffffffff
 FLOW_OK, FLOW_ERROR, FLOW_NOT_SUPPORTED, ENOENT = 0, -5, -6, -2
 
 
@@ -134,6 +139,8 @@ _PROTOS = {
     "nnsb_plan_launch_elems": (C.c_int, [_VP, _VP, _VP, C.c_uint64, C.c_uint64, _VP]),
     "nnsb_plan_last_launch_count": (C.c_int, [_VP]),
     "nnsb_plan_describe": (C.c_int, [_VP, C.c_char_p, C.c_size_t]),
+    "nnsb_plan_create_permute": (C.c_int, [_VP, C.c_int, C.c_int, C.POINTER(C.c_uint32),
+                                           C.POINTER(C.c_uint64), C.POINTER(_VP)]),
     "nnsb_plan_stand_stats": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(C.c_double),
                                         C.POINTER(C.c_double), C.c_size_t]),
     "nnsb_strip_launch": (C.c_int, [_VP, _VP, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),
@@ -165,6 +172,18 @@ _PROTOS = {
     "nnsb_converter_remove_padding": (C.c_int, [_VP]),
     "nnsb_converter_frame_size": (C.c_size_t, [_VP]),
     "nnsb_converter_chain": (C.c_int, [_VP, C.POINTER(Memory), C.POINTER(Memory), C.POINTER(C.c_int)]),
+    "nnsb_aggregator_new": (C.c_int, [C.c_int, C.POINTER(_VP)]),
+    "nnsb_aggregator_free": (C.c_int, [_VP]),
+    "nnsb_aggregator_set_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p]),
+    "nnsb_aggregator_get_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "nnsb_aggregator_set_caps": (C.c_int, [_VP, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "nnsb_aggregator_get_config": (C.c_int, [_VP, C.c_int, C.POINTER(TensorsConfig)]),
+    "nnsb_aggregator_reset": (C.c_int, [_VP]),
+    "nnsb_aggregator_outputs_for": (C.c_int, [_VP, C.c_size_t]),
+    "nnsb_aggregator_chain": (C.c_int, [_VP, C.POINTER(Memory), C.POINTER(BufferTime),
+                                        C.POINTER(Memory), C.POINTER(BufferTime), C.c_uint32,
+                                        C.POINTER(C.c_uint32)]),
+    "nnsb_aggregator_kernel_launches": (C.c_int, [_VP, C.POINTER(C.c_uint64)]),
     "nnsb_queue_create": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(_VP)]),
     "nnsb_queue_destroy": (C.c_int, [_VP]),
     "nnsb_queue_push": (C.c_int, [_VP, _VP, C.c_int, C.POINTER(C.c_int)]),

@@ -541,6 +541,8 @@ nnsb_plan_destroy (nnsb_plan * plan)
   return NNSB_OK;
 }
 
+static int attach_perm_vec (nnsb_ctx * ctx, nnsb_plan * plan);
+
 extern "C" int
 nnsb_plan_create (nnsb_ctx * ctx, const nnsb_option * opt, const nnsb_tensor_info * in_info,
     int acceleration, nnsb_plan ** out)
@@ -670,25 +672,89 @@ nnsb_plan_create (nnsb_ctx * ctx, const nnsb_option * opt, const nnsb_tensor_inf
       return nnsb_set_error (NNSB_ENOTSUP, "Not supported tensor transform mode");
   }
   if (opt->mode == NNSB_MODE_TRANSPOSE || opt->mode == NNSB_MODE_DIMCHG) {
-    /* per-box table of the vector kernel: built and verified on the host, kept in HBM */
-    void *host_table = nullptr;
-    if (perm_vec_build (plan->perm, plan->frame_elems, &plan->perm_vec, &host_table) == 0) {
-      void *d = nullptr;
-      r = nnsb_dev_alloc (ctx, plan->perm_vec.table_bytes, &d);
-      if (r == NNSB_OK) {
-        plan->d_perm_table = d;
-        cudaError_t e = cudaMemcpy (d, host_table, plan->perm_vec.table_bytes,
-            cudaMemcpyHostToDevice);
-        if (e != cudaSuccess)
-          r = nnsb_set_error (NNSB_ECUDA, "cudaMemcpy (permute table) failed: %s",
-              cudaGetErrorString (e));
-      }
-      free (host_table);
-      if (r) {
-        nnsb_plan_destroy (plan);
-        return r;
-      }
+    r = attach_perm_vec (ctx, plan);
+    if (r) {
+      nnsb_plan_destroy (plan);
+      return r;
     }
+  }
+  *out = plan;
+  return NNSB_OK;
+}
+
+static int
+attach_perm_vec (nnsb_ctx * ctx, nnsb_plan * plan)
+{
+  /* per-box table of the vector kernel: built and verified on the host, kept in HBM */
+  void *host_table = nullptr;
+  int r = NNSB_OK;
+  if (perm_vec_build (plan->perm, plan->frame_elems, &plan->perm_vec, &host_table) == 0) {
+    void *d = nullptr;
+    r = nnsb_dev_alloc (ctx, plan->perm_vec.table_bytes, &d);
+    if (r == NNSB_OK) {
+      plan->d_perm_table = d;
+      cudaError_t e = cudaMemcpy (d, host_table, plan->perm_vec.table_bytes,
+          cudaMemcpyHostToDevice);
+      if (e != cudaSuccess)
+        r = nnsb_set_error (NNSB_ECUDA, "cudaMemcpy (permute table) failed: %s",
+            cudaGetErrorString (e));
+    }
+    free (host_table);
+  }
+  return r;
+}
+
+extern "C" int
+nnsb_plan_create_permute (nnsb_ctx * ctx, int es, int rank, const uint32_t *size,
+    const uint64_t *in_stride, nnsb_plan ** out)
+{
+  if (!out || !size || !in_stride)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_create_permute: null argument");
+  *out = nullptr;
+  int r = bind (ctx);
+  if (r)
+    return r;
+  if (rank < 1 || rank > NNSB_PERM_MAX_RANK)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_create_permute: rank must be 1..%d",
+        NNSB_PERM_MAX_RANK);
+  int type;
+  switch (es) {
+    case 1: type = NNSB_UINT8; break;
+    case 2: type = NNSB_UINT16; break;
+    case 4: type = NNSB_UINT32; break;
+    case 8: type = NNSB_UINT64; break;
+    default:
+      return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_create_permute: element size must be 1, 2, 4 or 8");
+  }
+  nnsb_plan *plan = new (std::nothrow) nnsb_plan ();
+  if (!plan)
+    return nnsb_set_error (NNSB_ENOMEM, "nnsb_plan_create_permute: out of memory");
+  memset (plan, 0, sizeof (*plan));
+  plan->ctx = ctx;
+  plan->opt.mode = NNSB_MODE_TRANSPOSE;
+  uint64_t elems = 1;
+  plan->perm.rank = rank;
+  plan->perm.es = es;
+  for (int i = 0; i < NNSB_RANK_LIMIT; i++)
+    plan->in_info.dim[i] = 1;
+  for (int i = 0; i < rank; i++) {
+    if (size[i] == 0) {
+      delete plan;
+      return nnsb_set_error (NNSB_EINVAL, "nnsb_plan_create_permute: zero extent");
+    }
+    plan->perm.size[i] = size[i];
+    plan->perm.in_stride[i] = in_stride[i];
+    plan->in_info.dim[i] = size[i];
+    elems *= size[i];
+  }
+  plan->in_info.type = type;
+  plan->out_info = plan->in_info;
+  plan->frame_elems = elems;
+  plan->in_size = plan->out_size = (size_t) elems * es;
+  r = attach_perm_vec (ctx, plan);
+  if (r) {
+    nnsb_plan_destroy (plan);
+    return r;
   }
   *out = plan;
   return NNSB_OK;

@@ -251,6 +251,95 @@ class TensorConverter:
         return flow, (DeviceMemory(out) if produced.value else None)
 
 
+class TensorAggregator:
+    """gst_element_factory_make ("tensor_aggregator"): frames-in / frames-out / frames-flush /
+    frames-dim / concat, with the adapter and the concatenation on the device."""
+
+    _UINT_PROPS = ("frames-in", "frames-out", "frames-flush", "frames-dim")
+
+    def __init__(self, device_id=0, **props):
+        self._lib = L.lib()
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_aggregator_new(int(device_id), C.byref(self.handle)))
+        for k, v in props.items():
+            self.set_property(k.replace("_", "-"), v)
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_aggregator_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_property(self, name, value):
+        if isinstance(value, bool):
+            value = "true" if value else "false"
+        L.check(self._lib.nnsb_aggregator_set_property(self.handle, name.encode(), str(value).encode()))
+
+    def get_property(self, name):
+        buf = C.create_string_buffer(256)
+        code = self._lib.nnsb_aggregator_get_property(self.handle, name.encode(), buf, 256)
+        if code < 0:
+            L.check(code)
+        s = buf.value.decode()
+        return int(s) if name in self._UINT_PROPS else (s == "true")
+
+    def set_caps(self, caps):
+        """Sink caps in, source caps out (gst_tensor_aggregator_parse_caps)."""
+        buf = C.create_string_buffer(_CAPS_BUF)
+        code = self._lib.nnsb_aggregator_set_caps(self.handle, caps.encode(), buf, _CAPS_BUF)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def config(self, direction):
+        cfg = L.TensorsConfig()
+        L.check(self._lib.nnsb_aggregator_get_config(self.handle, int(direction), C.byref(cfg)))
+        return cfg
+
+    def reset(self):
+        L.check(self._lib.nnsb_aggregator_reset(self.handle))
+
+    def outputs_for(self, nbytes):
+        return self._lib.nnsb_aggregator_outputs_for(self.handle, int(nbytes))
+
+    def chain(self, buf, pts=None, dts=None, duration=None):
+        """One buffer in (numpy array or DeviceMemory); returns (flow, [DeviceMemory...],
+        [(pts, dts, duration)...]) with None for GST_CLOCK_TIME_NONE."""
+        if isinstance(buf, DeviceMemory):
+            m = buf.mem
+        else:
+            a = np.ascontiguousarray(buf)
+            m = _host_memory(a)
+        none = L.CLOCK_TIME_NONE
+        t_in = L.BufferTime(none if pts is None else int(pts), none if dts is None else int(dts),
+                            none if duration is None else int(duration))
+        room = max(1, self.outputs_for(m.size))
+        outs = (L.Memory * room)()
+        t_outs = (L.BufferTime * room)()
+        n_out = C.c_uint32(0)
+        flow = self._lib.nnsb_aggregator_chain(self.handle, C.byref(m), C.byref(t_in), outs, t_outs,
+                                               room, C.byref(n_out))
+        mems, times = [], []
+        for i in range(n_out.value):
+            o = L.Memory()
+            C.memmove(C.byref(o), C.byref(outs[i]), C.sizeof(L.Memory))
+            mems.append(DeviceMemory(o))
+            t = t_outs[i]
+            times.append(tuple(None if v == none else int(v) for v in (t.pts, t.dts, t.duration)))
+        return flow, mems, times
+
+    @property
+    def kernel_launches(self):
+        c = C.c_uint64(0)
+        L.check(self._lib.nnsb_aggregator_kernel_launches(self.handle, C.byref(c)))
+        return int(c.value)
+
+
 class BatchQueue:
     """nnsb_queue: groups frames so that one launch covers `batch` tensors."""
 

@@ -654,3 +654,26 @@ oracle_stride_strip (const void *src, void *dst, uint32_t color, uint32_t width,
     memcpy ((char *) dst + h * size, (const char *) src + h * offset, size);
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------- */
+/* tensor_aggregator: the block interleave of gst_tensor_aggregator_concat               */
+/* (gsttensor_aggregator.c:768-787).  src holds frames_out frames of frame_size bytes     */
+/* back to back; block_size = element size * prod (frame dim[0..frames_dim]).             */
+/* ------------------------------------------------------------------------------------- */
+int
+oracle_aggregator_concat (const void *src, void *dst, uint64_t frame_size, uint32_t frames_out,
+    uint64_t block_size)
+{
+  uint64_t src_idx = 0, dest_idx = 0;
+  uint32_t f;
+  if (block_size == 0 || frame_size == 0 || frame_size % block_size)
+    return -1;
+  do {
+    for (f = 0; f < frames_out; f++) {
+      memcpy ((char *) dst + dest_idx, (const char *) src + src_idx + frame_size * f, block_size);
+      dest_idx += block_size;
+    }
+    src_idx += block_size;
+  } while (src_idx < frame_size);
+  return 0;
+}

@@ -143,6 +143,9 @@ class Port:
                                    C.c_double]
         L.oracle_stride_strip.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
 
+        L.oracle_aggregator_concat.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32,
+                                               C.c_uint64]
+
     def typecast(self, x, out_type, accel=False):
         x = np.ascontiguousarray(x)
         out = np.empty(x.size, dtype=NP_DTYPE[out_type])
@@ -208,6 +211,64 @@ class Port:
         out = np.empty(color * width * height, dtype=np.uint8)
         self.lib.oracle_stride_strip(_ptr(src), _ptr(out), color, width, height)
         return out
+
+
+    def aggregator_concat(self, src, frame_size, frames_out, block_size):
+        """gst_tensor_aggregator_concat (gsttensor_aggregator.c:768-787) on raw bytes."""
+        src = np.ascontiguousarray(src).view(np.uint8).reshape(-1)
+        assert src.size == frame_size * frames_out
+        out = np.empty_like(src)
+        r = self.lib.oracle_aggregator_concat(_ptr(src), _ptr(out), frame_size, frames_out, block_size)
+        assert r == 0
+        return out
+
+
+class AggregatorModel:
+    """CPU model of GstTensorAggregator's data path (gsttensor_aggregator.c:835-941): a byte
+    adapter, frames_out frames per output, concatenation along frames-dim, frames_flush frames
+    flushed.  dim / type describe the INCOMING tensor (the sink caps)."""
+
+    def __init__(self, port_, dim, type_name, frames_in=1, frames_out=1, frames_flush=0,
+                 frames_dim=7, concat=True):
+        self.port = port_
+        self.dim = dims8(dim)
+        self.es = np.dtype(type_name).itemsize
+        self.fi, self.fo, self.ff, self.fd = frames_in, frames_out, frames_flush, frames_dim
+        self.concat = concat
+        assert self.dim[frames_dim] % frames_in == 0          # :1066-1070
+        self.out_dim = list(self.dim)
+        self.out_dim[frames_dim] = self.dim[frames_dim] // frames_in * frames_out
+        self.frame_dim = list(self.out_dim)
+        self.frame_dim[frames_dim] //= frames_out             # :813-815
+        self.adapter = bytearray()
+
+    def reset(self):
+        self.adapter = bytearray()
+
+    def _push_out(self, data, frame_size):
+        need = self.concat and self.fo > 1 and any(d > 1 for d in self.frame_dim[self.fd + 1:])
+        assert frame_size == self.es * int(np.prod(self.frame_dim, dtype=np.uint64))
+        if not need:
+            return np.frombuffer(bytes(data), dtype=np.uint8).copy()
+        block = self.es * int(np.prod(self.frame_dim[:self.fd + 1], dtype=np.uint64))
+        return self.port.aggregator_concat(np.frombuffer(bytes(data), dtype=np.uint8), frame_size,
+                                           self.fo, block)
+
+    def chain(self, buf):
+        buf = np.ascontiguousarray(buf).view(np.uint8).reshape(-1)
+        frame_size = buf.size // self.fi
+        if self.fi == self.fo:
+            return [self._push_out(buf, frame_size)]
+        self.adapter += buf.tobytes()
+        out_size = frame_size * self.fo
+        outs = []
+        while len(self.adapter) >= out_size:
+            avail = len(self.adapter)
+            outs.append(self._push_out(self.adapter[:out_size], frame_size))
+            flush = frame_size * self.ff if self.ff > 0 else out_size
+            flush = min(flush, avail)
+            del self.adapter[:flush]
+        return outs
 
 
 class Ref:
