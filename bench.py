@@ -295,6 +295,52 @@ def extra_kernels(dev, peak, with_cpu=True):
         out["stride_strip_1918x1080_rgb_b32"]["cpu_reference_1_thread_GB/s"] = 2 * row * 1080 / dt / 1e9
     dev.free(d_src)
     dev.free(d_dst)
+    out.update(aggregator_extras(dev, peak, checker is not None))
+    return out
+
+
+def aggregator_extras(dev, peak, with_cpu):
+    """tensor_aggregator: 1080p RGB uint8 frames already in HBM, frames-out=32.
+    frames-dim=3 batches by appending (one D2D copy per frame + one per output); frames-dim=1
+    concatenates along the width (adapter copy + one permutation launch per output).  Algorithmic
+    bytes: 2 x frame bytes per frame (read once, written once)."""
+    from nnstreamer_b200 import TensorAggregator, device_memory
+    out = {}
+    rng = np.random.default_rng(11)
+    frame = rng.integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
+    d_frame = dev.upload(frame)
+    mem = device_memory(d_frame, frame.nbytes)
+    caps = ("other/tensor, dimension=(string)3:1920:1080:1, type=(string)uint8, "
+            "framerate=(fraction)30/1")
+    for name, fdim in (("aggregator_1080p_u8_out32_append", 3), ("aggregator_1080p_u8_out32_concat_w", 1)):
+        agg = TensorAggregator(frames_out=32, frames_dim=fdim)
+        agg.set_caps(caps)
+        n_frames = 32 * 6
+        for i in range(32):                         # warm-up: one output
+            _, mems, _ = agg.chain(mem)
+            for m in mems:
+                m.release()
+        t0 = time.perf_counter()
+        produced = 0
+        for i in range(n_frames):
+            _, mems, _ = agg.chain(mem)
+            for m in mems:
+                produced += 1
+                m.release()
+        dt = time.perf_counter() - t0
+        out[name] = {"frames/s": n_frames / dt, "GB/s": 2 * frame.nbytes * n_frames / dt / 1e9,
+                     "outputs": produced, "kernel_launches": agg.kernel_launches,
+                     "timing": "wall clock around synchronous chain calls, device-resident frames"}
+        agg.close()
+    if with_cpu:
+        port = cpu_checker_port()
+        frames4 = np.tile(frame, 4)
+        t0 = time.perf_counter()
+        port.aggregator_concat(frames4, frame.nbytes, 4, 3 * 1920)
+        dt = time.perf_counter() - t0
+        out["aggregator_1080p_u8_out32_concat_w"]["cpu_reference_1_thread_GB/s"] = \
+            2 * frames4.nbytes / dt / 1e9
+    dev.free(d_frame)
     return out
 
 
