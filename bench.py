@@ -293,6 +293,19 @@ def extra_kernels(dev, peak, with_cpu=True):
         cpu_checker_port().stride_strip(src[:pitch * 1080], 3, w, 1080)
         dt = time.perf_counter() - t0
         out["stride_strip_1918x1080_rgb_b32"]["cpu_reference_1_thread_GB/s"] = 2 * row * 1080 / dt / 1e9
+    # tensor_decoder direct_video (K9): the inverse, dense rows -> rows padded to 4 bytes
+    d_pad = dev.alloc(pitch * rows)
+    ms = time_launches(dev, lambda: dev.pad(d_dst, d_pad, row, pitch, rows), 10, 3) / 10
+    gbs = 2 * row * rows / (ms * 1e-3) / 1e9
+    out["direct_video_pad_1918x1080_rgb_b32"] = {"ms": ms, "GB/s": gbs,
+                                                 "frac_of_measured_peak": gbs / peak, "launches": 1}
+    if checker is not None:
+        dense = src[:row * 1080]
+        t0 = time.perf_counter()
+        cpu_checker_port().direct_video(dense, 3, w, 1080)
+        dt = time.perf_counter() - t0
+        out["direct_video_pad_1918x1080_rgb_b32"]["cpu_reference_1_thread_GB/s"] = 2 * row * 1080 / dt / 1e9
+    dev.free(d_pad)
     dev.free(d_src)
     dev.free(d_dst)
     out.update(aggregator_extras(dev, peak, checker is not None))

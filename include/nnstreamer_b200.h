@@ -285,6 +285,16 @@ NNSB_API int nnsb_plan_create_permute (nnsb_ctx * ctx, int es, int rank, const u
 NNSB_API int nnsb_strip_launch (nnsb_stream * s, const void *d_src, void *d_dst,
     size_t row_bytes, size_t src_pitch, size_t rows);
 
+/* tensor_decoder direct_video row padding, tensordec-directvideo.c:326-339 (the inverse of the
+ * strip): `rows` dense rows of `row_bytes` go to a destination with pitch `dst_pitch`; the
+ * padding bytes are written as zero (the reference leaves them uninitialised).  Device memory. */
+NNSB_API int nnsb_pad_launch (nnsb_stream * s, const void *d_src, void *d_dst,
+    size_t row_bytes, size_t dst_pitch, size_t rows);
+/* pitched D2H: the same padding done by the copy engine on the way to a host video buffer
+ * (padding bytes of the host buffer are left untouched) */
+NNSB_API int nnsb_d2h_2d_async (nnsb_stream * s, void *dst_host, size_t dst_pitch,
+    const void *src_dev, size_t src_pitch, size_t row_bytes, size_t rows);
+
 /* ---------------------------------------------------------------------------------------
  * Element mirrors.  GStreamer is not available in the build image, so the GObject /
  * GstBaseTransform surface of the two elements is exposed as plain functions with the same
@@ -422,6 +432,27 @@ NNSB_API int nnsb_aggregator_chain (nnsb_aggregator * a, const nnsb_memory * in,
     const nnsb_buffer_time * t_in, nnsb_memory * outs, nnsb_buffer_time * t_outs, uint32_t max_out,
     uint32_t *n_out);
 NNSB_API int nnsb_aggregator_kernel_launches (nnsb_aggregator * a, uint64_t *count);
+
+/* ---------------------------------------------------------------------------------------
+ * tensor_decoder mode=direct_video mirror: the GstTensorDecoderDef
+ * callbacks of ext/nnstreamer/tensor_decoder/tensordec-directvideo.c.
+ * ------------------------------------------------------------------------------------- */
+typedef struct nnsb_direct_video nnsb_direct_video;
+NNSB_API int nnsb_direct_video_new (int device_id, nnsb_direct_video ** out);      /* dv_init :102 */
+NNSB_API int nnsb_direct_video_free (nnsb_direct_video * dv);                       /* dv_exit :118 */
+/* dv_setOption, :126-158: option 0 (= "option1") is the video format name; returns 1 (TRUE)
+ * or 0 (FALSE) like the callback */
+NNSB_API int nnsb_direct_video_set_option (nnsb_direct_video * dv, int op_num, const char *param);
+/* dv_getOutCaps, :161-262: video/x-raw caps for the first tensor of `config` */
+NNSB_API int nnsb_direct_video_get_out_caps (nnsb_direct_video * dv, const nnsb_tensors_config * config,
+    char *caps, size_t capslen);
+/* dv_getTransformSize / _get_video_xraw_bufsize, :265-287 */
+NNSB_API size_t nnsb_direct_video_transform_size (const nnsb_tensors_config * config);
+/* dv_decode, :290-349.  `in` = the first tensor (uint8, host or device).  If out->data is set
+ * and out->size equals the video buffer size that memory is filled (host: pitched D2H, device:
+ * pad kernel), else a device memory is allocated (owned).  Returns a NNSB_FLOW_* code. */
+NNSB_API int nnsb_direct_video_decode (nnsb_direct_video * dv, const nnsb_tensors_config * config,
+    const nnsb_memory * in, nnsb_memory * out);
 
 /* No counterpart in the reference (its CPU element simply mallocs).  The same stand kernels
  * as nnsb_plan_launch(), for callers that must not allocate while frames are flowing: a

@@ -6,8 +6,8 @@ this package only mirrors the reference element's interface on top of that C-ABI
 from . import _lib  # noqa: F401
 from ._lib import NnsbError, lib  # noqa: F401
 from .device import Device, Plan  # noqa: F401
-from .element import (BatchQueue, DeviceMemory, TensorAggregator, TensorConverter,  # noqa: F401
-                      TensorTransform, device_memory)
+from .element import (BatchQueue, DeviceMemory, DirectVideoDecoder, TensorAggregator,  # noqa: F401
+                      TensorConverter, TensorTransform, device_memory)
 
 __all__ = ["Device", "Plan", "NnsbError", "lib", "TensorTransform", "TensorConverter",
-           "TensorAggregator", "BatchQueue", "DeviceMemory"]
+           "TensorAggregator", "DirectVideoDecoder", "BatchQueue", "DeviceMemory"]

@@ -184,6 +184,16 @@ _PROTOS = {
                                         C.POINTER(Memory), C.POINTER(BufferTime), C.c_uint32,
                                         C.POINTER(C.c_uint32)]),
     "nnsb_aggregator_kernel_launches": (C.c_int, [_VP, C.POINTER(C.c_uint64)]),
+    "nnsb_pad_launch": (C.c_int, [_VP, _VP, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),
+    "nnsb_d2h_2d_async": (C.c_int, [_VP, _VP, C.c_size_t, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),
+    "nnsb_direct_video_new": (C.c_int, [C.c_int, C.POINTER(_VP)]),
+    "nnsb_direct_video_free": (C.c_int, [_VP]),
+    "nnsb_direct_video_set_option": (C.c_int, [_VP, C.c_int, C.c_char_p]),
+    "nnsb_direct_video_get_out_caps": (C.c_int, [_VP, C.POINTER(TensorsConfig), C.c_char_p,
+                                                 C.c_size_t]),
+    "nnsb_direct_video_transform_size": (C.c_size_t, [C.POINTER(TensorsConfig)]),
+    "nnsb_direct_video_decode": (C.c_int, [_VP, C.POINTER(TensorsConfig), C.POINTER(Memory),
+                                           C.POINTER(Memory)]),
     "nnsb_queue_create": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(_VP)]),
     "nnsb_queue_destroy": (C.c_int, [_VP]),
     "nnsb_queue_push": (C.c_int, [_VP, _VP, C.c_int, C.POINTER(C.c_int)]),

@@ -22,6 +22,8 @@
  *            rows of row_bytes at pitch RU4 (row_bytes) -> dense.  Rows are 1..3 bytes off
  *            word alignment, so each thread assembles aligned 16-byte output chunks from
  *            aligned 4-byte source words with funnel shifts.
+ *  pad     : the inverse, tensor_decoder direct_video (tensordec-directvideo.c:326-339):
+ *            dense rows -> pitch RU4 (row_bytes), padding bytes written as zero.
  *
  * Algorithmic bytes: 2 * es per element (permute, copy), 2 * row_bytes per row (strip).
  */
@@ -507,86 +509,116 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
 }
 
 /* ------------------------------------------------------------------------------------- */
-/* strip                                                                                   */
+/* strip / pad: rows re-pitched                                                            */
 /* ------------------------------------------------------------------------------------- */
 constexpr int STRIP_THREADS = 256;
 
-/* 4 source bytes starting at byte offset `s` (any alignment) from word-aligned memory */
-__device__ __forceinline__ uint32_t
-load_unaligned_u32 (const unsigned char *base, uint64_t s)
-{
-  const uint32_t *w = reinterpret_cast<const uint32_t *> (base + (s & ~3ull));
-  const uint32_t sh = (uint32_t) (s & 3) * 8;
-  const uint32_t lo = __ldg (w);
-  if (sh == 0)
-    return lo;
-  const uint32_t hi = __ldg (w + 1);
-  return __funnelshift_r (lo, hi, sh);
-}
-
-/* word path: dst 16-byte aligned, src 4-byte aligned, pitch % 4 == 0, row_bytes >= 4 */
+/* `rows` rows of row_bytes bytes move from pitch ps to pitch pd >= row_bytes; bytes
+ * [row_bytes, pd) of every destination row are written as zero.
+ *   strip (gsttensor_converter.c:1087-1100): ps = RU4 (row_bytes), pd = row_bytes
+ *   pad   (tensordec-directvideo.c:326-339): ps = row_bytes,        pd = RU4 (row_bytes)
+ * A thread owns aligned 16-byte destination chunks; its (row, col) advances by a constant
+ * step, so the loop holds no division.  A chunk that lies inside one row's payload is
+ * assembled from five aligned source words with funnel shifts (the source is 0..3 bytes off
+ * word alignment); the few chunks that touch a row end or the padding go byte by byte. */
 __global__ void __launch_bounds__ (STRIP_THREADS)
-strip_kernel_w (const unsigned char *__restrict__ src, unsigned char *__restrict__ dst,
-    uint32_t row_bytes, uint64_t pitch, uint64_t total, uint64_t src_bytes)
+repitch_kernel (const unsigned char *__restrict__ src, unsigned char *__restrict__ dst,
+    uint32_t row_bytes, uint64_t ps, uint32_t pd, uint64_t total_dst, uint64_t src_bytes,
+    uint32_t step_row, uint32_t step_col)
 {
-  const uint64_t n_chunks = total / 16;
   const uint64_t tid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-  const uint64_t nthreads = (uint64_t) gridDim.x * blockDim.x;
-  for (uint64_t i = tid; i < n_chunks; i += nthreads) {
-    const uint64_t o = i * 16;
-    uint64_t row = o / row_bytes;
-    uint32_t col = (uint32_t) (o - row * row_bytes);
+  const uint64_t step = ((uint64_t) gridDim.x * blockDim.x) * 16;
+  const uint64_t n_chunk_bytes = total_dst & ~15ull;
+  uint64_t o = tid * 16;
+  uint64_t row = o / pd;
+  uint32_t col = (uint32_t) (o - row * pd);
+  for (; o < n_chunk_bytes; o += step) {
     uint32_t w[4];
+    const uint64_t s = row * ps + col;
+    const uint64_t base = s & ~3ull;
+    if (col + 16 <= row_bytes && base + 20 <= src_bytes) {
+      const uint32_t *p = reinterpret_cast<const uint32_t *> (src + base);
+      const uint32_t sh = (uint32_t) (s & 3) * 8;
+      uint32_t v[5];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-      if (col + 4 <= row_bytes) {
-        const uint64_t s = row * pitch + col;
-        /* the second word of an unaligned read may be the padding after the last row */
-        if (s + 8 <= src_bytes || (s & 3) == 0) {
-          w[k] = load_unaligned_u32 (src, s);
-        } else {
-          w[k] = (uint32_t) src[s] | ((uint32_t) src[s + 1] << 8) | ((uint32_t) src[s + 2] << 16)
-              | ((uint32_t) src[s + 3] << 24);
-        }
-        col += 4;
-        if (col == row_bytes) {
-          col = 0;
-          row++;
-        }
-      } else {
-        /* the word straddles a row boundary: byte by byte */
-        uint32_t v = 0;
+      for (int k = 0; k < 5; k++)
+        v[k] = __ldg (p + k);
+#pragma unroll
+      for (int k = 0; k < 4; k++)
+        w[k] = __funnelshift_r (v[k], v[k + 1], sh);    /* sh == 0: v[k] */
+    } else {
+      uint64_t r = row;
+      uint32_t c = col;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        uint32_t x = 0;
 #pragma unroll
         for (int b = 0; b < 4; b++) {
-          v |= (uint32_t) src[row * pitch + col] << (8 * b);
-          if (++col == row_bytes) {
-            col = 0;
-            row++;
+          if (c < row_bytes)
+            x |= (uint32_t) src[r * ps + c] << (8 * b);
+          if (++c == pd) {
+            c = 0;
+            r++;
           }
         }
-        w[k] = v;
+        w[k] = x;
       }
     }
     st_stream<16> (dst + o, w);
+    col += step_col;
+    row += step_row;
+    if (col >= pd) {
+      col -= pd;
+      row++;
+    }
   }
-  /* last (total % 16) bytes */
-  for (uint64_t b = n_chunks * 16 + tid; b < total; b += nthreads) {
-    const uint64_t row = b / row_bytes;
-    dst[b] = src[row * pitch + (b - row * row_bytes)];
+  /* last (total_dst % 16) bytes */
+  for (uint64_t b = n_chunk_bytes + tid; b < total_dst; b += step / 16) {
+    const uint64_t r = b / pd;
+    const uint32_t c = (uint32_t) (b - r * pd);
+    dst[b] = c < row_bytes ? src[r * ps + c] : (unsigned char) 0;
   }
 }
 
-/* byte path: any alignment */
+/* any alignment */
 __global__ void __launch_bounds__ (STRIP_THREADS)
-strip_kernel_b (const unsigned char *__restrict__ src, unsigned char *__restrict__ dst,
-    uint64_t row_bytes, uint64_t pitch, uint64_t total)
+repitch_kernel_b (const unsigned char *__restrict__ src, unsigned char *__restrict__ dst,
+    uint64_t row_bytes, uint64_t ps, uint64_t pd, uint64_t total_dst)
 {
   const uint64_t tid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t nthreads = (uint64_t) gridDim.x * blockDim.x;
-  for (uint64_t b = tid; b < total; b += nthreads) {
-    const uint64_t row = b / row_bytes;
-    dst[b] = src[row * pitch + (b - row * row_bytes)];
+  for (uint64_t b = tid; b < total_dst; b += nthreads) {
+    const uint64_t r = b / pd;
+    const uint64_t c = b - r * pd;
+    dst[b] = c < row_bytes ? src[r * ps + c] : (unsigned char) 0;
   }
+}
+
+static int
+launch_repitch (const void *src, void *dst, size_t row_bytes, size_t ps, size_t pd, size_t rows,
+    const LaunchCfg &cfg, cudaStream_t stream)
+{
+  const uint64_t total_dst = (uint64_t) pd * (rows - 1) + (pd > row_bytes ? pd : row_bytes);
+  const uint64_t src_bytes = (uint64_t) ps * (rows - 1) + row_bytes;
+  const bool word_ok = ((uintptr_t) dst % 16 == 0) && ((uintptr_t) src % 4 == 0)
+      && row_bytes >= 16 && pd <= 0x7fffffffull;
+  const uint64_t work = word_ok ? (total_dst + 15) / 16 : total_dst;
+  uint64_t blocks = (work + STRIP_THREADS - 1) / STRIP_THREADS;
+  const uint64_t cap = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 64);
+  if (blocks > cap)
+    blocks = cap;
+  if (blocks == 0)
+    blocks = 1;
+  if (word_ok) {
+    const uint64_t step = blocks * STRIP_THREADS * 16;
+    repitch_kernel<<<(unsigned int) blocks, STRIP_THREADS, 0, stream>>> ((const unsigned char *) src,
+        (unsigned char *) dst, (uint32_t) row_bytes, ps, (uint32_t) pd, total_dst, src_bytes,
+        (uint32_t) (step / pd), (uint32_t) (step % pd));
+  } else {
+    repitch_kernel_b<<<(unsigned int) blocks, STRIP_THREADS, 0, stream>>> ((const unsigned char *) src,
+        (unsigned char *) dst, row_bytes, ps, pd, total_dst);
+  }
+  return (int) cudaGetLastError ();
 }
 
 int launch_strip (const void *src, void *dst, size_t row_bytes, size_t src_pitch, size_t rows,
@@ -598,24 +630,19 @@ int launch_strip (const void *src, void *dst, size_t row_bytes, size_t src_pitch
     return (int) cudaErrorInvalidValue;
   if (src_pitch == row_bytes)
     return launch_copy (src, dst, row_bytes * rows, cfg, stream);
-  const uint64_t total = (uint64_t) row_bytes * rows;
-  const uint64_t src_bytes = (uint64_t) src_pitch * (rows - 1) + row_bytes;
-  const bool word_ok = ((uintptr_t) dst % 16 == 0) && ((uintptr_t) src % 4 == 0)
-      && (src_pitch % 4 == 0) && row_bytes >= 4 && row_bytes <= 0xffffffffull;
-  const uint64_t work = word_ok ? (total + 15) / 16 : total;
-  uint64_t blocks = (work + STRIP_THREADS - 1) / STRIP_THREADS;
-  const uint64_t cap = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 8);
-  if (blocks > cap)
-    blocks = cap;
-  if (blocks == 0)
-    blocks = 1;
-  if (word_ok)
-    strip_kernel_w<<<(unsigned int) blocks, STRIP_THREADS, 0, stream>>> ((const unsigned char *) src,
-        (unsigned char *) dst, (uint32_t) row_bytes, src_pitch, total, src_bytes);
-  else
-    strip_kernel_b<<<(unsigned int) blocks, STRIP_THREADS, 0, stream>>> ((const unsigned char *) src,
-        (unsigned char *) dst, row_bytes, src_pitch, total);
-  return (int) cudaGetLastError ();
+  return launch_repitch (src, dst, row_bytes, src_pitch, row_bytes, rows, cfg, stream);
+}
+
+int launch_pad (const void *src, void *dst, size_t row_bytes, size_t dst_pitch, size_t rows,
+    const LaunchCfg &cfg, cudaStream_t stream)
+{
+  if (rows == 0 || row_bytes == 0)
+    return 0;
+  if (dst_pitch < row_bytes)
+    return (int) cudaErrorInvalidValue;
+  if (dst_pitch == row_bytes)
+    return launch_copy (src, dst, row_bytes * rows, cfg, stream);
+  return launch_repitch (src, dst, row_bytes, row_bytes, dst_pitch, rows, cfg, stream);
 }
 
 }  // namespace nnsb

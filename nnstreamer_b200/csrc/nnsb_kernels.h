@@ -113,5 +113,10 @@ int launch_plane (bool to_planar, int channels, int es, uint64_t pixels, uint64_
 int launch_strip (const void *src, void *dst, size_t row_bytes, size_t src_pitch, size_t rows,
     const LaunchCfg & cfg, cudaStream_t stream);
 
+/* K9: row padding, the inverse of K8 (tensordec-directvideo.c:326-339); the dst_pitch -
+ * row_bytes padding bytes of every row are written as zero */
+int launch_pad (const void *src, void *dst, size_t row_bytes, size_t dst_pitch, size_t rows,
+    const LaunchCfg & cfg, cudaStream_t stream);
+
 }  // namespace nnsb
 #endif

@@ -998,6 +998,32 @@ nnsb_plan_stand_stats (nnsb_plan * plan, nnsb_stream * s, uint32_t batch, double
 }
 
 extern "C" int
+nnsb_pad_launch (nnsb_stream * s, const void *d_src, void *d_dst, size_t row_bytes,
+    size_t dst_pitch, size_t rows)
+{
+  STREAM_PROLOGUE ("nnsb_pad_launch");
+  if (!d_src || !d_dst)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_pad_launch: null device pointer");
+  int err = launch_pad (d_src, d_dst, row_bytes, dst_pitch, rows, cfg_of (s->ctx), s->s);
+  if (err)
+    return nnsb_set_error (NNSB_ECUDA, "pad launch failed: %s",
+        cudaGetErrorString ((cudaError_t) err));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_d2h_2d_async (nnsb_stream * s, void *dst_host, size_t dst_pitch, const void *src_dev,
+    size_t src_pitch, size_t row_bytes, size_t rows)
+{
+  STREAM_PROLOGUE ("nnsb_d2h_2d_async");
+  if (rows == 0 || row_bytes == 0)
+    return NNSB_OK;
+  CUDA_TRY (cudaMemcpy2DAsync (dst_host, dst_pitch, src_dev, src_pitch, row_bytes, rows,
+          cudaMemcpyDeviceToHost, s->s));
+  return NNSB_OK;
+}
+
+extern "C" int
 nnsb_strip_launch (nnsb_stream * s, const void *d_src, void *d_dst, size_t row_bytes,
     size_t src_pitch, size_t rows)
 {

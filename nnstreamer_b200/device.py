@@ -118,6 +118,11 @@ class Device:
                                             C.c_void_p(d_dst), row_bytes, src_pitch, rows))
 
 
+    def pad(self, d_src, d_dst, row_bytes, dst_pitch, rows, stream=None):
+        L.check(self._lib.nnsb_pad_launch(stream or self.stream, C.c_void_p(d_src),
+                                          C.c_void_p(d_dst), row_bytes, dst_pitch, rows))
+
+
 class Plan:
     """nnsb_plan: parsed (mode, option) bound to one input tensor info."""
 

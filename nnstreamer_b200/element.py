@@ -340,6 +340,71 @@ class TensorAggregator:
         return int(c.value)
 
 
+class DirectVideoDecoder:
+    """tensor_decoder mode=direct_video (tensordec-directvideo.c): tensor -> video/x-raw frame,
+    rows padded to a multiple of 4 bytes."""
+
+    def __init__(self, device_id=0, option1=None):
+        self._lib = L.lib()
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_direct_video_new(int(device_id), C.byref(self.handle)))
+        if option1 is not None and not self.set_option(0, option1):
+            raise ValueError("direct_video: unknown format %r" % (option1,))
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_direct_video_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_option(self, op_num, param):
+        return bool(self._lib.nnsb_direct_video_set_option(
+            self.handle, int(op_num), None if param is None else str(param).encode()))
+
+    @staticmethod
+    def make_config(channels, width, height, rate=(0, 1), type_name="uint8"):
+        cfg = L.TensorsConfig()
+        cfg.num_tensors = 1
+        cfg.info[0] = L.make_info(type_name, [channels, width, height, 1])
+        cfg.rate_n, cfg.rate_d = rate
+        return cfg
+
+    def out_caps(self, cfg):
+        buf = C.create_string_buffer(_CAPS_BUF)
+        code = self._lib.nnsb_direct_video_get_out_caps(self.handle, C.byref(cfg), buf, _CAPS_BUF)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def transform_size(self, cfg):
+        return self._lib.nnsb_direct_video_transform_size(C.byref(cfg))
+
+    def decode(self, cfg, tensor, out=None):
+        """tensor: numpy uint8 array or DeviceMemory.  out: None (a device memory is allocated),
+        a numpy uint8 array of transform_size bytes, or a DeviceMemory to fill.  Returns
+        (flow, DeviceMemory or the numpy array)."""
+        if isinstance(tensor, DeviceMemory):
+            m = tensor.mem
+        else:
+            a = np.ascontiguousarray(tensor, dtype=np.uint8)
+            m = _host_memory(a)
+        if out is None:
+            o = L.Memory()
+        elif isinstance(out, DeviceMemory):
+            o = out.mem
+        else:
+            o = _host_memory(out)
+        flow = self._lib.nnsb_direct_video_decode(self.handle, C.byref(cfg), C.byref(m), C.byref(o))
+        if out is None:
+            return flow, (DeviceMemory(o) if flow == 0 else None)
+        return flow, out
+
+
 class BatchQueue:
     """nnsb_queue: groups frames so that one launch covers `batch` tensors."""
 

@@ -677,3 +677,23 @@ oracle_aggregator_concat (const void *src, void *dst, uint64_t frame_size, uint3
   } while (src_idx < frame_size);
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------- */
+/* tensor_decoder direct_video, dv_decode (tensordec-directvideo.c:322-339): dense rows of  */
+/* dim[0]*dim[1] bytes -> rows padded to a multiple of 4.  The reference leaves the padding */
+/* bytes uninitialised; dst is expected to be pre-filled by the caller (tests use zero).    */
+/* ------------------------------------------------------------------------------------- */
+int
+oracle_direct_video (const void *src, void *dst, uint32_t color, uint32_t width, uint32_t height)
+{
+  const size_t row = (size_t) color * width;
+  const size_t pitch = ((row - 1) / 4 + 1) * 4;
+  uint32_t h;
+  if (row % 4 == 0) {
+    memcpy (dst, src, row * height);
+    return 0;
+  }
+  for (h = 0; h < height; h++)
+    memcpy ((char *) dst + h * pitch, (const char *) src + h * row, row);
+  return 0;
+}

@@ -145,6 +145,7 @@ class Port:
 
         L.oracle_aggregator_concat.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32,
                                                C.c_uint64]
+        L.oracle_direct_video.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
 
     def typecast(self, x, out_type, accel=False):
         x = np.ascontiguousarray(x)
@@ -212,6 +213,14 @@ class Port:
         self.lib.oracle_stride_strip(_ptr(src), _ptr(out), color, width, height)
         return out
 
+
+    def direct_video(self, src, color, width, height):
+        """dv_decode (tensordec-directvideo.c:322-339); padding bytes come back as zero."""
+        src = np.ascontiguousarray(src, dtype=np.uint8)
+        pitch = (color * width + 3) // 4 * 4
+        out = np.zeros(pitch * height, dtype=np.uint8)
+        self.lib.oracle_direct_video(_ptr(src), _ptr(out), color, width, height)
+        return out
 
     def aggregator_concat(self, src, frame_size, frames_out, block_size):
         """gst_tensor_aggregator_concat (gsttensor_aggregator.c:768-787) on raw bytes."""
