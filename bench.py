@@ -418,6 +418,24 @@ def multi_stream_chain(device_id, n_streams=8, frames_per_stream=40):
     return out
 
 
+def native_stream_chain(device_id, n_streams=8, frames_per_stream=300):
+    """The same chain driven by tools/stream_bench (native threads through the C-ABI): what the
+    element mirrors cost without the Python interpreter in the per-frame loop."""
+    exe = os.path.join(ROOT, "tools", "stream_bench")
+    if not os.path.isfile(exe):
+        return {"unavailable": "tools/stream_bench not built (python -c 'import __graft_entry__ as g; g.build()')"}
+    out = {}
+    for mode, key in (("resident", "device_resident"), ("h2d", "h2d_per_frame")):
+        try:
+            r = subprocess.run([exe, str(device_id), str(n_streams), str(frames_per_stream), mode],
+                               capture_output=True, text=True, timeout=300)
+            out[key] = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else \
+                {"error": r.stderr.strip()[-300:]}
+        except Exception as exc:                    # noqa: BLE001
+            out[key] = {"error": str(exc)}
+    return out
+
+
 def run_b200(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -537,6 +555,7 @@ def run_b200(args):
                 extras = extra_kernels(dev, peak, with_cpu=not args.no_cpu_baseline)
                 extras["chain_8_streams_1080p_converter_typecast_arith_transpose"] = \
                     multi_stream_chain(local_rank)
+                extras["chain_8_streams_1080p_native_driver"] = native_stream_chain(local_rank)
 
     if rank == 0:
         ms_step = ms_dev / args.steps

@@ -933,6 +933,14 @@ nnsb_converter_chain (nnsb_converter * c, const nnsb_memory * frame, nnsb_memory
     nnsb_set_error (NNSB_FLOW_ERROR, "tensor_converter: frame of %zu bytes, %zu expected", frame->size, c->frame_size);
     return NNSB_FLOW_ERROR;
   }
+  if (c->frames_per_tensor == 1 && frame->on_device && !c->remove_padding) {
+    /* nothing to strip, nothing to batch: the frame IS the tensor (the reference pushes the
+     * incoming buffer itself when remove_padding is FALSE, gsttensor_converter.c:1062,1107-1109) */
+    *out = *frame;
+    out->owned = 0;
+    *produced = 1;
+    return NNSB_FLOW_OK;
+  }
   const size_t batch_bytes = c->dense_frame * c->frames_per_tensor;
   if (!c->d_batch) {
     if (nnsb_dev_alloc (c->ctx, batch_bytes, &c->d_batch) != NNSB_OK)
