@@ -295,6 +295,12 @@ NNSB_API int nnsb_pad_launch (nnsb_stream * s, const void *d_src, void *d_dst,
 NNSB_API int nnsb_d2h_2d_async (nnsb_stream * s, void *dst_host, size_t dst_pitch,
     const void *src_dev, size_t src_pitch, size_t row_bytes, size_t rows);
 
+/* tensor_merge mode=linear, gsttensor_merge.c:506-586: output row r = block r of every input
+ * back to back; block_bytes[k] = element size * prod (dim_k[0..axis]), rows = prod of the dims
+ * above the axis.  n <= 16, device pointers. */
+NNSB_API int nnsb_merge_launch (nnsb_stream * s, uint32_t n, const void *const *d_in,
+    const uint64_t *block_bytes, void *d_out, uint64_t rows);
+
 /* ---------------------------------------------------------------------------------------
  * Element mirrors.  GStreamer is not available in the build image, so the GObject /
  * GstBaseTransform surface of the two elements is exposed as plain functions with the same
@@ -453,6 +459,40 @@ NNSB_API size_t nnsb_direct_video_transform_size (const nnsb_tensors_config * co
  * pad kernel), else a device memory is allocated (owned).  Returns a NNSB_FLOW_* code. */
 NNSB_API int nnsb_direct_video_decode (nnsb_direct_video * dv, const nnsb_tensors_config * config,
     const nnsb_memory * in, nnsb_memory * out);
+
+/* ---------------------------------------------------------------------------------------
+ * tensor_merge / tensor_split data paths.
+ * ------------------------------------------------------------------------------------- */
+typedef struct nnsb_merge nnsb_merge;
+NNSB_API int nnsb_merge_new (int device_id, nnsb_merge ** out);
+NNSB_API int nnsb_merge_free (nnsb_merge * m);
+/* properties of gsttensor_merge.c:159-185: "mode" (linear), "option" ("0".."3" = merge axis),
+ * "silent", "sync-mode", "sync-option" (stored; the time synchronisation is not mirrored) */
+NNSB_API int nnsb_merge_set_property (nnsb_merge * m, const char *name, const char *value);
+NNSB_API int nnsb_merge_get_property (nnsb_merge * m, const char *name, char *buf, size_t buflen);
+/* gst_tensor_merge_get_merged_config, :380-427: the fixed caps of the n sink pads in, the
+ * source caps out */
+NNSB_API int nnsb_merge_set_caps (nnsb_merge * m, uint32_t n, const char *const *caps, char *out,
+    size_t outlen);
+NNSB_API int nnsb_merge_get_config (nnsb_merge * m, nnsb_tensors_config * cfg);
+/* gst_tensor_merge_generate_mem, :463-600: one memory per sink pad (host or device) in, the
+ * merged tensor (device, owned) out.  Returns a NNSB_FLOW_* code. */
+NNSB_API int nnsb_merge_chain (nnsb_merge * m, const nnsb_memory * in, uint32_t n, nnsb_memory * out);
+
+typedef struct nnsb_split nnsb_split;
+NNSB_API int nnsb_split_new (int device_id, nnsb_split ** out);
+NNSB_API int nnsb_split_free (nnsb_split * s);
+/* gst_tensor_split_set_property / _get_property, gsttensor_split.c:566-700: "tensorseg"
+ * ("2:100:100,1:100:100"), "tensorpick" ("0,2"), "silent" */
+NNSB_API int nnsb_split_set_property (nnsb_split * s, const char *name, const char *value);
+NNSB_API int nnsb_split_get_property (nnsb_split * s, const char *name, char *buf, size_t buflen);
+NNSB_API int nnsb_split_set_caps (nnsb_split * s, const char *caps);
+NNSB_API int nnsb_split_num_outputs (nnsb_split * s);
+/* caps of source pad src_<idx> (gst_tensor_split_get_tensor_pad, :345-361) */
+NNSB_API int nnsb_split_get_out_caps (nnsb_split * s, uint32_t idx, char *out, size_t outlen);
+/* gst_tensor_split_chain, :455-530: one device memory (owned) per picked segment */
+NNSB_API int nnsb_split_chain (nnsb_split * s, const nnsb_memory * in, nnsb_memory * outs,
+    uint32_t max_out, uint32_t *n_out);
 
 /* No counterpart in the reference (its CPU element simply mallocs).  The same stand kernels
  * as nnsb_plan_launch(), for callers that must not allocate while frames are flowing: a

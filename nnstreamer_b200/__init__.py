@@ -7,7 +7,8 @@ from . import _lib  # noqa: F401
 from ._lib import NnsbError, lib  # noqa: F401
 from .device import Device, Plan  # noqa: F401
 from .element import (BatchQueue, DeviceMemory, DirectVideoDecoder, TensorAggregator,  # noqa: F401
-                      TensorConverter, TensorTransform, device_memory)
+                      TensorConverter, TensorMerge, TensorSplit, TensorTransform, device_memory)
 
 __all__ = ["Device", "Plan", "NnsbError", "lib", "TensorTransform", "TensorConverter",
-           "TensorAggregator", "DirectVideoDecoder", "BatchQueue", "DeviceMemory"]
+           "TensorAggregator", "DirectVideoDecoder", "TensorMerge", "TensorSplit", "BatchQueue",
+           "DeviceMemory"]

@@ -194,6 +194,24 @@ _PROTOS = {
     "nnsb_direct_video_transform_size": (C.c_size_t, [C.POINTER(TensorsConfig)]),
     "nnsb_direct_video_decode": (C.c_int, [_VP, C.POINTER(TensorsConfig), C.POINTER(Memory),
                                            C.POINTER(Memory)]),
+    "nnsb_merge_launch": (C.c_int, [_VP, C.c_uint32, C.POINTER(_VP), C.POINTER(C.c_uint64), _VP,
+                                    C.c_uint64]),
+    "nnsb_merge_new": (C.c_int, [C.c_int, C.POINTER(_VP)]),
+    "nnsb_merge_free": (C.c_int, [_VP]),
+    "nnsb_merge_set_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p]),
+    "nnsb_merge_get_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "nnsb_merge_set_caps": (C.c_int, [_VP, C.c_uint32, C.POINTER(C.c_char_p), C.c_char_p, C.c_size_t]),
+    "nnsb_merge_get_config": (C.c_int, [_VP, C.POINTER(TensorsConfig)]),
+    "nnsb_merge_chain": (C.c_int, [_VP, C.POINTER(Memory), C.c_uint32, C.POINTER(Memory)]),
+    "nnsb_split_new": (C.c_int, [C.c_int, C.POINTER(_VP)]),
+    "nnsb_split_free": (C.c_int, [_VP]),
+    "nnsb_split_set_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p]),
+    "nnsb_split_get_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "nnsb_split_set_caps": (C.c_int, [_VP, C.c_char_p]),
+    "nnsb_split_num_outputs": (C.c_int, [_VP]),
+    "nnsb_split_get_out_caps": (C.c_int, [_VP, C.c_uint32, C.c_char_p, C.c_size_t]),
+    "nnsb_split_chain": (C.c_int, [_VP, C.POINTER(Memory), C.POINTER(Memory), C.c_uint32,
+                                   C.POINTER(C.c_uint32)]),
     "nnsb_queue_create": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(_VP)]),
     "nnsb_queue_destroy": (C.c_int, [_VP]),
     "nnsb_queue_push": (C.c_int, [_VP, _VP, C.c_int, C.POINTER(C.c_int)]),

@@ -645,4 +645,138 @@ int launch_pad (const void *src, void *dst, size_t row_bytes, size_t dst_pitch, 
   return launch_repitch (src, dst, row_bytes, row_bytes, dst_pitch, rows, cfg, stream);
 }
 
+/* ------------------------------------------------------------------------------------- */
+/* merge: tensor_merge mode=linear (gsttensor_merge.c:506-586)                             */
+/* ------------------------------------------------------------------------------------- */
+/* out row r = [ in_0 block r | in_1 block r | ... ], block k is blk[k] bytes (the input's extent
+ * along the merge axis and everything below it), rows = product of the dims above the axis.
+ * Same scheme as repitch_kernel: a thread owns aligned 16-byte output chunks, (row, col) advance
+ * without a division, a chunk inside one block is assembled from five aligned source words. */
+struct MergeDev
+{
+  int n;
+  const unsigned char *in[NNSB_MERGE_MAX];
+  uint32_t blk[NNSB_MERGE_MAX];
+  uint32_t off[NNSB_MERGE_MAX + 1];     /* prefix sums of blk; off[n] = row bytes */
+  uint64_t in_bytes[NNSB_MERGE_MAX];
+};
+
+__device__ __forceinline__ int
+merge_find (const MergeDev &m, uint32_t col)
+{
+  int k = 0;
+  while (k + 1 < m.n && col >= m.off[k + 1])
+    k++;
+  return k;
+}
+
+template <bool WORDS>
+__global__ void __launch_bounds__ (STRIP_THREADS)
+merge_kernel (unsigned char *__restrict__ dst, const __grid_constant__ MergeDev m, uint64_t total,
+    uint32_t step_row, uint32_t step_col)
+{
+  const uint32_t S = m.off[m.n];
+  const uint64_t tid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t nthreads = (uint64_t) gridDim.x * blockDim.x;
+  const uint64_t n_chunk_bytes = WORDS ? (total & ~15ull) : 0;
+  if (WORDS) {
+    const uint64_t step = nthreads * 16;
+    uint64_t o = tid * 16;
+    uint64_t row = o / S;
+    uint32_t col = (uint32_t) (o - row * S);
+    for (; o < n_chunk_bytes; o += step) {
+      uint32_t w[4];
+      const int k = merge_find (m, col);
+      const uint64_t s = row * m.blk[k] + (col - m.off[k]);
+      const uint64_t base = s & ~3ull;
+      if (col + 16 <= m.off[k + 1] && base + 20 <= m.in_bytes[k]) {
+        const uint32_t *p = reinterpret_cast<const uint32_t *> (m.in[k] + base);
+        const uint32_t sh = (uint32_t) (s & 3) * 8;
+        uint32_t v[5];
+#pragma unroll
+        for (int j = 0; j < 5; j++)
+          v[j] = __ldg (p + j);
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+          w[j] = __funnelshift_r (v[j], v[j + 1], sh);
+      } else {
+        uint64_t r = row;
+        uint32_t c = col;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          uint32_t x = 0;
+#pragma unroll
+          for (int b = 0; b < 4; b++) {
+            const int kk = merge_find (m, c);
+            x |= (uint32_t) m.in[kk][r * m.blk[kk] + (c - m.off[kk])] << (8 * b);
+            if (++c == S) {
+              c = 0;
+              r++;
+            }
+          }
+          w[j] = x;
+        }
+      }
+      st_stream<16> (dst + o, w);
+      col += step_col;
+      row += step_row;
+      if (col >= S) {
+        col -= S;
+        row++;
+      }
+    }
+  }
+  for (uint64_t b = n_chunk_bytes + tid; b < total; b += nthreads) {
+    const uint64_t r = b / S;
+    const uint32_t c = (uint32_t) (b - r * S);
+    const int k = merge_find (m, c);
+    dst[b] = m.in[k][r * m.blk[k] + (c - m.off[k])];
+  }
+}
+
+int launch_merge (int n, const void *const *in, const uint64_t *block_bytes, void *out,
+    uint64_t rows, const LaunchCfg &cfg, cudaStream_t stream)
+{
+  if (n < 1 || n > NNSB_MERGE_MAX)
+    return (int) cudaErrorInvalidValue;
+  if (rows == 0)
+    return 0;
+  MergeDev m;
+  memset (&m, 0, sizeof (m));
+  m.n = n;
+  uint64_t S = 0;
+  bool words = (uintptr_t) out % 16 == 0;
+  for (int k = 0; k < n; k++) {
+    if (block_bytes[k] == 0 || block_bytes[k] > 0x7fffffffull)
+      return (int) cudaErrorInvalidValue;
+    m.in[k] = (const unsigned char *) in[k];
+    m.blk[k] = (uint32_t) block_bytes[k];
+    m.off[k] = (uint32_t) S;
+    m.in_bytes[k] = block_bytes[k] * rows;
+    S += block_bytes[k];
+    words = words && (uintptr_t) in[k] % 4 == 0;
+  }
+  if (S > 0x7fffffffull)
+    return (int) cudaErrorInvalidValue;
+  m.off[n] = (uint32_t) S;
+  if (n == 1)
+    return launch_copy (in[0], out, S * rows, cfg, stream);
+  const uint64_t total = S * rows;
+  const uint64_t work = words ? (total + 15) / 16 : total;
+  uint64_t blocks = (work + STRIP_THREADS - 1) / STRIP_THREADS;
+  const uint64_t cap = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 64);
+  if (blocks > cap)
+    blocks = cap;
+  if (blocks == 0)
+    blocks = 1;
+  const uint64_t step = blocks * STRIP_THREADS * 16;
+  if (words)
+    merge_kernel<true><<<(unsigned int) blocks, STRIP_THREADS, 0, stream>>> ((unsigned char *) out, m,
+        total, (uint32_t) (step / S), (uint32_t) (step % S));
+  else
+    merge_kernel<false><<<(unsigned int) blocks, STRIP_THREADS, 0, stream>>> ((unsigned char *) out, m,
+        total, 0, 0);
+  return (int) cudaGetLastError ();
+}
+
 }  // namespace nnsb

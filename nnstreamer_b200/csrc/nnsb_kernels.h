@@ -118,5 +118,11 @@ int launch_strip (const void *src, void *dst, size_t row_bytes, size_t src_pitch
 int launch_pad (const void *src, void *dst, size_t row_bytes, size_t dst_pitch, size_t rows,
     const LaunchCfg & cfg, cudaStream_t stream);
 
+/* K10: tensor_merge mode=linear (gsttensor_merge.c:506-586): output row r is the concatenation
+ * of block r of every input; block_bytes[k] = element size * prod (dim_k[0..axis]) */
+#define NNSB_MERGE_MAX 16
+int launch_merge (int n, const void *const *in, const uint64_t *block_bytes, void *out,
+    uint64_t rows, const LaunchCfg & cfg, cudaStream_t stream);
+
 }  // namespace nnsb
 #endif

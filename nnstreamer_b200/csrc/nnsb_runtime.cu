@@ -998,6 +998,23 @@ nnsb_plan_stand_stats (nnsb_plan * plan, nnsb_stream * s, uint32_t batch, double
 }
 
 extern "C" int
+nnsb_merge_launch (nnsb_stream * s, uint32_t n, const void *const *d_in, const uint64_t *block_bytes,
+    void *d_out, uint64_t rows)
+{
+  STREAM_PROLOGUE ("nnsb_merge_launch");
+  if (!d_in || !block_bytes || !d_out || n < 1 || n > NNSB_MERGE_MAX)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_merge_launch: invalid argument");
+  for (uint32_t k = 0; k < n; k++)
+    if (!d_in[k] || block_bytes[k] == 0)
+      return nnsb_set_error (NNSB_EINVAL, "nnsb_merge_launch: input %u is empty", k);
+  int err = launch_merge ((int) n, d_in, block_bytes, d_out, rows, cfg_of (s->ctx), s->s);
+  if (err)
+    return nnsb_set_error (NNSB_ECUDA, "merge launch failed: %s",
+        cudaGetErrorString ((cudaError_t) err));
+  return NNSB_OK;
+}
+
+extern "C" int
 nnsb_pad_launch (nnsb_stream * s, const void *d_src, void *d_dst, size_t row_bytes,
     size_t dst_pitch, size_t rows)
 {

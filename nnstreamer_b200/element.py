@@ -405,6 +405,131 @@ class DirectVideoDecoder:
         return flow, out
 
 
+class TensorMerge:
+    """tensor_merge mode=linear: N single-tensor pads concatenated along axis `option`."""
+
+    def __init__(self, device_id=0, **props):
+        self._lib = L.lib()
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_merge_new(int(device_id), C.byref(self.handle)))
+        for k, v in props.items():
+            self.set_property(k.replace("_", "-"), v)
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_merge_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_property(self, name, value):
+        if isinstance(value, bool):
+            value = "true" if value else "false"
+        L.check(self._lib.nnsb_merge_set_property(self.handle, name.encode(), str(value).encode()))
+
+    def get_property(self, name):
+        buf = C.create_string_buffer(256)
+        code = self._lib.nnsb_merge_get_property(self.handle, name.encode(), buf, 256)
+        if code == L.ENOENT:
+            return None
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def set_caps(self, caps_list):
+        arr = (C.c_char_p * len(caps_list))(*[c.encode() for c in caps_list])
+        buf = C.create_string_buffer(_CAPS_BUF)
+        code = self._lib.nnsb_merge_set_caps(self.handle, len(caps_list), arr, buf, _CAPS_BUF)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def chain(self, tensors):
+        """One memory per pad (numpy arrays or DeviceMemory); returns (flow, DeviceMemory)."""
+        n = len(tensors)
+        ins = (L.Memory * n)()
+        keep = []
+        for i, t in enumerate(tensors):
+            if isinstance(t, DeviceMemory):
+                ins[i] = t.mem
+            else:
+                a = np.ascontiguousarray(t)
+                keep.append(a)
+                ins[i] = _host_memory(a)
+        out = L.Memory()
+        flow = self._lib.nnsb_merge_chain(self.handle, ins, n, C.byref(out))
+        return flow, (DeviceMemory(out) if flow == 0 else None)
+
+
+class TensorSplit:
+    """tensor_split: tensorseg / tensorpick, one device memory per picked segment."""
+
+    def __init__(self, device_id=0, **props):
+        self._lib = L.lib()
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_split_new(int(device_id), C.byref(self.handle)))
+        for k, v in props.items():
+            self.set_property(k.replace("_", "-"), v)
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_split_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_property(self, name, value):
+        if isinstance(value, bool):
+            value = "true" if value else "false"
+        L.check(self._lib.nnsb_split_set_property(self.handle, name.encode(), str(value).encode()))
+
+    def get_property(self, name):
+        buf = C.create_string_buffer(1024)
+        code = self._lib.nnsb_split_get_property(self.handle, name.encode(), buf, 1024)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def set_caps(self, caps):
+        L.check(self._lib.nnsb_split_set_caps(self.handle, caps.encode()))
+
+    @property
+    def num_outputs(self):
+        return self._lib.nnsb_split_num_outputs(self.handle)
+
+    def out_caps(self, idx):
+        buf = C.create_string_buffer(_CAPS_BUF)
+        code = self._lib.nnsb_split_get_out_caps(self.handle, int(idx), buf, _CAPS_BUF)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def chain(self, tensor):
+        if isinstance(tensor, DeviceMemory):
+            m = tensor.mem
+        else:
+            a = np.ascontiguousarray(tensor)
+            m = _host_memory(a)
+        room = max(1, self.num_outputs)
+        outs = (L.Memory * room)()
+        n_out = C.c_uint32(0)
+        flow = self._lib.nnsb_split_chain(self.handle, C.byref(m), outs, room, C.byref(n_out))
+        mems = []
+        for i in range(n_out.value):
+            o = L.Memory()
+            C.memmove(C.byref(o), C.byref(outs[i]), C.sizeof(L.Memory))
+            mems.append(DeviceMemory(o))
+        return flow, mems
+
+
 class BatchQueue:
     """nnsb_queue: groups frames so that one launch covers `batch` tensors."""
 

@@ -697,3 +697,66 @@ oracle_direct_video (const void *src, void *dst, uint32_t color, uint32_t width,
     memcpy ((char *) dst + h * pitch, (const char *) src + h * row, row);
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------- */
+/* tensor_merge mode=linear, gst_tensor_merge_generate_mem (gsttensor_merge.c:506-586).   */
+/* dims: n x 4 (only rank 4 takes part, as in the reference); direction 0..3.             */
+/* ------------------------------------------------------------------------------------- */
+int
+oracle_merge_linear (int n, const void *const *in, const uint32_t *dims, uint64_t element_size,
+    int direction, void *out)
+{
+  const uint32_t *dim = dims;           /* outer loops run over the first tensor's dims */
+  char *outptr = (char *) out;
+  uint32_t i, j, l;
+  int k, jj;
+  uint64_t c, s;
+  switch (direction) {
+    case 0:
+      for (l = 0; l < dim[3]; l++)
+        for (i = 0; i < dim[2]; i++)
+          for (j = 0; j < dim[1]; j++)
+            for (k = 0; k < n; k++) {
+              c = dims[k * 4 + 0];
+              s = element_size * c;
+              memcpy (outptr, (const char *) in[k] + ((uint64_t) l * dim[2] * dim[1] + (uint64_t) i * dim[1] + j) * s, s);
+              outptr += s;
+            }
+      return 0;
+    case 1:
+      for (l = 0; l < dim[3]; l++)
+        for (i = 0; i < dim[2]; i++)
+          for (k = 0; k < n; k++) {
+            c = 1;
+            for (jj = 0; jj < 2; jj++)
+              c *= dims[k * 4 + jj];
+            s = element_size * c;
+            memcpy (outptr, (const char *) in[k] + ((uint64_t) l * dim[2] + i) * s, s);
+            outptr += s;
+          }
+      return 0;
+    case 2:
+      for (l = 0; l < dim[3]; l++)
+        for (k = 0; k < n; k++) {
+          c = 1;
+          for (jj = 0; jj < 3; jj++)
+            c *= dims[k * 4 + jj];
+          s = element_size * c;
+          memcpy (outptr, (const char *) in[k] + (uint64_t) l * s, s);
+          outptr += s;
+        }
+      return 0;
+    case 3:
+      for (k = 0; k < n; k++) {
+        c = 1;
+        for (jj = 0; jj < 4; jj++)
+          c *= dims[k * 4 + jj];
+        s = element_size * c;
+        memcpy (outptr, in[k], s);
+        outptr += s;
+      }
+      return 0;
+    default:
+      return -1;
+  }
+}

@@ -146,6 +146,8 @@ class Port:
         L.oracle_aggregator_concat.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32,
                                                C.c_uint64]
         L.oracle_direct_video.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.oracle_merge_linear.argtypes = [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32),
+                                          C.c_uint64, C.c_int, C.c_void_p]
 
     def typecast(self, x, out_type, accel=False):
         x = np.ascontiguousarray(x)
@@ -220,6 +222,19 @@ class Port:
         pitch = (color * width + 3) // 4 * 4
         out = np.zeros(pitch * height, dtype=np.uint8)
         self.lib.oracle_direct_video(_ptr(src), _ptr(out), color, width, height)
+        return out
+
+    def merge_linear(self, tensors, dims, direction):
+        """gst_tensor_merge_generate_mem (gsttensor_merge.c:506-586): tensors = list of arrays
+        of one type, dims = their rank-4 dims (innermost first)."""
+        arrs = [np.ascontiguousarray(t) for t in tensors]
+        es = arrs[0].dtype.itemsize
+        n = len(arrs)
+        ptrs = (C.c_void_p * n)(*[a.ctypes.data for a in arrs])
+        flat = (C.c_uint32 * (4 * n))(*[int(d) for dim in dims for d in (list(dim) + [1] * 4)[:4]])
+        out = np.empty(sum(a.size for a in arrs), dtype=arrs[0].dtype)
+        r = self.lib.oracle_merge_linear(n, ptrs, flat, es, int(direction), _ptr(out))
+        assert r == 0
         return out
 
     def aggregator_concat(self, src, frame_size, frames_out, block_size):
