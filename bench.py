@@ -309,6 +309,59 @@ def extra_kernels(dev, peak, with_cpu=True):
     dev.free(d_src)
     dev.free(d_dst)
     out.update(aggregator_extras(dev, peak, checker is not None))
+    out.update(merge_extras(dev, peak, checker is not None))
+    return out
+
+
+def merge_extras(dev, peak, with_cpu):
+    """tensor_merge mode=linear option=0 (K10): a 1080p RGB frame and an alpha plane -> RGBA, 32
+    frames per launch through nnsb_merge_launch.  Algorithmic bytes: 2 x output bytes."""
+    import ctypes as C
+    from nnstreamer_b200 import _lib as L
+    rng = np.random.default_rng(12)
+    frames = 32
+    px = W * H * frames
+    rgb = rng.integers(0, 256, 3 * px, dtype=np.uint8)
+    alpha = rng.integers(0, 256, px, dtype=np.uint8)
+    d_rgb, d_a = dev.upload(rgb), dev.upload(alpha)
+    d_out = dev.alloc(4 * px)
+    ptrs = (C.c_void_p * 2)(d_rgb, d_a)
+    blk = (C.c_uint64 * 2)(3, 1)
+    lib = L.lib()
+
+    def launch():
+        L.check(lib.nnsb_merge_launch(dev.stream, 2, ptrs, blk, C.c_void_p(d_out), px))
+
+    ms = time_launches(dev, launch, 10, 3) / 10
+    gbs = 2 * 4 * px / (ms * 1e-3) / 1e9
+    out = {"merge_rgb_alpha_1080p_b32": {"ms": ms, "GB/s": gbs, "frac_of_measured_peak": gbs / peak,
+                                          "launches": 1}}
+    if with_cpu:
+        n1 = W * H
+        t0 = time.perf_counter()
+        cpu_checker_port().merge_linear([rgb[:3 * n1], alpha[:n1]], [[3, W, H, 1], [1, W, H, 1]], 0)
+        dt = time.perf_counter() - t0
+        out["merge_rgb_alpha_1080p_b32"]["cpu_reference_1_thread_GB/s"] = 2 * 4 * n1 / dt / 1e9
+    for p in (d_rgb, d_a, d_out):
+        dev.free(p)
+    # feature maps: 64 + 32 float32 channels per position (256- and 128-byte blocks)
+    pos = 1 << 21
+    fa = rng.standard_normal(64 * pos, dtype=np.float32)
+    fb = rng.standard_normal(32 * pos, dtype=np.float32)
+    d_fa, d_fb = dev.upload(fa), dev.upload(fb)
+    d_out = dev.alloc(96 * 4 * pos)
+    ptrs2 = (C.c_void_p * 2)(d_fa, d_fb)
+    blk2 = (C.c_uint64 * 2)(256, 128)
+
+    def launch2():
+        L.check(lib.nnsb_merge_launch(dev.stream, 2, ptrs2, blk2, C.c_void_p(d_out), pos))
+
+    ms = time_launches(dev, launch2, 10, 3) / 10
+    gbs = 2 * 96 * 4 * pos / (ms * 1e-3) / 1e9
+    out["merge_f32_64ch_32ch_2M_positions"] = {"ms": ms, "GB/s": gbs, "frac_of_measured_peak": gbs / peak,
+                                               "launches": 1}
+    for p in (d_fa, d_fb, d_out):
+        dev.free(p)
     return out
 
 
