@@ -27,6 +27,7 @@
  */
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "nnsb_device.cuh"
 #include "nnsb_kernels.h"
@@ -125,7 +126,10 @@ gather (uint32_t stage_addr, const uint32_t *slot, uint32_t *w)
   }
 }
 
-template <int ES>
+/* MICRO: the VE store vectors of a thread form VE x VE register micro-transposes: VE LDS.128
+ * (whole shared-memory chunks; entry [j] of st_slot holds chunk j % VE of block j / VE) feed VE
+ * output vectors, instead of VE scalar LDS per vector. */
+template <int ES, bool MICRO>
 __global__ void __launch_bounds__ (PV_THREADS, NNSB_PV_MIN_BLOCKS)
 permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
     const unsigned char *__restrict__ table, const __grid_constant__ PermVecDev p)
@@ -203,10 +207,12 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
   };
 
   /* bit j: vector j of this thread exists in the box (always, when the box fills the stage) */
-  uint32_t present = 0;
+  uint32_t present = 0, present_st = 0;     /* (the store side differs under MICRO) */
 #pragma unroll
-  for (int j = 0; j < PV_VPT; j++)
+  for (int j = 0; j < PV_VPT; j++) {
     present |= (ld_off[j] != PV_INVALID ? 1u : 0u) << j;
+    present_st |= (st_off[j] != PV_INVALID ? 1u : 0u) << j;
+  }
 
   /* stage_off is a compile-time ring slot: shared-memory addresses are register + immediate.
    * Vectors that are absent, or outside the tensor in an edge box, are predicated off (their
@@ -239,9 +245,31 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
     unsigned char *dst = ti.dst;
     const uint32_t stage_addr = ring_addr + stage_off;
     uint32_t w[PV_VPT][4];
+    if constexpr (MICRO) {
 #pragma unroll
-    for (int j = 0; j < PV_VPT; j++)
-      gather<ES> (stage_addr, st_slot[j], w[j]);
+      for (int b = 0; b < PV_VPT / VE; b++) {
+        uint32_t r[VE][4];
+#pragma unroll
+        for (int e = 0; e < VE; e++)
+          asm volatile ("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r" (r[e][0]), "=r" (r[e][1]),
+              "=r" (r[e][2]), "=r" (r[e][3]) : "r" (stage_addr + st_slot[b * VE + e][0]));
+#pragma unroll
+        for (int jj = 0; jj < VE; jj++)
+#pragma unroll
+          for (int e = 0; e < VE; e++) {
+            if constexpr (ES == 4) {
+              w[b * VE + jj][e] = r[e][jj];
+            } else {
+              w[b * VE + jj][2 * e] = r[e][2 * jj];
+              w[b * VE + jj][2 * e + 1] = r[e][2 * jj + 1];
+            }
+          }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < PV_VPT; j++)
+        gather<ES> (stage_addr, st_slot[j], w[j]);
+    }
     if (ti.full && whole) {
 #pragma unroll
       for (int j = 0; j < PV_VPT; j++)
@@ -249,12 +277,12 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
     } else if (ti.full) {
 #pragma unroll
       for (int j = 0; j < PV_VPT; j++)
-        st_stream_16_if ((present >> j) & 1u, dst + st_off[j], w[j]);
+        st_stream_16_if ((present_st >> j) & 1u, dst + st_off[j], w[j]);
     } else {
       const uint64_t lim = ti.limits;
 #pragma unroll
       for (int j = 0; j < PV_VPT; j++)
-        st_stream_16_if (((present >> j) & 1u)
+        st_stream_16_if (((present_st >> j) & 1u)
             && inside4 (t_st_coord[threadIdx.x + j * PV_THREADS], lim), dst + st_off[j], w[j]);
     }
   };
@@ -640,6 +668,57 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
   for (int i = 0; i < n; i++)
     tiles *= (dims[i].size + T[i] - 1) / T[i];
 
+  /* 2b. register micro-transposes: possible when the fastest output dim O is not the fastest
+   *     input dim, every shared-memory chunk lies at one O coordinate and O-vectors are whole.
+   *     A block = one chunk column x VE consecutive O: VE chunks in, VE store vectors out. */
+  bool micro = false;
+  uint32_t lstride_o = 0;
+  std::vector<uint32_t> blocks;         /* representative store vector (element 0 at lin % VE == 0) */
+  std::vector<int32_t> vec_of_lin;
+  if ((es == 4 || es == 8) && out_order[0] != in_order[0] && !getenv ("NNSB_PERM_NO_MICRO")) {
+    uint32_t ls = 1;
+    for (int k = 0; k < n && in_order[k] != out_order[0]; k++)
+      ls *= (uint32_t) T[in_order[k]];
+    lstride_o = ls;
+    if (lstride_o % VE == 0 && T[out_order[0]] % VE == 0) {
+      vec_of_lin.assign (volume, -1);
+      for (uint32_t v = 0; v < n_vec; v++)
+        vec_of_lin[st_lin[(size_t) v * VE]] = (int32_t) v;
+      for (uint32_t v = 0; v < n_vec; v++)
+        if (st_lin[(size_t) v * VE] % VE == 0)
+          blocks.push_back (v);
+      micro = blocks.size () * VE == n_vec;
+      for (size_t mb = 0; mb < blocks.size () && micro; mb++) {
+        const uint32_t lin0 = st_lin[(size_t) blocks[mb] * VE];
+        for (uint32_t jj = 0; jj < VE && micro; jj++) {
+          const int32_t u = lin0 + jj < volume ? vec_of_lin[lin0 + jj] : -1;
+          micro = u >= 0;
+          for (uint32_t e = 0; e < VE && micro; e++)
+            micro = st_lin[(size_t) u * VE + e] == lin0 + jj + e * lstride_o;
+        }
+      }
+    }
+  }
+  /* chunk read by LDS.128 number e of block mb (micro mode) */
+  auto micro_cost = [&] (const Swizzle &sw) {
+    uint64_t cost = 0;
+    for (size_t base = 0; base < blocks.size (); base += 8)
+      for (uint32_t e = 0; e < VE; e++) {
+        int count[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }, worst = 0;
+        for (size_t l = 0; l < 8 && base + l < blocks.size (); l++) {
+          const uint32_t lin0 = st_lin[(size_t) blocks[base + l] * VE];
+          const int b = (int) (sw ((lin0 + e * lstride_o) / (uint32_t) VE) % 8);
+          if (++count[b] > worst)
+            worst = count[b];
+        }
+        cost += worst;
+      }
+    return cost;
+  };
+  auto cost_of = [&] (const Swizzle &sw) {
+    return micro ? micro_cost (sw) : gather_cost (st_lin, n_vec, (int) VE, es, sw);
+  };
+
   /* 3. shared-memory swizzle: the candidate with the fewest gather wavefronts */
   Swizzle best_sw = { -1, -1 };
   {
@@ -650,9 +729,9 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
         best_sw.s2 = atoi (strchr (env_sw, ',') + 1);
       if (!best_sw.is_permutation ())
         best_sw.s1 = best_sw.s2 = -1;
-      pl->gather_wavefronts = gather_cost (st_lin, n_vec, (int) VE, es, best_sw);
+      pl->gather_wavefronts = cost_of (best_sw);
     } else {
-      uint64_t best = gather_cost (st_lin, n_vec, (int) VE, es, best_sw);
+      uint64_t best = cost_of (best_sw);
       /* s1 = 1 is left out: same simulated gather cost, but measured 8 % slower (the
        * cp.async writes seem to dislike chunk pairs being swapped) */
       for (int s1 = 2; s1 <= 9; s1++)
@@ -662,7 +741,7 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
           const Swizzle sw = { s1, s2 };
           if (!sw.is_permutation ())
             continue;
-          const uint64_t c = gather_cost (st_lin, n_vec, (int) VE, es, sw);
+          const uint64_t c = cost_of (sw);
           if (c < best) {
             best = c;
             best_sw = sw;
@@ -671,12 +750,33 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
       pl->gather_wavefronts = best;
     }
   }
-  for (uint32_t v = 0; v < n_vec; v++) {
+  for (uint32_t v = 0; v < n_vec; v++)
     t_ld_slot[v] = best_sw (v) * 16;
-    for (uint64_t e = 0; e < VE; e++) {
-      const uint32_t li = st_lin[(size_t) v * VE + e];
-      t_st_slot[(size_t) v * VE + e] = (uint16_t) (best_sw (li / (uint32_t) VE) * 16 + (li % VE) * es);
+  if (micro) {
+    /* entry t + j * 256 of the store-side arrays = vector j % VE of block t + (j / VE) * 256 */
+    uint64_t *t_st_coord = (uint64_t *) (tab + PV_T_ST_COORD);
+    std::vector<uint32_t> off (t_st_off, t_st_off + PV_NVT);
+    std::vector<uint64_t> coord (t_st_coord, t_st_coord + PV_NVT);
+    for (int i = 0; i < PV_NVT; i++) {
+      t_st_off[i] = PV_INVALID;
+      t_st_coord[i] = 0;
     }
+    for (size_t mb = 0; mb < blocks.size (); mb++) {
+      const uint32_t lin0 = st_lin[(size_t) blocks[mb] * VE];
+      for (uint32_t jj = 0; jj < VE; jj++) {
+        const size_t entry = (mb % PV_THREADS) + ((mb / PV_THREADS) * VE + jj) * PV_THREADS;
+        const uint32_t u = (uint32_t) vec_of_lin[lin0 + jj];
+        t_st_off[entry] = off[u];
+        t_st_coord[entry] = coord[u];
+        t_st_slot[entry * VE] = (uint16_t) (best_sw ((lin0 + jj * lstride_o) / (uint32_t) VE) * 16);
+      }
+    }
+  } else {
+    for (uint32_t v = 0; v < n_vec; v++)
+      for (uint64_t e = 0; e < VE; e++) {
+        const uint32_t li = st_lin[(size_t) v * VE + e];
+        t_st_slot[(size_t) v * VE + e] = (uint16_t) (best_sw (li / (uint32_t) VE) * 16 + (li % VE) * es);
+      }
   }
   free (st_lin);
 
@@ -696,28 +796,29 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
   pl->frame_bytes = (uint64_t) frame_elems * d0.es;
   pl->swizzle_shift = best_sw.s1;
   pl->swizzle_shift2 = best_sw.s2;
+  pl->micro = micro ? 1 : 0;
   *host_table = tab;
   return 0;
 }
 
-template <int ES> static int
+template <int ES, bool MICRO> static int
 launch_permute_vec_t (const PermVecDev &p, const void *d_table, const void *in, void *out,
     const LaunchCfg &cfg, cudaStream_t stream)
 {
   const size_t smem = (size_t) PV_STAGES * PV_STAGE_BYTES;
   static int resident = 0;
   if (resident == 0) {
-    cudaError_t e = cudaFuncSetAttribute (permute_vec_kernel<ES>,
+    cudaError_t e = cudaFuncSetAttribute (permute_vec_kernel<ES, MICRO>,
         cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
     if (e != cudaSuccess)
       return (int) e;
-    resident = resident_blocks_per_sm (permute_vec_kernel<ES>, PV_THREADS, smem);
+    resident = resident_blocks_per_sm (permute_vec_kernel<ES, MICRO>, PV_THREADS, smem);
   }
   uint64_t grid = p.n_tiles;
   const uint64_t cap = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : resident);
   if (grid > cap)
     grid = cap;
-  permute_vec_kernel<ES><<<(unsigned int) grid, PV_THREADS, smem, stream>>> (
+  permute_vec_kernel<ES, MICRO><<<(unsigned int) grid, PV_THREADS, smem, stream>>> (
       (const unsigned char *) in, (unsigned char *) out, (const unsigned char *) d_table, p);
   return (int) cudaGetLastError ();
 }
@@ -758,9 +859,11 @@ launch_permute_vec (const PermVecPlan &pl, const void *d_table, const void *in, 
   p.n_vec = pl.n_vec;
   p.n_tiles = (uint32_t) tiles;
   switch (pl.es) {
-    case 4: return launch_permute_vec_t<4> (p, d_table, in, out, cfg, stream);
-    case 8: return launch_permute_vec_t<8> (p, d_table, in, out, cfg, stream);
-    case 16: return launch_permute_vec_t<16> (p, d_table, in, out, cfg, stream);
+    case 4: return pl.micro ? launch_permute_vec_t<4, true> (p, d_table, in, out, cfg, stream)
+          : launch_permute_vec_t<4, false> (p, d_table, in, out, cfg, stream);
+    case 8: return pl.micro ? launch_permute_vec_t<8, true> (p, d_table, in, out, cfg, stream)
+          : launch_permute_vec_t<8, false> (p, d_table, in, out, cfg, stream);
+    case 16: return launch_permute_vec_t<16, false> (p, d_table, in, out, cfg, stream);
     default: return -1;
   }
 }

@@ -91,6 +91,7 @@ struct PermVecPlan
   uint64_t tiles_per_frame;
   size_t table_bytes;
   int swizzle_shift, swizzle_shift2;            /* chosen shared-memory swizzle (-1 = none) */
+  int micro;                                    /* store side uses VE x VE register micro-transposes */
   uint64_t gather_wavefronts;                   /* simulated LDS wavefronts per box (ideal:
                                                  * one per 128 bytes gathered) */
 };

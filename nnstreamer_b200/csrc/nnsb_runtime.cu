@@ -802,8 +802,9 @@ nnsb_plan_describe (const nnsb_plan * plan, char *buf, size_t buflen)
         for (int i = 0; i < plan->perm_vec.n && o < (int) sizeof (box) - 12; i++)
           o += snprintf (box + o, sizeof (box) - o, "%s%u", i ? "x" : "", plan->perm_vec.tile[i]);
         len = snprintf (buf, buflen, "permute: vector table, %d-byte elements, box %s, %u vectors, "
-            "swizzle %d/%d, %llu gather wavefronts", plan->perm_vec.es, box, plan->perm_vec.n_vec,
+            "swizzle %d/%d, %s%llu gather wavefronts", plan->perm_vec.es, box, plan->perm_vec.n_vec,
             plan->perm_vec.swizzle_shift, plan->perm_vec.swizzle_shift2,
+            plan->perm_vec.micro ? "register micro-transposes, " : "",
             (unsigned long long) plan->perm_vec.gather_wavefronts);
       } else {
         len = snprintf (buf, buflen, "permute: scalar box kernel");

@@ -135,9 +135,20 @@ main (int argc, char **argv)
           printf ("MISMATCH store out of range (tile %llu vector %u)\n", (unsigned long long) t, v);
           return 1;
         }
-        for (int e = 0; e < VE; e++)
-          memcpy (&got[ob + t_st_off[v] + (size_t) e * pl.es], &stage[t_st_slot[(size_t) v * VE + e]],
-              pl.es);
+        if (pl.micro) {
+          /* entry v = thread + j * 256: vector jj = j % VE of that thread's block j / VE; element
+           * e comes from chunk e of the block (slot kept in entry (block, e)), position jj */
+          const uint32_t t = v % PV_THREADS, j = v / PV_THREADS, b = j / VE, jj = j % VE;
+          for (int e = 0; e < VE; e++) {
+            const uint32_t entry = t + (b * VE + e) * PV_THREADS;
+            memcpy (&got[ob + t_st_off[v] + (size_t) e * pl.es],
+                &stage[t_st_slot[(size_t) entry * VE] + (size_t) jj * pl.es], pl.es);
+          }
+        } else {
+          for (int e = 0; e < VE; e++)
+            memcpy (&got[ob + t_st_off[v] + (size_t) e * pl.es], &stage[t_st_slot[(size_t) v * VE + e]],
+                pl.es);
+        }
         writes += 16;
       }
   }
@@ -154,9 +165,9 @@ main (int argc, char **argv)
   int o = 0;
   for (int i = 0; i < pl.n; i++)
     o += snprintf (box + o, sizeof (box) - o, "%s%u", i ? "x" : "", pl.tile[i]);
-  printf ("ok es=%d box=%s n_vec=%u swizzle=%d/%d wavefronts=%llu ideal=%u tiles=%llu\n", pl.es, box,
-      pl.n_vec, pl.swizzle_shift, pl.swizzle_shift2, (unsigned long long) pl.gather_wavefronts,
-      pl.n_vec * 16 / 128, (unsigned long long) n_tiles);
+  printf ("ok es=%d box=%s n_vec=%u swizzle=%d/%d micro=%d wavefronts=%llu tiles=%llu\n", pl.es, box,
+      pl.n_vec, pl.swizzle_shift, pl.swizzle_shift2, pl.micro, (unsigned long long) pl.gather_wavefronts,
+      (unsigned long long) n_tiles);
   free (table);
   return 0;
 }
