@@ -6,7 +6,9 @@ run() { # name, run_kernel.py args...
   python profiles/run_kernel.py "$@" > gpurun_out/plain_$name.log 2>&1 && ncu --set full --clock-control none --import-source on -s 1 -c 2 -f -o gpurun_out/prof_$name python profiles/run_kernel.py "$@" > gpurun_out/ncu_$name.log 2>&1
   tail -1 gpurun_out/plain_$name.log
 }
-run transpose --batch 8 --iters 4 -- transpose 1:2:0:3 float32 3:3840:2160:1   # captured when f32 still took plane_kernel; now permute_vec_kernel
+run plane_u8 --batch 16 --iters 4 -- transpose 1:2:0:3 uint8 3:3840:2160:1
 run clamp --iters 4 -- clamp -33.3:77.7 float32 3:1920:1080:64
 run typecast --iters 4 -- typecast float32 uint8 3:1920:1080:32
-run permute_vec --batch 8 --iters 3 -- transpose 2:0:1:3 float32 3:3840:2160:1
+run permute_vec --batch 8 --iters 4 -- transpose 2:0:1:3 float32 3:3840:2160:1
+# launch list of the whole bench (r1_launches_bench.csv):
+# python bench.py --steps 2 --warmup 3 --no-cpu-baseline && ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline
