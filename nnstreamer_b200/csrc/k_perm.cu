@@ -363,15 +363,7 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
     if (dims[i].size > 0xffffffffull)
       return (int) cudaErrorInvalidValue;
 
-  /* 3. 4-byte and wider elements: the table-driven 16-byte vector kernel (k_perm_vec.cu), when
-   *    the plan qualified (measured faster than the TMA pipeline below at these widths) */
-  if (vec && vec->valid) {
-    const int r = launch_permute_vec (*vec, d_table, in, out, frame_elems, batch, cfg, stream);
-    if (r != -1)
-      return r;
-  }
-
-  /* 4. video-shaped [P][C] <-> [C][P] (2..4 channels): the TMA pipeline (k_plane.cu) */
+  /* 3. video-shaped [P][C] <-> [C][P] (2..4 channels): the TMA pipeline (k_plane.cu) */
   if (!getenv ("NNSB_NO_PLANE")) {
     /* find X (out stride 1) and Y (in stride 1); everything else is an outer dim */
     int ix = -1, iy = -1;
@@ -400,6 +392,14 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
       if (r != -1)
         return r;
     }
+  }
+
+  /* 4. 4-byte and wider elements: the table-driven 16-byte vector kernel (k_perm_vec.cu), when
+   *    the plan qualified */
+  if (vec && vec->valid) {
+    const int r = launch_permute_vec (*vec, d_table, in, out, frame_elems, batch, cfg, stream);
+    if (r != -1)
+      return r;
   }
 
   /* 5. the box: >= 32-element runs on both sides, then grown to ~2048 elements */

@@ -9,7 +9,7 @@
  *
  * Here no thread ever touches global memory:
  *   - an elected thread streams tiles global -> shared with `cp.async.bulk` (1-D TMA bulk
- *     copy, completion on an mbarrier) through a STAGES-deep ring, and shared -> global with
+ *     copy, completion on an mbarrier) through a STAGES-deep ring (3-5, by element size), and shared -> global with
  *     `cp.async.bulk ... bulk_group` (one copy per channel plane);
  *   - the 256 threads only re-order inside shared memory: each reads C x 16 bytes
  *     (16/ES pixels, interleaved) with LDS.128, permutes them in registers and writes C x 16
@@ -23,18 +23,38 @@
  */
 #include "nnsb_device.cuh"
 #include "nnsb_kernels.h"
+#include "k_perm_common.cuh"
 
 namespace nnsb {
 
-constexpr int PLANE_THREADS = 256;
-constexpr int PLANE_STAGES = 4;
+constexpr int PLANE_THREADS = 256;              /* threads that re-order tiles */
+constexpr int PLANE_BLOCK = PLANE_THREADS + 32; /* + the copy-engine warp */
+/* ring depth per element size, from a sweep on B200 (4K frames, 3 channels): 4-byte elements
+ * only move registers, so one CTA per SM with a deep ring is best (5 stages: 6.3 TB/s vs 5.7 with
+ * 4 stages and two CTAs); 1-byte elements spend ~50 ALU instructions per thread and tile on the
+ * byte shuffles and want more CTAs per SM to hide them (3 stages, three CTAs: 5.6 vs 5.2). */
+#ifndef NNSB_PLANE_STAGES_1
+#define NNSB_PLANE_STAGES_1 3
+#endif
+#ifndef NNSB_PLANE_STAGES_2
+#define NNSB_PLANE_STAGES_2 3
+#endif
+#ifndef NNSB_PLANE_STAGES_4
+#define NNSB_PLANE_STAGES_4 5
+#endif
+template <int ES> struct PlaneStages
+{
+  static constexpr int N = ES == 4 ? NNSB_PLANE_STAGES_4 : ES == 2 ? NNSB_PLANE_STAGES_2
+      : NNSB_PLANE_STAGES_1;
+};
 constexpr int PLANE_MAX_OUTER = NNSB_PERM_MAX_RANK;
 
 struct PlaneDev
 {
   uint64_t P;                   /* pixels per plane */
-  uint64_t tiles_per_plane;     /* ceil (P / TP) */
-  uint64_t n_tiles;             /* tiles_per_plane * prod (outer) */
+  FastDiv tiles_per_plane;      /* ceil (P / TP) */
+  uint32_t n_tiles;             /* tiles_per_plane * prod (outer), < 2^31 */
+  FastDiv o_div[PLANE_MAX_OUTER];
   uint64_t plane_stride;        /* elements between channel planes on the planar side */
   int n_outer;
   uint32_t o_size[PLANE_MAX_OUTER];
@@ -113,7 +133,9 @@ template <int C, int ES> struct PlaneGeom
   static constexpr int TP = PLANE_THREADS * G;            /* pixels per tile */
   static constexpr int TILE_BYTES = TP * C * ES;          /* 256 * 16 * C */
   static constexpr int PLANE_BYTES = TP * ES;             /* 4096 */
-  static constexpr size_t SMEM = (size_t) PLANE_STAGES * 2 * TILE_BYTES + 3 * PLANE_STAGES * 8 + 32;
+  static constexpr int FIT = (216 * 1024) / (2 * TILE_BYTES);        /* what one SM can hold */
+  static constexpr int STAGES = PlaneStages<ES>::N < FIT ? PlaneStages<ES>::N : FIT;
+  static constexpr size_t SMEM = (size_t) STAGES * 2 * TILE_BYTES + 3 * STAGES * 8 + 32;
 };
 
 /* element i (ES bytes wide) of a little-endian array of 32-bit words; i is a compile-time
@@ -133,12 +155,13 @@ template <int ES> __device__ __forceinline__ void put_elem (uint32_t *w, int i, 
 
 /* TO_PLANAR: in = interleaved [P][C], out = planar [C][P].  Otherwise the inverse. */
 template <int C, int ES, bool TO_PLANAR>
-__global__ void __launch_bounds__ (PLANE_THREADS)
+__global__ void __launch_bounds__ (PLANE_BLOCK)
 plane_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
     const __grid_constant__ PlaneDev p)
 {
   typedef PlaneGeom<C, ES> Gm;
   constexpr int G = Gm::G;
+  constexpr int PLANE_STAGES = Gm::STAGES;
   extern __shared__ __align__ (128) unsigned char smem[];
   unsigned char *in_buf = smem;                                          /* [STAGES][TILE_BYTES] */
   unsigned char *out_buf = smem + (size_t) PLANE_STAGES * Gm::TILE_BYTES;   /* [STAGES][TILE_BYTES] */
@@ -166,16 +189,17 @@ plane_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ 
       mbar_arrive (&empty[s]);          /* every output buffer starts out free (phase 0) */
 
   /* tile k of this CTA is global tile blockIdx.x + k * gridDim.x */
-  auto tile_of = [&] (uint64_t k) { return (uint64_t) blockIdx.x + k * gridDim.x; };
+  auto tile_of = [&] (uint32_t k) { return blockIdx.x + k * gridDim.x; };
 
   /* global addresses of one tile (only the elected thread needs them) */
-  auto locate = [&] (uint64_t tile, uint64_t &il_off, uint64_t &pl_off, uint32_t &npix) {
-    uint64_t q = tile / p.tiles_per_plane;
-    const uint64_t p0 = (tile - q * p.tiles_per_plane) * Gm::TP;
+  auto locate = [&] (uint32_t tile, uint64_t &il_off, uint64_t &pl_off, uint32_t &npix) {
+    uint32_t q, tp;
+    divmod (tile, p.tiles_per_plane, q, tp);
+    const uint64_t p0 = (uint64_t) tp * Gm::TP;
     uint64_t il = 0, pl = 0;
     for (int i = 0; i < p.n_outer; i++) {
-      const uint64_t idx = q % p.o_size[i];
-      q /= p.o_size[i];
+      uint32_t idx;
+      divmod (q, p.o_div[i], q, idx);
       il += idx * p.o_il[i];
       pl += idx * p.o_pl[i];
     }
@@ -185,7 +209,7 @@ plane_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ 
     npix = (uint32_t) (left < (uint64_t) Gm::TP ? left : (uint64_t) Gm::TP);
   };
 
-  auto issue_load = [&] (uint64_t tile, int s) {
+  auto issue_load = [&] (uint32_t tile, int s) {
     uint64_t il_off, pl_off;
     uint32_t npix;
     locate (tile, il_off, pl_off, npix);
@@ -200,7 +224,7 @@ plane_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ 
     }
   };
 
-  auto issue_store = [&] (uint64_t tile, int s) {
+  auto issue_store = [&] (uint32_t tile, int s) {
     uint64_t il_off, pl_off;
     uint32_t npix;
     locate (tile, il_off, pl_off, npix);
@@ -215,18 +239,37 @@ plane_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ 
     bulk_commit ();
   };
 
-  uint64_t my_tiles = 0;
-  if ((uint64_t) blockIdx.x < p.n_tiles)
+  uint32_t my_tiles = 0;
+  if (blockIdx.x < p.n_tiles)
     my_tiles = (p.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
 
-  if (t == 0) {
-    for (uint64_t k = 0; k < PLANE_STAGES && k < my_tiles; k++)
-      issue_load (tile_of (k), (int) k);
+  if (t >= PLANE_THREADS) {
+    /* ---- copy-engine warp: one thread keeps loads and stores flowing; it never touches the
+     * data, so the 256 re-ordering threads never wait for its address arithmetic ---- */
+    if (t == PLANE_THREADS) {
+      for (uint32_t k = 0; k < (uint32_t) PLANE_STAGES && k < my_tiles; k++)
+        issue_load (tile_of (k), (int) k);
+      for (uint32_t k = 0; k < my_tiles; k++) {
+        const int s = (int) (k % PLANE_STAGES);
+        const uint32_t parity = (k / PLANE_STAGES) & 1u;
+        mbar_wait (&done[s], parity);   /* everyone has read in_buf[s] and written out_buf[s] */
+        issue_store (tile_of (k), s);
+        if (k + PLANE_STAGES < my_tiles)
+          issue_load (tile_of (k + PLANE_STAGES), s);
+        /* stores complete in order: once all but the newest STAGES-1 have been read out of
+         * shared memory, the buffer of tile k-STAGES+1 -- the one tile k+1 writes -- is free */
+        bulk_wait_read<PLANE_STAGES - 1> ();
+        if (k + 1 >= (uint32_t) PLANE_STAGES)
+          mbar_arrive (&empty[(k + 1) % PLANE_STAGES]);
+      }
+      bulk_wait_all ();         /* stores must complete before the CTA's shared memory goes away */
+    }
+    return;
   }
 
-  for (uint64_t k = 0; k < my_tiles; k++) {
+  for (uint32_t k = 0; k < my_tiles; k++) {
     const int s = (int) (k % PLANE_STAGES);
-    const uint32_t parity = (uint32_t) ((k / PLANE_STAGES) & 1);
+    const uint32_t parity = (k / PLANE_STAGES) & 1u;
     mbar_wait (&full[s], parity);
     mbar_wait (&empty[s], parity);      /* the store that last read out_buf[s] has drained */
 
@@ -273,20 +316,7 @@ plane_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ 
     }
     fence_async_smem ();        /* generic-proxy writes -> visible to the bulk store */
     mbar_arrive (&done[s]);
-    if (t == 0) {
-      mbar_wait (&done[s], parity);     /* everyone has read in_buf[s] and written out_buf[s] */
-      issue_store (tile_of (k), s);
-      if (k + PLANE_STAGES < my_tiles)
-        issue_load (tile_of (k + PLANE_STAGES), s);
-      /* stores complete in order: once all but the newest STAGES-1 are done, the buffer of
-       * tile k-STAGES+1 -- the one iteration k+1 writes -- is free */
-      bulk_wait_read<PLANE_STAGES - 1> ();
-      if (k + 1 >= (uint64_t) PLANE_STAGES)
-        mbar_arrive (&empty[(k + 1) % PLANE_STAGES]);
-    }
   }
-  if (t == 0)
-    bulk_wait_all ();           /* stores must complete before the CTA's shared memory goes away */
 }
 
 template <int C, int ES, bool TO_PLANAR> static int
@@ -300,14 +330,14 @@ launch_plane_t (const PlaneDev &p, const void *in, void *out, const LaunchCfg &c
         cudaFuncAttributeMaxDynamicSharedMemorySize, (int) Gm::SMEM);
     if (e != cudaSuccess)
       return (int) e;
-    resident = resident_blocks_per_sm (plane_kernel<C, ES, TO_PLANAR>, PLANE_THREADS, Gm::SMEM);
+    resident = resident_blocks_per_sm (plane_kernel<C, ES, TO_PLANAR>, PLANE_BLOCK, Gm::SMEM);
   }
   uint64_t grid = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : resident);
   if (grid > p.n_tiles)
     grid = p.n_tiles;
   if (grid == 0)
     return 0;
-  plane_kernel<C, ES, TO_PLANAR><<<(unsigned int) grid, PLANE_THREADS, Gm::SMEM, stream>>> (
+  plane_kernel<C, ES, TO_PLANAR><<<(unsigned int) grid, PLANE_BLOCK, Gm::SMEM, stream>>> (
       (const unsigned char *) in, (unsigned char *) out, p);
   return (int) cudaGetLastError ();
 }
@@ -352,17 +382,22 @@ int launch_plane (bool to_planar, int channels, int es, uint64_t pixels, uint64_
   p.P = pixels;
   p.plane_stride = plane_stride;
   const uint64_t tp = (uint64_t) PLANE_THREADS * (16 / es);
-  p.tiles_per_plane = (pixels + tp - 1) / tp;
-  p.n_tiles = p.tiles_per_plane;
+  const uint64_t tiles_per_plane = (pixels + tp - 1) / tp;
+  uint64_t n_tiles = tiles_per_plane;
   p.n_outer = n_outer;
   for (int i = 0; i < n_outer; i++) {
     if ((o_il[i] * es) % 16 || (o_pl[i] * es) % 16)
       return -1;
     p.o_size[i] = o_size[i];
+    p.o_div[i] = make_fastdiv (o_size[i]);
     p.o_il[i] = o_il[i];
     p.o_pl[i] = o_pl[i];
-    p.n_tiles *= o_size[i];
+    n_tiles *= o_size[i];
   }
+  if (n_tiles >= (1ull << 31) || tiles_per_plane >= (1ull << 31))
+    return -1;
+  p.tiles_per_plane = make_fastdiv ((uint32_t) tiles_per_plane);
+  p.n_tiles = (uint32_t) n_tiles;
   /* tiny problems are not worth a pipeline */
   if (p.n_tiles * (uint64_t) PLANE_THREADS * 16 * channels < 64 * 1024)
     return -1;
