@@ -43,7 +43,10 @@ constexpr int PV_THREADS = NNSB_PV_THREADS;
 constexpr int PV_VPT = 1024 / PV_THREADS;                 /* vectors per thread per tile */
 constexpr int PV_NVT = PV_THREADS * PV_VPT;               /* vector slots per stage: 1024 */
 constexpr int PV_STAGE_BYTES = PV_NVT * 16;               /* 16 KiB */
-constexpr int PV_STAGES = 3;
+#ifndef NNSB_PV_STAGES
+#define NNSB_PV_STAGES 3
+#endif
+constexpr int PV_STAGES = NNSB_PV_STAGES;
 constexpr int PV_DIMS = NNSB_PERM_MAX_RANK + 1;           /* + batch */
 constexpr int PV_BOXED = 4;                               /* dims with a box extent > 1 */
 constexpr uint32_t PV_INVALID = 0xffffffffu;
@@ -301,15 +304,17 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
     for (uint32_t k = 0; k < (uint32_t) PV_STAGES && k < my_tiles; k++)
       locate (k);
   __syncthreads ();
-  static_assert (PV_STAGES == 3, "the tile loop below is unrolled for three ring slots");
-  issue (0, 0);
-  issue (1, PV_STAGE_BYTES);
-  for (uint32_t k = 0; k < my_tiles; k += 3) {
-    step (k, 0, 2 * PV_STAGE_BYTES);
-    if (k + 1 < my_tiles)
-      step (k + 1, PV_STAGE_BYTES, 0);
-    if (k + 2 < my_tiles)
-      step (k + 2, 2 * PV_STAGE_BYTES, PV_STAGE_BYTES);
+  /* prologue: PV_STAGES - 1 tiles in flight; the loop is unrolled over the ring slots so that
+   * every shared-memory offset is a compile-time constant */
+#pragma unroll
+  for (int s = 0; s < PV_STAGES - 1; s++)
+    issue ((uint32_t) s, (uint32_t) s * PV_STAGE_BYTES);
+  for (uint32_t k = 0; k < my_tiles; k += PV_STAGES) {
+#pragma unroll
+    for (int s = 0; s < PV_STAGES; s++)
+      if (k + s < my_tiles)
+        step (k + s, (uint32_t) s * PV_STAGE_BYTES,
+            (uint32_t) ((s + PV_STAGES - 1) % PV_STAGES) * PV_STAGE_BYTES);
   }
 }
 
@@ -815,7 +820,11 @@ launch_permute_vec_t (const PermVecDev &p, const void *d_table, const void *in, 
     resident = resident_blocks_per_sm (permute_vec_kernel<ES, MICRO>, PV_THREADS, smem);
   }
   uint64_t grid = p.n_tiles;
-  const uint64_t cap = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : resident);
+  /* two CTAs per SM, although four fit: fewer tiles in flight keep the DRAM pages of a tile
+   * row open (measured on the 4K float32 transposes: 6.0 / 5.5 / 5.2 TB/s with two, 5.4 / 4.7 /
+   * 5.0 with four, 4.7 / 4.7 / 4.3 with one) */
+  const int per_sm = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : (resident < 2 ? resident : 2);
+  const uint64_t cap = (uint64_t) cfg.sm_count * per_sm;
   if (grid > cap)
     grid = cap;
   permute_vec_kernel<ES, MICRO><<<(unsigned int) grid, PV_THREADS, smem, stream>>> (
