@@ -489,6 +489,20 @@ def native_stream_chain(device_id, n_streams=8, frames_per_stream=300):
     return out
 
 
+def bind_to_gpu_numa_node(gpu_index):
+    """Pin this process to the CPUs NVML reports as local to its GPU before any pinned host memory
+    is allocated, so the staging buffers of the end-to-end path sit on the GPU's NUMA node (the
+    host-side limiter of multi-GPU scaling).  Best effort: returns what was done."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByIndex(int(gpu_index))
+        pynvml.nvmlDeviceSetCpuAffinity(handle)
+        return "bound to %d cpus" % len(os.sched_getaffinity(0))
+    except Exception as exc:                        # noqa: BLE001
+        return "not bound (%s)" % (str(exc)[:60],)
+
+
 def run_b200(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -499,6 +513,8 @@ def run_b200(args):
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    numa = bind_to_gpu_numa_node(local_rank)
 
     from nnstreamer_b200 import Device
     dev = Device(local_rank)
@@ -630,6 +646,7 @@ def run_b200(args):
                            "chunks pipelined on two streams; wall clock around synchronous calls"},
             "gpu_launches": launches + e2e_launches,
             "gpu_launches_detail": {"device_resident": launches, "e2e": e2e_launches},
+            "host_affinity": numa,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8TBs": achieved / 8000.0,
                          # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
