@@ -60,7 +60,7 @@ int launch_stand (int in_type, int out_type, int stand_mode, const void *in, voi
     return err;
 
   /* apply grid: fill the machine; for the strided paths it must own at least nch threads */
-  const int bps = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 4;
+  const int bps = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : (batch > 1 ? 64 : 32);   /* as stand_geometry */
   uint64_t ax = ((uint64_t) cfg.sm_count * bps) / batch;
   if (ax < 8)
     ax = 8;

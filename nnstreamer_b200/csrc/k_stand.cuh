@@ -578,7 +578,9 @@ inline StandGeom
 stand_geometry (uint32_t batch, uint32_t nch, size_t frame_elems, const LaunchCfg &cfg)
 {
   StandGeom g;
-  const int bps = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 4;
+  /* oversubscribed like the chain kernels (sweep on f32 1080p x64: 4 blocks/SM 4.06 TB/s, 16: 4.23,
+   * 32: 4.39, 64: 4.47, 128: 4.48; one 400 MB tensor peaks at 32: 4.20) */
+  const int bps = cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : (batch > 1 ? 64 : 32);
   uint64_t cap = (uint64_t) cfg.sm_count * bps;
   /* split the SMs between the tensors of a batch, but keep at least 8 blocks per tensor */
   uint64_t bx = cap / (batch ? batch : 1);

@@ -128,12 +128,19 @@ nnsb_stand_launch_noalloc (const void *d_in, void *d_out, int in_type, int out_t
   const uint32_t nch = per_channel ? dim[0] : 1;
   nnsb::LaunchCfg cfg;
   cfg.sm_count = pd->sm_count;
-  cfg.blocks_per_sm = 0;
+  cfg.blocks_per_sm = 0;        /* the grid nnsb_plan_launch uses: identical results */
 
   /* layout inside the array: [block partial sums][per-tensor {mean, std}] */
-  const size_t partial_doubles = nnsb::stand_scratch_doubles (batch, nch, frame_elems, cfg);
+  size_t partial_doubles = nnsb::stand_scratch_doubles (batch, nch, frame_elems, cfg);
   const size_t stats_doubles = (size_t) batch * nch * 2;
-  const size_t need_bytes = (partial_doubles + stats_doubles) * sizeof (double);
+  size_t need_bytes = (partial_doubles + stats_doubles) * sizeof (double);
+  if (need_bytes > NNSB_NOALLOC_SCRATCH_BYTES) {
+    /* the default grid keeps more block partials than the array holds (many channels): fall
+     * back to four blocks per SM, a little slower, same arithmetic in another summation order */
+    cfg.blocks_per_sm = 4;
+    partial_doubles = nnsb::stand_scratch_doubles (batch, nch, frame_elems, cfg);
+    need_bytes = (partial_doubles + stats_doubles) * sizeof (double);
+  }
   if (need_bytes > NNSB_NOALLOC_SCRATCH_BYTES)
     return nnsb_set_error (NNSB_ERANGE,
         "nnsb_stand_launch_noalloc: batch %u x %u channel(s) needs %zu bytes of scratch, the "
