@@ -314,6 +314,150 @@ blocks_for_invariant_channels (size_t blocks, uint64_t elems_per_block, uint64_t
   return blocks / need * need;
 }
 
+/* ------------------------------------------------------------------------------------- */
+/* float32 working type, inputs wider than a byte: the generic kernel above is issue-bound     */
+/* (operand fetch, NaN fix-up branches and a ~12-instruction IEEE division per element and     */
+/* position: 2.1-4.5 TB/s).  This kernel runs a FAST chain per vector and falls back to the   */
+/* careful one (chain_apply, identical by construction) for the vectors that need it:         */
+/*   - operands come from registers (scalar chains) or a tiny shared-memory table indexed by   */
+/*     a per-lane channel offset that is loop-invariant (the launcher sizes the grid so that   */
+/*     one grid stride is a multiple of the channel period);                                   */
+/*   - add / mul are the plain IEEE operations; they differ from the careful path only when    */
+/*     the result is NaN (x86 payload rules) -- checked once per vector at the end;            */
+/*   - x / d with the host-provided r = RN (1 / d) is Markstein's correctly rounded            */
+/*     q0 = RN (x r), e = x - d q0 (exact, FMA), q = RN (q0 + e r); valid without over- or       */
+/*     underflow, which the kernel guarantees by taking the fast result only for               */
+/*     2^-63 <= |x| <= 2^63 (the host admits 2^-30 <= |d| <= 2^30, significand not all ones)   */
+/*     and +-0 (q0 has the right sign); anything else marks the vector for the careful path.   */
+/* ------------------------------------------------------------------------------------- */
+constexpr int FCHAIN_MAX_POS = 4;
+constexpr int FCHAIN_MAX_NCH = 64;
+
+template <typename In, bool ORC, int U>
+__global__ void __launch_bounds__ (CHAIN_THREADS)
+fchain_kernel (const In *__restrict__ in, float *__restrict__ out, size_t n, size_t n_vec,
+    const __grid_constant__ ChainDev p)
+{
+  constexpr int V = ChainVec<In, float>::V;
+  __shared__ unsigned long long s_tab[FCHAIN_MAX_POS * FCHAIN_MAX_NCH];
+  const size_t tid = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t nthreads = (size_t) gridDim.x * blockDim.x;
+  const bool perch = p.nch > 1;
+  if (perch) {
+    for (int i = threadIdx.x; i < p.n_pos * p.nch; i += CHAIN_THREADS)
+      s_tab[i] = p.table[i].raw;
+    __syncthreads ();
+  }
+  /* channel of lane k: the same for every vector this thread touches */
+  uint32_t ch[V];
+  {
+    uint64_t rr = 0;
+    uint32_t cc = 0;
+    if (perch) {
+      const uint64_t e0 = (uint64_t) tid * V;
+      rr = e0 % p.ch_size;
+      cc = (uint32_t) ((e0 / p.ch_size) % (uint64_t) p.nch);
+    }
+#pragma unroll
+    for (int k = 0; k < V; k++) {
+      ch[k] = cc;
+      if (perch && ++rr == p.ch_size) {
+        rr = 0;
+        cc = (cc + 1 == (uint32_t) p.nch) ? 0 : cc + 1;
+      }
+    }
+  }
+
+  for (size_t v = tid; v < n_vec; v += nthreads * U) {
+    Vec<In, V> x[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const size_t vu = v + (size_t) u * nthreads;
+      if (vu < n_vec)
+        load_vec (x[u], in + vu * V);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const size_t vu = v + (size_t) u * nthreads;
+      if (vu >= n_vec)
+        continue;
+      Vec<float, V> y;
+#pragma unroll
+      for (int k = 0; k < V; k++)
+        y.e[k] = Cast<float, In, ORC>::run (x[u].e[k]);
+      bool bad = false;
+      for (int pos = 0; pos < p.n_pos; pos++) {
+        const int opc = p.opcode[pos];
+        const unsigned long long sc = p.scalar[pos].raw;
+        float c[V], r[V];
+#pragma unroll
+        for (int k = 0; k < V; k++) {
+          const unsigned long long cell = perch ? s_tab[pos * p.nch + ch[k]] : sc;
+          c[k] = __uint_as_float ((uint32_t) cell);
+          r[k] = __uint_as_float ((uint32_t) (cell >> 32));
+        }
+        if (opc == NNSB_OP_ADD) {
+#pragma unroll
+          for (int k = 0; k < V; k++)
+            y.e[k] = __fadd_rn (y.e[k], c[k]);
+        } else if (opc == NNSB_OP_MUL) {
+#pragma unroll
+          for (int k = 0; k < V; k++)
+            y.e[k] = __fmul_rn (y.e[k], c[k]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < V; k++) {
+            const float a = y.e[k];
+            const uint32_t ea = (__float_as_uint (a) >> 23) & 0xffu;
+            const float q0 = __fmul_rn (a, r[k]);
+            const float e = __fmaf_rn (-c[k], q0, a);
+            const float q1 = __fmaf_rn (e, r[k], q0);
+            const bool zero = a == 0.0f;
+            bad = bad || (!zero && (ea - 64u) > 126u);
+            y.e[k] = zero ? q0 : q1;
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < V; k++)
+        bad = bad || !(y.e[k] == y.e[k]);
+      if (bad) {
+        /* NaN, infinity, denormal or out-of-range dividend somewhere in this vector */
+#pragma unroll
+        for (int k = 0; k < V; k++)
+          y.e[k] = Cast<float, In, ORC>::run (x[u].e[k]);
+        chain_apply<float, ORC, V> (y, ch, p, perch);
+      }
+      store_vec (out + vu * V, y);
+    }
+  }
+
+  /* scalar tail (and the whole tensor when the pointers are not vector-aligned) */
+  for (size_t e = n_vec * V + tid; e < n; e += nthreads) {
+    Vec<float, 1> y;
+    uint32_t c1[1] = { 0 };
+    In xv;
+    ld_stream<sizeof (In)> (&xv, in + e);
+    y.e[0] = Cast<float, In, ORC>::run (xv);
+    if (perch)
+      c1[0] = (uint32_t) (((uint64_t) e / p.ch_size) % (uint64_t) p.nch);
+    chain_apply<float, ORC, 1> (y, c1, p, perch);
+    st_stream<sizeof (float)> (out + e, &y.e[0]);
+  }
+}
+
+/* all divisors carry a reciprocal (nnsb_chain_compile) and the chain fits the kernel */
+static inline bool
+fchain_eligible (const ChainArgs &args)
+{
+  const int n_pos = args.desc.n_pos, nch = args.desc.nch > 0 ? args.desc.nch : 1;
+  if (n_pos < 1 || n_pos > FCHAIN_MAX_POS || nch > FCHAIN_MAX_NCH)
+    return false;
+  if (nch > 1 && !args.table)
+    return false;
+  return true;
+}
+
 template <typename In, typename Out, bool ORC>
 int launch_chain_t (const void *in, void *out, size_t n, const ChainArgs &args,
     const LaunchCfg &cfg, cudaStream_t stream)
@@ -375,6 +519,18 @@ int launch_chain_t (const void *in, void *out, size_t n, const ChainArgs &args,
       lut_chain_kernel<In, Out, ORC, U><<<(unsigned int) lb, CHAIN_THREADS, lut_bytes, stream>>> (
           (const In *) in, (Out *) out, n, l_vec, p);
       return (int) cudaGetLastError ();
+    }
+  }
+
+  if constexpr (sizeof (Out) == 4 && IsFloat<Out>::v && sizeof (In) > 1) {
+    if (args.fast_f32 && fchain_eligible (args)) {
+      const uint64_t period = p.ch_size * (uint64_t) p.nch;
+      const size_t fb = blocks_for_invariant_channels (blocks, (uint64_t) CHAIN_THREADS * V, period);
+      if (fb) {
+        fchain_kernel<In, ORC, U><<<(unsigned int) fb, CHAIN_THREADS, 0, stream>>> ((const In *) in,
+            (float *) out, n, n_vec, p);
+        return (int) cudaGetLastError ();
+      }
     }
   }
 

@@ -38,6 +38,7 @@ struct ChainArgs
 {
   nnsb_chain_desc desc;
   const nnsb_cell *table;       /* device, [n_pos][nch]; used when nch > 1 */
+  int fast_f32;                 /* float32 chain whose divisors all carry a reciprocal */
 };
 int launch_chain (int in_type, int out_type, bool orc, const void *in, void *out, size_t n,
     const ChainArgs & args, const LaunchCfg & cfg, cudaStream_t stream);

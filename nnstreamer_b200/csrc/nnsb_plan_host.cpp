@@ -208,6 +208,28 @@ nnsb_chain_compile (const nnsb_option * opt, int work_type, int acceleration,
   if (pos.size () > NNSB_MAX_OPS)
     return nnsb_set_error (NNSB_EINVAL, "arithmetic: chain too long");
 
+  if (work_type == NNSB_FLOAT32) {
+    /* float32 chains: the upper half of every divisor cell carries RN (1 / d) for the
+     * division-by-constant of the fast kernel (k_chain.cuh, fchain_kernel); 0 = not eligible
+     * (then the launch takes the generic kernel).  Other cells keep a zero upper half. */
+    for (auto & ps : pos)
+      for (auto & cell : ps.val) {
+        const uint32_t lo = (uint32_t) (cell.raw & 0xffffffffu);
+        uint32_t hi = 0;
+        if (ps.opcode == NNSB_OP_DIV) {
+          float d;
+          memcpy (&d, &lo, sizeof (d));
+          const uint32_t expo = (lo >> 23) & 0xffu, frac = lo & 0x7fffffu;
+          /* normal, 2^-30 <= |d| <= 2^30, significand not all ones (Markstein's exception) */
+          if (expo >= 97 && expo <= 157 && frac != 0x7fffffu) {
+            const float r = 1.0f / d;   /* correctly rounded (no contraction, SSE) */
+            memcpy (&hi, &r, sizeof (hi));
+          }
+        }
+        cell.raw = ((uint64_t) hi << 32) | lo;
+      }
+  }
+
   desc->n_pos = (int32_t) pos.size ();
   desc->nch = (int32_t) nch;
   desc->ch_size = ch_size;

@@ -603,6 +603,22 @@ nnsb_plan_create (nnsb_ctx * ctx, const nnsb_option * opt, const nnsb_tensor_inf
         }
         plan->chain.table = plan->d_table;
       }
+      if (r == NNSB_OK && plan->out_info.type == NNSB_FLOAT32 && !getenv ("NNSB_CHAIN_NO_FAST")) {
+        /* the fast float32 kernel needs a reciprocal next to every divisor */
+        const nnsb_chain_desc & dsc = plan->chain.desc;
+        bool ok = true;
+        for (int i = 0; i < dsc.n_pos && ok; i++) {
+          if (dsc.opcode[i] != NNSB_OP_DIV)
+            continue;
+          if (table) {
+            for (int c = 0; c < dsc.nch && ok; c++)
+              ok = (table[(size_t) i * dsc.nch + c].raw >> 32) != 0;
+          } else {
+            ok = (dsc.scalar[i].raw >> 32) != 0;
+          }
+        }
+        plan->chain.fast_f32 = ok ? 1 : 0;
+      }
       free (table);
       if (r) {
         nnsb_plan_destroy (plan);
@@ -812,8 +828,8 @@ nnsb_plan_describe (const nnsb_plan * plan, char *buf, size_t buflen)
       break;
     case NNSB_MODE_TYPECAST:
     case NNSB_MODE_ARITHMETIC:
-      len = snprintf (buf, buflen, "chain: %d position(s), %d channel(s)", (int) plan->chain.desc.n_pos,
-          (int) plan->chain.desc.nch);
+      len = snprintf (buf, buflen, "chain: %d position(s), %d channel(s)%s", (int) plan->chain.desc.n_pos,
+          (int) plan->chain.desc.nch, plan->chain.fast_f32 ? ", float32 fast path" : "");
       break;
     case NNSB_MODE_STAND:
       len = snprintf (buf, buflen, "stand: %u channel(s)", plan->stand_nch);

@@ -209,6 +209,82 @@ def test_arith_float_chain_random_f32_bitexact(dev, port):
     _arith_case(dev, port, xd, [n], "div:3.0,mul:1.7", [("div", 3.0), ("mul", 1.7)])
 
 
+FAST_CHAINS = [
+    # option, oracle ops, per-channel dim (None = scalar chain)
+    ("div:127.5", [("div", 127.5)], None),
+    ("add:-127.5,div:127.5", [("add", -127.5), ("div", 127.5)], None),
+    ("mul:0.017,div:3.0,add:1.5", [("mul", 0.017), ("div", 3.0), ("add", 1.5)], None),
+    ("div:0.1,div:-7e8", [("div", 0.1), ("div", -7e8)], None),
+    ("div:1e-5,mul:1e-5", [("div", 1e-5), ("mul", 1e-5)], None),
+    ("div:1.0000001", [("div", 1.0000001)], None),
+    ("div:1.9999999", [("div", 1.9999999)], None),          # significand all ones: generic kernel
+    ("div:1e12", [("div", 1e12)], None),                    # outside 2^+-30: generic kernel
+    ("per-channel:true@0,add:-123.675@0,add:-116.28@1,add:-103.53@2,div:58.395@0,div:57.12@1,div:57.375@2",
+     [("add", -123.675, 0), ("add", -116.28, 1), ("add", -103.53, 2), ("div", 58.395, 0),
+      ("div", 57.12, 1), ("div", 57.375, 2)], 0),
+    ("per-channel:true@1,div:3@0,mul:2@1,div:-0.7@3", [("div", 3, 0), ("mul", 2, 1), ("div", -0.7, 3)], 1),
+]
+
+
+@pytest.mark.parametrize("case", FAST_CHAINS, ids=lambda c: c[0][:40])
+def test_float32_fast_chain_is_bit_identical_to_the_careful_path(dev, port, case, monkeypatch):
+    """fchain_kernel (division by constant through a correctly rounded reciprocal, NaN check per
+    vector) against the generic kernel on 2^23 arbitrary bit patterns (NaNs with payloads,
+    infinities, denormals, zeros of both signs) and 2^23 image-range values, and against the
+    oracle (gsttensor_transform.c:563-645) on a subset.  Bit-exact."""
+    opt, ops, ch_dim = case
+    n = 1 << 23
+    dim = [4, 1 << 10, n >> 12, 1] if ch_dim is not None else [n]
+    rng = np.random.default_rng(len(opt))
+    bits = rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32)
+    bits[:64] = np.array([0, 0x80000000, 1, 0x80000001, 0x7f800000, 0xff800000, 0x7fc00000, 0x7f800001,
+                          0x00800000, 0x007fffff, 0x7f7fffff, 0x1f800000, 0x5f000000, 0x5f800000,
+                          0x1f7fffff, 0x20000000] * 4, dtype=np.uint32)
+    if ch_dim is not None:
+        # Channels an operator does not apply to go through an identity operand (x + -0, x / 1):
+        # exact for every value except that a SIGNALLING NaN comes out quieted where the reference
+        # leaves the element untouched (DESIGN.md section 5) -- keep signalling NaNs out of here.
+        snan = ((bits & 0x7f800000) == 0x7f800000) & ((bits & 0x007fffff) != 0) & ((bits & 0x00400000) == 0)
+        bits[snan] |= 0x00400000
+    for x in (bits.view(np.float32), (rng.random(n, dtype=np.float32) * 255.0)):
+        monkeypatch.delenv("NNSB_CHAIN_NO_FAST", raising=False)
+        fast = dev.plan("arithmetic", opt, "float32", dim)
+        monkeypatch.setenv("NNSB_CHAIN_NO_FAST", "1")
+        slow = dev.plan("arithmetic", opt, "float32", dim)
+        monkeypatch.delenv("NNSB_CHAIN_NO_FAST", raising=False)
+        assert "fast path" not in slow.describe()
+        if "1.9999999" in opt or "1e12" in opt:
+            assert "fast path" not in fast.describe()
+        else:
+            assert "fast path" in fast.describe(), fast.describe()
+        got = fast.run_host(x)
+        ref = slow.run_host(x)
+        fast.close()
+        slow.close()
+        assert bits_equal(got, ref), "%s: %s" % (opt, first_mismatch(got, ref))
+        m = 1 << 16
+        sub = [m] if ch_dim is None else [4, 1 << 10, m >> 12, 1]
+        want = port.arithmetic(x[:m], sub, ops, ch_dim is not None, ch_dim or 0)
+        assert bits_equal(got[:m], want), "%s vs oracle: %s" % (opt, first_mismatch(got[:m], want))
+
+
+@pytest.mark.parametrize("in_type", ["int32", "uint16", "int16", "float64", "int64", "float16"])
+def test_float32_fast_chain_other_input_types(dev, port, in_type):
+    n = 3 * 640 * 48
+    dim = [3, 640, 48, 1]
+    x = rand_small(in_type, n, seed=77)
+    opt = ("typecast:float32,per-channel:true@0,add:-123.675@0,add:-116.28@1,add:-103.53@2,"
+           "div:58.395@0,div:57.12@1,div:57.375@2")
+    ops = [("typecast", "float32"), ("add", -123.675, 0), ("add", -116.28, 1), ("add", -103.53, 2),
+           ("div", 58.395, 0), ("div", 57.12, 1), ("div", 57.375, 2)]
+    plan = dev.plan("arithmetic", opt, in_type, dim)
+    assert "fast path" in plan.describe()
+    got = plan.run_host(x)
+    plan.close()
+    want = port.arithmetic(x, dim, ops, True, 0)
+    assert bits_equal(got, want), first_mismatch(got, want)
+
+
 # ---------------------------------------------------------------------------------------
 # transpose / dimchg
 # ---------------------------------------------------------------------------------------
