@@ -333,8 +333,30 @@ blocks_for_invariant_channels (size_t blocks, uint64_t elems_per_block, uint64_t
 constexpr int FCHAIN_MAX_POS = 4;
 constexpr int FCHAIN_MAX_NCH = 64;
 
+/* the careful chain for one vector, out of line: it runs for a handful of vectors at most and
+ * must not cost the fast path its registers */
+template <int V> struct ChanIdx
+{
+  uint32_t c[V];
+};
+
+template <typename In, bool ORC, int V>
+__device__ __noinline__ Vec<float, V>
+fchain_careful (Vec<In, V> x, ChanIdx<V> ch, const ChainDev &p, bool perch)
+{
+  Vec<float, V> y;
+#pragma unroll
+  for (int k = 0; k < V; k++)
+    y.e[k] = Cast<float, In, ORC>::run (x.e[k]);
+  chain_apply<float, ORC, V> (y, ch.c, p, perch);
+  return y;
+}
+
+#ifndef NNSB_FCHAIN_MIN_BLOCKS
+#define NNSB_FCHAIN_MIN_BLOCKS 3
+#endif
 template <typename In, bool ORC, int U>
-__global__ void __launch_bounds__ (CHAIN_THREADS)
+__global__ void __launch_bounds__ (CHAIN_THREADS, NNSB_FCHAIN_MIN_BLOCKS)
 fchain_kernel (const In *__restrict__ in, float *__restrict__ out, size_t n, size_t n_vec,
     const __grid_constant__ ChainDev p)
 {
@@ -344,8 +366,9 @@ fchain_kernel (const In *__restrict__ in, float *__restrict__ out, size_t n, siz
   const size_t nthreads = (size_t) gridDim.x * blockDim.x;
   const bool perch = p.nch > 1;
   if (perch) {
+    /* [channel][position]: a lane's operands sit at (its channel offset) + constant */
     for (int i = threadIdx.x; i < p.n_pos * p.nch; i += CHAIN_THREADS)
-      s_tab[i] = p.table[i].raw;
+      s_tab[(i % p.nch) * FCHAIN_MAX_POS + i / p.nch] = p.table[i].raw;
     __syncthreads ();
   }
   /* channel of lane k: the same for every vector this thread touches */
@@ -386,13 +409,16 @@ fchain_kernel (const In *__restrict__ in, float *__restrict__ out, size_t n, siz
       for (int k = 0; k < V; k++)
         y.e[k] = Cast<float, In, ORC>::run (x[u].e[k]);
       bool bad = false;
-      for (int pos = 0; pos < p.n_pos; pos++) {
+#pragma unroll
+      for (int pos = 0; pos < FCHAIN_MAX_POS; pos++) {
+        if (pos >= p.n_pos)
+          break;
         const int opc = p.opcode[pos];
         const unsigned long long sc = p.scalar[pos].raw;
         float c[V], r[V];
 #pragma unroll
         for (int k = 0; k < V; k++) {
-          const unsigned long long cell = perch ? s_tab[pos * p.nch + ch[k]] : sc;
+          const unsigned long long cell = perch ? s_tab[ch[k] * FCHAIN_MAX_POS + pos] : sc;
           c[k] = __uint_as_float ((uint32_t) cell);
           r[k] = __uint_as_float ((uint32_t) (cell >> 32));
         }
@@ -423,10 +449,11 @@ fchain_kernel (const In *__restrict__ in, float *__restrict__ out, size_t n, siz
         bad = bad || !(y.e[k] == y.e[k]);
       if (bad) {
         /* NaN, infinity, denormal or out-of-range dividend somewhere in this vector */
+        ChanIdx<V> ci;
 #pragma unroll
         for (int k = 0; k < V; k++)
-          y.e[k] = Cast<float, In, ORC>::run (x[u].e[k]);
-        chain_apply<float, ORC, V> (y, ch, p, perch);
+          ci.c[k] = ch[k];
+        y = fchain_careful<In, ORC, V> (x[u], ci, p, perch);
       }
       store_vec (out + vu * V, y);
     }
