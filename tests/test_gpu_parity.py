@@ -451,7 +451,11 @@ def test_clamp_every_type(dev, port, dtype):
     n = 9001
     x = rand_full(dtype, n, seed=70)
     for lo, hi, opt in ((-50.0, 50.0, "-50:50"), (20.0, 80.0, "+20:80"), (-33.3, 77.7, "-33.3:+77.7"),
-                        (0.0, 0.0, "0:0"), (-1e30, 1e30, "-1e30:1e30"), (1e10, 1e18, "1e10:1e18")):
+                        (0.0, 0.0, "0:0"), (-1e30, 1e30, "-1e30:1e30"), (1e10, 1e18, "1e10:1e18"),
+                        (-0.5, 0.5, "-0.5:0.5"), (254.5, 300.0, "254.5:300"),
+                        (-200.7, -100.2, "-200.7:-100.2"), (3e9, 4e9, "3e9:4e9"),
+                        (-1e18, -1e10, "-1e18:-1e10"), (-32768.5, 65535.5, "-32768.5:65535.5"),
+                        (127.0, 128.0, "127:128"), (-2147483648.0, 2147483647.0, "-2147483648:2147483647")):
         plan = dev.plan("clamp", opt, dtype, [n])
         got = plan.run_host(x)
         plan.close()
