@@ -78,8 +78,11 @@ chain_apply (Vec<Out, V> &y, const uint32_t (&ch)[V], const ChainDev &p, bool pe
   }
 }
 
+#ifndef NNSB_CHAIN_MIN_BLOCKS
+#define NNSB_CHAIN_MIN_BLOCKS 3
+#endif
 template <typename In, typename Out, bool ORC, int U>
-__global__ void __launch_bounds__ (CHAIN_THREADS)
+__global__ void __launch_bounds__ (CHAIN_THREADS, NNSB_CHAIN_MIN_BLOCKS)
 chain_kernel (const In *__restrict__ in, Out *__restrict__ out, size_t n, size_t n_vec,
     const __grid_constant__ ChainDev p)
 {
