@@ -1,7 +1,8 @@
 /*
  * k_perm_vec.cu -- K3/K4 vector path: rank-N permutation copy with 16-byte global accesses on
- * both sides, for 4-, 8- and 16-byte elements (an innermost block that is common to both
- * sides -- RGBA bytes, a float4 -- is folded into the element first).
+ * both sides, for every element size (an innermost block that is common to both sides --
+ * RGBA bytes, a float4 -- is folded into the element first; 1- and 2-byte elements gather
+ * 16 / 8 of them per output vector).
  *
  * Same job as permute_kernel (k_perm.cu): the per-element nns_memcpy nest of
  * gst_tensor_transform_transpose (gsttensor_transform.c:1417-1500) and the block memcpy nest
@@ -111,10 +112,35 @@ inside4 (uint64_t c, uint64_t lim)
   return ok;
 }
 
+/* slots per store vector kept in registers: one per element for 4/8/16-byte elements, two
+ * 16-bit slots per register for 1- and 2-byte elements (16 / 8 elements per vector) */
+template <int ES> struct PvSlots
+{
+  static constexpr int N = ES < 4 ? (16 / ES) / 2 : 16 / ES;
+};
+
 template <int ES> __device__ __forceinline__ void
 gather (uint32_t stage_addr, const uint32_t *slot, uint32_t *w)
 {
-  if constexpr (ES == 4) {
+  if constexpr (ES == 1) {
+    w[0] = w[1] = w[2] = w[3] = 0;
+#pragma unroll
+    for (int e = 0; e < 16; e++) {
+      const uint32_t sl = (slot[e >> 1] >> (16 * (e & 1))) & 0xffffu;
+      uint32_t v;
+      asm volatile ("ld.shared.u8 %0, [%1];" : "=r" (v) : "r" (stage_addr + sl));
+      w[e >> 2] |= v << (8 * (e & 3));
+    }
+  } else if constexpr (ES == 2) {
+    w[0] = w[1] = w[2] = w[3] = 0;
+#pragma unroll
+    for (int e = 0; e < 8; e++) {
+      const uint32_t sl = (slot[e >> 1] >> (16 * (e & 1))) & 0xffffu;
+      uint32_t v;
+      asm volatile ("ld.shared.u16 %0, [%1];" : "=r" (v) : "r" (stage_addr + sl));
+      w[e >> 1] |= v << (16 * (e & 1));
+    }
+  } else if constexpr (ES == 4) {
 #pragma unroll
     for (int e = 0; e < 4; e++)
       asm volatile ("ld.shared.u32 %0, [%1];" : "=r" (w[e]) : "r" (stage_addr + slot[e]));
@@ -133,7 +159,7 @@ gather (uint32_t stage_addr, const uint32_t *slot, uint32_t *w)
  * (whole shared-memory chunks; entry [j] of st_slot holds chunk j % VE of block j / VE) feed VE
  * output vectors, instead of VE scalar LDS per vector. */
 template <int ES, bool MICRO>
-__global__ void __launch_bounds__ (PV_THREADS, NNSB_PV_MIN_BLOCKS)
+__global__ void __launch_bounds__ (PV_THREADS, ES < 4 ? 2 : NNSB_PV_MIN_BLOCKS)
 permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
     const unsigned char *__restrict__ table, const __grid_constant__ PermVecDev p)
 {
@@ -142,7 +168,7 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
   const uint32_t ring_addr = (uint32_t) __cvta_generic_to_shared (ring);
 
   /* this thread's share of the box, from the host-built table */
-  uint32_t ld_off[PV_VPT], ld_slot[PV_VPT], st_off[PV_VPT], st_slot[PV_VPT][VE];
+  uint32_t ld_off[PV_VPT], ld_slot[PV_VPT], st_off[PV_VPT], st_slot[PV_VPT][PvSlots<ES>::N];
   {
     const uint32_t *t_ld_off = reinterpret_cast<const uint32_t *> (table + PV_T_LD_OFF);
     const uint32_t *t_ld_slot = reinterpret_cast<const uint32_t *> (table + PV_T_LD_SLOT);
@@ -154,7 +180,13 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
       ld_off[j] = t_ld_off[i];
       ld_slot[j] = ring_addr + t_ld_slot[i];
       st_off[j] = t_st_off[i];
-      if constexpr (VE == 4) {
+      if constexpr (ES < 4) {
+        /* packed pairs, straight from the table */
+        const uint32_t *packed = reinterpret_cast<const uint32_t *> (t_st_slot + (size_t) i * VE);
+#pragma unroll
+        for (int q = 0; q < PvSlots<ES>::N; q++)
+          st_slot[j][q] = packed[q];
+      } else if constexpr (VE == 4) {
         const uint2 s = *reinterpret_cast<const uint2 *> (t_st_slot + (size_t) i * 4);
         st_slot[j][0] = s.x & 0xffffu;
         st_slot[j][1] = s.x >> 16;
@@ -402,7 +434,9 @@ uint64_t
 gather_cost (const uint32_t *lin, uint32_t n_vec, int ve, int es, const Swizzle &sw)
 {
   uint64_t cost = 0;
-  const int lanes = 128 / es, banks = 128 / es;
+  /* 1/2-byte accesses: a warp at a time, 32 banks of 4 bytes, distinct words per bank */
+  const int lanes = es < 4 ? 32 : 128 / es, banks = lanes;
+  const int per_word = es < 4 ? 4 / es : 1;
   for (uint32_t base = 0; base < n_vec; base += lanes) {
     for (int e = 0; e < ve; e++) {
       uint32_t words[32][32];
@@ -411,7 +445,7 @@ gather_cost (const uint32_t *lin, uint32_t n_vec, int ve, int es, const Swizzle 
       int worst = 0;
       for (int l = 0; l < lanes && base + l < n_vec; l++) {
         const uint32_t li = lin[(size_t) (base + l) * ve + e];
-        const uint32_t w = sw (li / ve) * ve + li % ve;         /* element-sized word index */
+        const uint32_t w = (sw (li / ve) * ve + li % ve) / per_word;  /* bank-unit word index */
         const int b = (int) (w % banks);
         bool dup = false;
         for (int k = 0; k < count[b]; k++)
@@ -550,7 +584,7 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
   const int n = B.n, es = B.es;
   if (n < 2)
     return -1;                  /* identity: the flat copy */
-  if (es != 4 && es != 8 && es != 16)
+  if (es != 1 && es != 2 && es != 4 && es != 8 && es != 16)
     return -1;
   const uint64_t VE = B.VE = 16 / es;
   const uint64_t TILE_MAX = B.TILE_MAX = PV_STAGE_BYTES / es;
@@ -868,6 +902,8 @@ launch_permute_vec (const PermVecPlan &pl, const void *d_table, const void *in, 
   p.n_vec = pl.n_vec;
   p.n_tiles = (uint32_t) tiles;
   switch (pl.es) {
+    case 1: return launch_permute_vec_t<1, false> (p, d_table, in, out, cfg, stream);
+    case 2: return launch_permute_vec_t<2, false> (p, d_table, in, out, cfg, stream);
     case 4: return pl.micro ? launch_permute_vec_t<4, true> (p, d_table, in, out, cfg, stream)
           : launch_permute_vec_t<4, false> (p, d_table, in, out, cfg, stream);
     case 8: return pl.micro ? launch_permute_vec_t<8, true> (p, d_table, in, out, cfg, stream)

@@ -359,6 +359,11 @@ VEC_CASES = [
     ("float64", [3, 130, 98, 1], 2),      # 2-element vectors
     ("int64", [6, 34, 18, 1], 1),
     ("int32", [64, 64, 64, 1], 1),
+    ("uint8", [3, 192, 112, 1], 2),       # 1-byte elements: 16 gathered per output vector
+    ("uint8", [3, 160, 80, 1], 1),
+    ("int8", [16, 48, 40, 1], 1),
+    ("uint16", [3, 64, 48, 1], 3),        # 2-byte elements: 8 per vector
+    ("float16", [5, 32, 24, 1], 1),
     ("uint32", [5, 7, 9, 1], 4),          # odd sizes: must fall back to the scalar kernel
 ]
 

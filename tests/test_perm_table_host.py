@@ -48,6 +48,10 @@ CASES = [
     (1, 2, (4, 68, 36, 1)),         # RGBA bytes fold into one 4-byte element
     (1, 1, (16, 20, 12, 1)),
     (2, 3, (8, 12, 20, 1)),
+    (1, 1, (3, 192, 112, 1)),       # RGB bytes: 16 one-byte elements per vector
+    (1, 2, (3, 160, 80, 1)),
+    (2, 1, (3, 64, 48, 1)),         # 8 two-byte elements per vector
+    (2, 2, (5, 32, 24, 1)),
     (4, 1, (3, 3840, 16, 1)),       # long rows
     (4, 1, (1, 2160, 512, 1)),      # plain 2-D transposes
 ]
@@ -71,6 +75,9 @@ def test_expected_boxes(checker):
     # odd sizes cannot be vectorised: the scalar kernel takes them
     rc, out = run(checker, 4, 4, (5, 7, 9, 1), (2, 1, 0, 3))
     assert rc == 0 and out == "ineligible", out
-    # 1- and 2-byte elements without a common innermost block are not eligible either
-    rc, out = run(checker, 1, 1, (3, 64, 64, 1), (2, 1, 0, 3))
+    # rows that are not 16-byte multiples cannot be vectorised (1080 RGB bytes = 3240)
+    rc, out = run(checker, 1, 1, (3, 1080, 1920, 1), (0, 2, 1, 3))
     assert rc == 0 and out == "ineligible", out
+    # one-byte elements: 16 per vector
+    rc, out = run(checker, 1, 1, (3, 1920, 1088, 1), (0, 2, 1, 3))
+    assert rc == 0 and "es=1" in out and out.startswith("ok"), out
