@@ -74,31 +74,47 @@ struct PermVecDev
   uint32_t n_tiles;
 };
 
-__device__ __forceinline__ void
-cp_async_16 (uint32_t smem_dst, const void *gmem_src)
+/* one vector global -> shared: 16 bytes bypass L1 (.cg), 8 and 4 bytes exist only as .ca */
+template <int VB> __device__ __forceinline__ void
+cp_async_vec (uint32_t smem_dst, const void *gmem_src)
 {
-  asm volatile ("cp.async.cg.shared.global [%0], [%1], 16;" :: "r" (smem_dst), "l" (gmem_src) : "memory");
+  if constexpr (VB == 16)
+    asm volatile ("cp.async.cg.shared.global [%0], [%1], 16;" :: "r" (smem_dst), "l" (gmem_src) : "memory");
+  else if constexpr (VB == 8)
+    asm volatile ("cp.async.ca.shared.global [%0], [%1], 8;" :: "r" (smem_dst), "l" (gmem_src) : "memory");
+  else
+    asm volatile ("cp.async.ca.shared.global [%0], [%1], 4;" :: "r" (smem_dst), "l" (gmem_src) : "memory");
 }
 
-__device__ __forceinline__ void
-cp_async_16_if (bool on, uint32_t smem_dst, const void *gmem_src)
+template <int VB> __device__ __forceinline__ void
+cp_async_vec_if (bool on, uint32_t smem_dst, const void *gmem_src)
 {
-  asm volatile ("{\n"
-      ".reg .pred p;\n"
-      "setp.ne.u32 p, %2, 0;\n"
-      "@p cp.async.cg.shared.global [%0], [%1], 16;\n"
-      "}\n" :: "r" (smem_dst), "l" (gmem_src), "r" ((uint32_t) on) : "memory");
+  if constexpr (VB == 16) {
+    asm volatile ("{\n"
+        ".reg .pred p;\n"
+        "setp.ne.u32 p, %2, 0;\n"
+        "@p cp.async.cg.shared.global [%0], [%1], 16;\n"
+        "}\n" :: "r" (smem_dst), "l" (gmem_src), "r" ((uint32_t) on) : "memory");
+  } else {
+    if (on)
+      cp_async_vec<VB> (smem_dst, gmem_src);
+  }
 }
 
-__device__ __forceinline__ void
-st_stream_16_if (bool on, void *dst, const uint32_t *w)
+template <int VB> __device__ __forceinline__ void
+st_stream_vec_if (bool on, void *dst, const uint32_t *w)
 {
-  asm volatile ("{\n"
-      ".reg .pred p;\n"
-      "setp.ne.u32 p, %5, 0;\n"
-      "@p st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};\n"
-      "}\n" :: "l" (dst), "r" (w[0]), "r" (w[1]), "r" (w[2]), "r" (w[3]), "r" ((uint32_t) on)
-      : "memory");
+  if constexpr (VB == 16) {
+    asm volatile ("{\n"
+        ".reg .pred p;\n"
+        "setp.ne.u32 p, %5, 0;\n"
+        "@p st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};\n"
+        "}\n" :: "l" (dst), "r" (w[0]), "r" (w[1]), "r" (w[2]), "r" (w[3]), "r" ((uint32_t) on)
+        : "memory");
+  } else {
+    if (on)
+      st_stream<VB> (dst, w);
+  }
 }
 
 /* all four 16-bit fields of c below the matching field of lim */
@@ -114,27 +130,34 @@ inside4 (uint64_t c, uint64_t lim)
 
 /* slots per store vector kept in registers: one per element for 4/8/16-byte elements, two
  * 16-bit slots per register for 1- and 2-byte elements (16 / 8 elements per vector) */
-template <int ES> struct PvSlots
+template <int ES, int VB> struct PvSlots
 {
-  static constexpr int N = ES < 4 ? (16 / ES) / 2 : 16 / ES;
+  static constexpr int VE = VB / ES;
+  static constexpr int N = ES < 4 ? (VE + 1) / 2 : VE;
 };
 
-template <int ES> __device__ __forceinline__ void
+/* the VB / ES elements of one output vector out of shared memory */
+template <int ES, int VB> __device__ __forceinline__ void
 gather (uint32_t stage_addr, const uint32_t *slot, uint32_t *w)
 {
+  constexpr int VE = VB / ES;
   if constexpr (ES == 1) {
-    w[0] = w[1] = w[2] = w[3] = 0;
 #pragma unroll
-    for (int e = 0; e < 16; e++) {
+    for (int q = 0; q < VB / 4; q++)
+      w[q] = 0;
+#pragma unroll
+    for (int e = 0; e < VE; e++) {
       const uint32_t sl = (slot[e >> 1] >> (16 * (e & 1))) & 0xffffu;
       uint32_t v;
       asm volatile ("ld.shared.u8 %0, [%1];" : "=r" (v) : "r" (stage_addr + sl));
       w[e >> 2] |= v << (8 * (e & 3));
     }
   } else if constexpr (ES == 2) {
-    w[0] = w[1] = w[2] = w[3] = 0;
 #pragma unroll
-    for (int e = 0; e < 8; e++) {
+    for (int q = 0; q < VB / 4; q++)
+      w[q] = 0;
+#pragma unroll
+    for (int e = 0; e < VE; e++) {
       const uint32_t sl = (slot[e >> 1] >> (16 * (e & 1))) & 0xffffu;
       uint32_t v;
       asm volatile ("ld.shared.u16 %0, [%1];" : "=r" (v) : "r" (stage_addr + sl));
@@ -142,11 +165,11 @@ gather (uint32_t stage_addr, const uint32_t *slot, uint32_t *w)
     }
   } else if constexpr (ES == 4) {
 #pragma unroll
-    for (int e = 0; e < 4; e++)
+    for (int e = 0; e < VE; e++)
       asm volatile ("ld.shared.u32 %0, [%1];" : "=r" (w[e]) : "r" (stage_addr + slot[e]));
   } else if constexpr (ES == 8) {
 #pragma unroll
-    for (int e = 0; e < 2; e++)
+    for (int e = 0; e < VE; e++)
       asm volatile ("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r" (w[2 * e]), "=r" (w[2 * e + 1])
           : "r" (stage_addr + slot[e]));
   } else {
@@ -158,17 +181,18 @@ gather (uint32_t stage_addr, const uint32_t *slot, uint32_t *w)
 /* MICRO: the VE store vectors of a thread form VE x VE register micro-transposes: VE LDS.128
  * (whole shared-memory chunks; entry [j] of st_slot holds chunk j % VE of block j / VE) feed VE
  * output vectors, instead of VE scalar LDS per vector. */
-template <int ES, bool MICRO>
+template <int ES, int VB, bool MICRO>
 __global__ void __launch_bounds__ (PV_THREADS, ES < 4 ? 2 : NNSB_PV_MIN_BLOCKS)
 permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
     const unsigned char *__restrict__ table, const __grid_constant__ PermVecDev p)
 {
-  constexpr int VE = 16 / ES;
+  constexpr int VE = VB / ES;
+  constexpr uint32_t STAGE_BYTES = PV_NVT * VB;
   extern __shared__ __align__ (128) unsigned char ring[];       /* [PV_STAGES][PV_STAGE_BYTES] */
   const uint32_t ring_addr = (uint32_t) __cvta_generic_to_shared (ring);
 
   /* this thread's share of the box, from the host-built table */
-  uint32_t ld_off[PV_VPT], ld_slot[PV_VPT], st_off[PV_VPT], st_slot[PV_VPT][PvSlots<ES>::N];
+  uint32_t ld_off[PV_VPT], ld_slot[PV_VPT], st_off[PV_VPT], st_slot[PV_VPT][PvSlots<ES, VB>::N];
   {
     const uint32_t *t_ld_off = reinterpret_cast<const uint32_t *> (table + PV_T_LD_OFF);
     const uint32_t *t_ld_slot = reinterpret_cast<const uint32_t *> (table + PV_T_LD_SLOT);
@@ -184,7 +208,7 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
         /* packed pairs, straight from the table */
         const uint32_t *packed = reinterpret_cast<const uint32_t *> (t_st_slot + (size_t) i * VE);
 #pragma unroll
-        for (int q = 0; q < PvSlots<ES>::N; q++)
+        for (int q = 0; q < PvSlots<ES, VB>::N; q++)
           st_slot[j][q] = packed[q];
       } else if constexpr (VE == 4) {
         const uint2 s = *reinterpret_cast<const uint2 *> (t_st_slot + (size_t) i * 4);
@@ -259,16 +283,16 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
       if (ti.full && whole) {
 #pragma unroll
         for (int j = 0; j < PV_VPT; j++)
-          cp_async_16 (ld_slot[j] + stage_off, src + ld_off[j]);
+          cp_async_vec<VB> (ld_slot[j] + stage_off, src + ld_off[j]);
       } else if (ti.full) {
 #pragma unroll
         for (int j = 0; j < PV_VPT; j++)
-          cp_async_16_if ((present >> j) & 1u, ld_slot[j] + stage_off, src + ld_off[j]);
+          cp_async_vec_if<VB> ((present >> j) & 1u, ld_slot[j] + stage_off, src + ld_off[j]);
       } else {
         const uint64_t lim = ti.limits;
 #pragma unroll
         for (int j = 0; j < PV_VPT; j++)
-          cp_async_16_if (((present >> j) & 1u)
+          cp_async_vec_if<VB> (((present >> j) & 1u)
               && inside4 (t_ld_coord[threadIdx.x + j * PV_THREADS], lim),
               ld_slot[j] + stage_off, src + ld_off[j]);
       }
@@ -303,21 +327,21 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
     } else {
 #pragma unroll
       for (int j = 0; j < PV_VPT; j++)
-        gather<ES> (stage_addr, st_slot[j], w[j]);
+        gather<ES, VB> (stage_addr, st_slot[j], w[j]);
     }
     if (ti.full && whole) {
 #pragma unroll
       for (int j = 0; j < PV_VPT; j++)
-        st_stream<16> (dst + st_off[j], w[j]);
+        st_stream<VB> (dst + st_off[j], w[j]);
     } else if (ti.full) {
 #pragma unroll
       for (int j = 0; j < PV_VPT; j++)
-        st_stream_16_if ((present_st >> j) & 1u, dst + st_off[j], w[j]);
+        st_stream_vec_if<VB> ((present_st >> j) & 1u, dst + st_off[j], w[j]);
     } else {
       const uint64_t lim = ti.limits;
 #pragma unroll
       for (int j = 0; j < PV_VPT; j++)
-        st_stream_16_if (((present_st >> j) & 1u)
+        st_stream_vec_if<VB> (((present_st >> j) & 1u)
             && inside4 (t_st_coord[threadIdx.x + j * PV_THREADS], lim), dst + st_off[j], w[j]);
     }
   };
@@ -340,13 +364,13 @@ permute_vec_kernel (const unsigned char *__restrict__ in, unsigned char *__restr
    * every shared-memory offset is a compile-time constant */
 #pragma unroll
   for (int s = 0; s < PV_STAGES - 1; s++)
-    issue ((uint32_t) s, (uint32_t) s * PV_STAGE_BYTES);
+    issue ((uint32_t) s, (uint32_t) s * STAGE_BYTES);
   for (uint32_t k = 0; k < my_tiles; k += PV_STAGES) {
 #pragma unroll
     for (int s = 0; s < PV_STAGES; s++)
       if (k + s < my_tiles)
-        step (k + s, (uint32_t) s * PV_STAGE_BYTES,
-            (uint32_t) ((s + PV_STAGES - 1) % PV_STAGES) * PV_STAGE_BYTES);
+        step (k + s, (uint32_t) s * STAGE_BYTES,
+            (uint32_t) ((s + PV_STAGES - 1) % PV_STAGES) * STAGE_BYTES);
   }
 }
 
@@ -465,7 +489,7 @@ gather_cost (const uint32_t *lin, uint32_t n_vec, int ve, int es, const Swizzle 
 struct Builder
 {
   CDim dims[PV_DIMS];
-  int n, es;
+  int n, es, vb;                /* vb: vector bytes (16, 8 or 4) */
   uint64_t VE, TILE_MAX;
   int in_order[PV_DIMS], out_order[PV_DIMS];
 
@@ -480,8 +504,8 @@ struct Builder
     uint64_t span_in = 0, span_out = 0, tiles = 1;
     int n_boxed = 0, slot[PV_DIMS];
     for (int i = 0; i < n; i++) {
-      /* box origins 16-byte aligned on both sides */
-      if (T[i] < dims[i].size && ((T[i] * dims[i].in * es) % 16 || (T[i] * dims[i].out * es) % 16))
+      /* box origins vector aligned on both sides */
+      if (T[i] < dims[i].size && ((T[i] * dims[i].in * es) % vb || (T[i] * dims[i].out * es) % vb))
         return false;
       span_in += (T[i] - 1) * dims[i].in * es;
       span_out += (T[i] - 1) * dims[i].out * es;
@@ -542,7 +566,7 @@ struct Builder
           if (side == 1 && st_lin)
             st_lin[(size_t) v * VE + e] = (uint32_t) lin;
         }
-        if ((off0 * es) % 16)
+        if ((off0 * es) % vb)
           return false;
         if (tab) {
           if (side == 0) {
@@ -568,6 +592,11 @@ struct Builder
 
 }  // namespace
 
+static int perm_vec_build_vb (const PermDesc &d0, size_t frame_elems, int vb, PermVecPlan *pl,
+    void **host_table);
+
+/* widest vector that the shape allows: 16 bytes, else 8, else 4 (rows of 3240 bytes -- 1080 RGB
+ * pixels -- are 8-byte but not 16-byte multiples) */
 int
 perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **host_table)
 {
@@ -575,19 +604,37 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
   *host_table = nullptr;
   if (getenv ("NNSB_PERM_NO_VEC"))
     return -1;
-  if (((uint64_t) frame_elems * d0.es) % 16)
+  const char *env_vb = getenv ("NNSB_PERM_VEC_BYTES");
+  for (int vb = 16; vb >= 4; vb /= 2) {
+    if (env_vb && atoi (env_vb) != vb)
+      continue;
+    if (perm_vec_build_vb (d0, frame_elems, vb, pl, host_table) == 0)
+      return 0;
+  }
+  memset (pl, 0, sizeof (*pl));
+  return -1;
+}
+
+static int
+perm_vec_build_vb (const PermDesc &d0, size_t frame_elems, int vb, PermVecPlan *pl,
+    void **host_table)
+{
+  memset (pl, 0, sizeof (*pl));
+  *host_table = nullptr;
+  if (((uint64_t) frame_elems * d0.es) % vb)
     return -1;
-  /* launches require 16-byte aligned bases, so an innermost block may fold up to 16 bytes */
+  /* launches require vector-aligned bases, so an innermost block may fold up to one vector */
   Builder B;
   B.es = d0.es;
-  B.n = canonicalise_perm (d0.size, d0.in_stride, d0.rank, frame_elems, 0, 16, 16, B.dims, &B.es);
+  B.vb = vb;
+  B.n = canonicalise_perm (d0.size, d0.in_stride, d0.rank, frame_elems, 0, vb, vb, B.dims, &B.es);
   const int n = B.n, es = B.es;
   if (n < 2)
     return -1;                  /* identity: the flat copy */
-  if (es != 1 && es != 2 && es != 4 && es != 8 && es != 16)
+  if ((es != 1 && es != 2 && es != 4 && es != 8 && es != 16) || es > vb)
     return -1;
-  const uint64_t VE = B.VE = 16 / es;
-  const uint64_t TILE_MAX = B.TILE_MAX = PV_STAGE_BYTES / es;
+  const uint64_t VE = B.VE = vb / es;
+  const uint64_t TILE_MAX = B.TILE_MAX = (uint64_t) PV_NVT * vb / es;
   const CDim *dims = B.dims;
   for (int i = 0; i < n; i++)
     if (dims[i].size > 0xffffffffull)
@@ -714,7 +761,8 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
   uint32_t lstride_o = 0;
   std::vector<uint32_t> blocks;         /* representative store vector (element 0 at lin % VE == 0) */
   std::vector<int32_t> vec_of_lin;
-  if ((es == 4 || es == 8) && out_order[0] != in_order[0] && !getenv ("NNSB_PERM_NO_MICRO")) {
+  if (vb == 16 && (es == 4 || es == 8) && out_order[0] != in_order[0]
+      && !getenv ("NNSB_PERM_NO_MICRO")) {
     uint32_t ls = 1;
     for (int k = 0; k < n && in_order[k] != out_order[0]; k++)
       ls *= (uint32_t) T[in_order[k]];
@@ -790,7 +838,7 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
     }
   }
   for (uint32_t v = 0; v < n_vec; v++)
-    t_ld_slot[v] = best_sw (v) * 16;
+    t_ld_slot[v] = best_sw (v) * vb;
   if (micro) {
     /* entry t + j * 256 of the store-side arrays = vector j % VE of block t + (j / VE) * 256 */
     uint64_t *t_st_coord = (uint64_t *) (tab + PV_T_ST_COORD);
@@ -807,14 +855,14 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
         const uint32_t u = (uint32_t) vec_of_lin[lin0 + jj];
         t_st_off[entry] = off[u];
         t_st_coord[entry] = coord[u];
-        t_st_slot[entry * VE] = (uint16_t) (best_sw ((lin0 + jj * lstride_o) / (uint32_t) VE) * 16);
+        t_st_slot[entry * VE] = (uint16_t) (best_sw ((lin0 + jj * lstride_o) / (uint32_t) VE) * vb);
       }
     }
   } else {
     for (uint32_t v = 0; v < n_vec; v++)
       for (uint64_t e = 0; e < VE; e++) {
         const uint32_t li = st_lin[(size_t) v * VE + e];
-        t_st_slot[(size_t) v * VE + e] = (uint16_t) (best_sw (li / (uint32_t) VE) * 16 + (li % VE) * es);
+        t_st_slot[(size_t) v * VE + e] = (uint16_t) (best_sw (li / (uint32_t) VE) * vb + (li % VE) * es);
       }
   }
   free (st_lin);
@@ -836,22 +884,23 @@ perm_vec_build (const PermDesc &d0, size_t frame_elems, PermVecPlan *pl, void **
   pl->swizzle_shift = best_sw.s1;
   pl->swizzle_shift2 = best_sw.s2;
   pl->micro = micro ? 1 : 0;
+  pl->vb = vb;
   *host_table = tab;
   return 0;
 }
 
-template <int ES, bool MICRO> static int
+template <int ES, int VB, bool MICRO> static int
 launch_permute_vec_t (const PermVecDev &p, const void *d_table, const void *in, void *out,
     const LaunchCfg &cfg, cudaStream_t stream)
 {
-  const size_t smem = (size_t) PV_STAGES * PV_STAGE_BYTES;
+  const size_t smem = (size_t) PV_STAGES * PV_NVT * VB;
   static int resident = 0;
   if (resident == 0) {
-    cudaError_t e = cudaFuncSetAttribute (permute_vec_kernel<ES, MICRO>,
+    cudaError_t e = cudaFuncSetAttribute (permute_vec_kernel<ES, VB, MICRO>,
         cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
     if (e != cudaSuccess)
       return (int) e;
-    resident = resident_blocks_per_sm (permute_vec_kernel<ES, MICRO>, PV_THREADS, smem);
+    resident = resident_blocks_per_sm (permute_vec_kernel<ES, VB, MICRO>, PV_THREADS, smem);
   }
   uint64_t grid = p.n_tiles;
   /* two CTAs per SM, although four fit: fewer tiles in flight keep the DRAM pages of a tile
@@ -861,7 +910,7 @@ launch_permute_vec_t (const PermVecDev &p, const void *d_table, const void *in, 
   const uint64_t cap = (uint64_t) cfg.sm_count * per_sm;
   if (grid > cap)
     grid = cap;
-  permute_vec_kernel<ES, MICRO><<<(unsigned int) grid, PV_THREADS, smem, stream>>> (
+  permute_vec_kernel<ES, VB, MICRO><<<(unsigned int) grid, PV_THREADS, smem, stream>>> (
       (const unsigned char *) in, (unsigned char *) out, (const unsigned char *) d_table, p);
   return (int) cudaGetLastError ();
 }
@@ -872,7 +921,7 @@ launch_permute_vec (const PermVecPlan &pl, const void *d_table, const void *in, 
 {
   if (!pl.valid || !d_table || batch == 0)
     return -1;
-  if ((uintptr_t) in % 16 || (uintptr_t) out % 16)
+  if ((uintptr_t) in % pl.vb || (uintptr_t) out % pl.vb)
     return -1;
   const uint64_t tiles = pl.tiles_per_frame * batch;
   if (tiles >= (1ull << 31))
@@ -901,16 +950,34 @@ launch_permute_vec (const PermVecPlan &pl, const void *d_table, const void *in, 
   p.limits_init = pl.limits_init;
   p.n_vec = pl.n_vec;
   p.n_tiles = (uint32_t) tiles;
-  switch (pl.es) {
-    case 1: return launch_permute_vec_t<1, false> (p, d_table, in, out, cfg, stream);
-    case 2: return launch_permute_vec_t<2, false> (p, d_table, in, out, cfg, stream);
-    case 4: return pl.micro ? launch_permute_vec_t<4, true> (p, d_table, in, out, cfg, stream)
-          : launch_permute_vec_t<4, false> (p, d_table, in, out, cfg, stream);
-    case 8: return pl.micro ? launch_permute_vec_t<8, true> (p, d_table, in, out, cfg, stream)
-          : launch_permute_vec_t<8, false> (p, d_table, in, out, cfg, stream);
-    case 16: return launch_permute_vec_t<16, false> (p, d_table, in, out, cfg, stream);
-    default: return -1;
+#define NNSB_PV(ES, VB, M) launch_permute_vec_t<ES, VB, M> (p, d_table, in, out, cfg, stream)
+  if (pl.vb == 16) {
+    switch (pl.es) {
+      case 1: return NNSB_PV (1, 16, false);
+      case 2: return NNSB_PV (2, 16, false);
+      case 4: return pl.micro ? NNSB_PV (4, 16, true) : NNSB_PV (4, 16, false);
+      case 8: return pl.micro ? NNSB_PV (8, 16, true) : NNSB_PV (8, 16, false);
+      case 16: return NNSB_PV (16, 16, false);
+      default: return -1;
+    }
+  } else if (pl.vb == 8) {
+    switch (pl.es) {
+      case 1: return NNSB_PV (1, 8, false);
+      case 2: return NNSB_PV (2, 8, false);
+      case 4: return NNSB_PV (4, 8, false);
+      case 8: return NNSB_PV (8, 8, false);
+      default: return -1;
+    }
+  } else if (pl.vb == 4) {
+    switch (pl.es) {
+      case 1: return NNSB_PV (1, 4, false);
+      case 2: return NNSB_PV (2, 4, false);
+      case 4: return NNSB_PV (4, 4, false);
+      default: return -1;
+    }
   }
+  return -1;
+#undef NNSB_PV
 }
 
 }  // namespace nnsb

@@ -79,7 +79,8 @@ struct PermDesc
 struct PermVecPlan
 {
   int valid;
-  int es;                                       /* element bytes after folding (4, 8, 16) */
+  int es;                                       /* element bytes after folding (1 .. 16) */
+  int vb;                                       /* vector bytes: 16, 8 or 4 */
   uint64_t frame_bytes;
   int n;                                        /* canonical dims, output order, no batch */
   uint32_t size[NNSB_PERM_MAX_RANK];

@@ -59,7 +59,7 @@ main (int argc, char **argv)
   const uint64_t *t_ld_coord = (const uint64_t *) (tab + PV_T_LD_COORD);
   const uint64_t *t_st_coord = (const uint64_t *) (tab + PV_T_ST_COORD);
   const uint16_t *t_st_slot = (const uint16_t *) (tab + PV_T_ST_SLOT);
-  const int VE = 16 / pl.es;
+  const int VB = pl.vb, VE = VB / pl.es;
 
   /* input: byte b of the tensor = a hash of its position; reference output by definition */
   const size_t frame_bytes = (size_t) frame_elems * es, total = frame_bytes * batch;
@@ -99,7 +99,7 @@ main (int argc, char **argv)
     n++;
   }
   const uint64_t n_tiles = pl.tiles_per_frame * batch;
-  std::vector<unsigned char> stage (PV_STAGE_BYTES);
+  std::vector<unsigned char> stage ((size_t) PV_NVT * VB);
   auto inside = [] (uint64_t c, uint64_t lim) {
     for (int b = 0; b < PV_BOXED; b++)
       if (((c >> (16 * b)) & 0xffff) >= ((lim >> (16 * b)) & 0xffff))
@@ -123,15 +123,15 @@ main (int argc, char **argv)
     std::fill (stage.begin (), stage.end (), 0xCD);
     for (uint32_t v = 0; v < (uint32_t) PV_NVT; v++)
       if (t_ld_off[v] != PV_INVALID && inside (t_ld_coord[v], lim)) {
-        if (ib + t_ld_off[v] + 16 > total || t_ld_slot[v] + 16 > (uint32_t) PV_STAGE_BYTES) {
+        if (ib + t_ld_off[v] + VB > total || t_ld_slot[v] + VB > (uint32_t) PV_NVT * VB) {
           printf ("MISMATCH load out of range (tile %llu vector %u)\n", (unsigned long long) t, v);
           return 1;
         }
-        memcpy (&stage[t_ld_slot[v]], &in[ib + t_ld_off[v]], 16);
+        memcpy (&stage[t_ld_slot[v]], &in[ib + t_ld_off[v]], VB);
       }
     for (uint32_t v = 0; v < (uint32_t) PV_NVT; v++)
       if (t_st_off[v] != PV_INVALID && inside (t_st_coord[v], lim)) {
-        if (ob + t_st_off[v] + 16 > total) {
+        if (ob + t_st_off[v] + VB > total) {
           printf ("MISMATCH store out of range (tile %llu vector %u)\n", (unsigned long long) t, v);
           return 1;
         }
@@ -149,7 +149,7 @@ main (int argc, char **argv)
             memcpy (&got[ob + t_st_off[v] + (size_t) e * pl.es], &stage[t_st_slot[(size_t) v * VE + e]],
                 pl.es);
         }
-        writes += 16;
+        writes += VB;
       }
   }
   if (writes != total) {
@@ -165,7 +165,7 @@ main (int argc, char **argv)
   int o = 0;
   for (int i = 0; i < pl.n; i++)
     o += snprintf (box + o, sizeof (box) - o, "%s%u", i ? "x" : "", pl.tile[i]);
-  printf ("ok es=%d box=%s n_vec=%u swizzle=%d/%d micro=%d wavefronts=%llu tiles=%llu\n", pl.es, box,
+  printf ("ok vb=%d es=%d box=%s n_vec=%u swizzle=%d/%d micro=%d wavefronts=%llu tiles=%llu\n", pl.vb, pl.es, box,
       pl.n_vec, pl.swizzle_shift, pl.swizzle_shift2, pl.micro, (unsigned long long) pl.gather_wavefronts,
       (unsigned long long) n_tiles);
   free (table);

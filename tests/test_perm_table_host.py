@@ -52,6 +52,9 @@ CASES = [
     (1, 2, (3, 160, 80, 1)),
     (2, 1, (3, 64, 48, 1)),         # 8 two-byte elements per vector
     (2, 2, (5, 32, 24, 1)),
+    (1, 1, (3, 1080, 64, 1)),       # 3240-byte rows: 8-byte vectors
+    (4, 2, (3, 227, 31, 1)),        # 4-byte vectors
+    (2, 1, (3, 226, 34, 1)),        # 2-byte elements in 4-byte vectors
     (4, 1, (3, 3840, 16, 1)),       # long rows
     (4, 1, (1, 2160, 512, 1)),      # plain 2-D transposes
 ]
@@ -72,12 +75,16 @@ def test_expected_boxes(checker):
     assert rc == 0 and "box=64x64" in out and "n_vec=1024" in out, out
     waves = int(out.split("wavefronts=")[1].split()[0])
     assert waves <= 256, out
-    # odd sizes cannot be vectorised: the scalar kernel takes them
-    rc, out = run(checker, 4, 4, (5, 7, 9, 1), (2, 1, 0, 3))
-    assert rc == 0 and out == "ineligible", out
-    # rows that are not 16-byte multiples cannot be vectorised (1080 RGB bytes = 3240)
+    # rows that are 8- but not 16-byte multiples (1080 RGB bytes = 3240) take 8-byte vectors,
+    # float rows that are only 4-byte multiples take 4-byte ones
     rc, out = run(checker, 1, 1, (3, 1080, 1920, 1), (0, 2, 1, 3))
-    assert rc == 0 and out == "ineligible", out
-    # one-byte elements: 16 per vector
+    assert rc == 0 and out.startswith("ok vb=8 es=1"), out
+    rc, out = run(checker, 4, 4, (5, 7, 9, 1), (2, 1, 0, 3))
+    assert rc == 0 and out.startswith("ok vb=4 es=4"), out
     rc, out = run(checker, 1, 1, (3, 1920, 1088, 1), (0, 2, 1, 3))
-    assert rc == 0 and "es=1" in out and out.startswith("ok"), out
+    assert rc == 0 and out.startswith("ok vb=16 es=1"), out
+    # odd byte counts cannot be vectorised at all: the scalar kernel takes them
+    rc, out = run(checker, 2, 1, (3, 225, 113, 1), (0, 2, 1, 3))
+    assert rc == 0 and out == "ineligible", out
+    rc, out = run(checker, 1, 3, (3, 50, 100, 1), (2, 0, 1, 3))
+    assert rc == 0 and out == "ineligible", out
