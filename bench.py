@@ -36,6 +36,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 W, H, C, B = 1920, 1080, 3, 32
+C_ = C                              # (`C` is rebound to ctypes inside some functions)
 DIM = [C, W, H, 1]
 FRAME_ELEMS = C * W * H
 OPTION = ("typecast:float32,per-channel:true@0,add:-123.675@0,add:-116.28@1,add:-103.53@2,"
@@ -44,9 +45,32 @@ ORACLE_OPS = [("typecast", "float32"), ("add", -123.675, 0), ("add", -116.28, 1)
               ("add", -103.53, 2), ("div", 58.395, 0), ("div", 57.12, 1), ("div", 57.375, 2)]
 WORKLOAD = "3:1920:1080:32 uint8 -> float32, arithmetic " + OPTION
 ALGO_BYTES_PER_ELEM = 5           # sizeof(u8) + sizeof(f32), SURVEY.md 8d
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 938.4e6   # measured once with ncu, see profiles/
+# ncu --set full capture of the headline kernel (one launch of this very workload), committed
+NCU_RAW_CSV = os.path.join(ROOT, "profiles", "r1_lut_chain_u8_f32_raw.csv")
 METRIC = "tensor_transform_1080p_frames_per_sec"
 UNIT = "frames/s"
+# the same dict in both arms (`same_config`): what the step is and how L2 is kept out of it
+CONFIG = {"workload": WORKLOAD, "batch_frames": B,
+          "l2": "inputs larger than L2 (199 MB in + 796 MB out per step vs 126 MB L2)",
+          "sharding": "one independent 32-frame stream per GPU, no collective"}
+
+
+def ncu_traffic_bytes(path=NCU_RAW_CSV, launch="0"):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch, read from the committed ncu
+    CSV (profiles/summarize.py format: launch,metric,unit,value).  None if the file is absent."""
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total, seen = 0.0, 0
+    try:
+        with open(path) as fh:
+            for line in fh:
+                parts = line.rstrip("\n").split(",")
+                if len(parts) == 4 and parts[0] == launch and parts[1] in (
+                        "dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    total += float(parts[3]) * scale[parts[2]]
+                    seen += 1
+    except Exception:
+        return None
+    return total if seen == 2 else None
 
 
 def measured_peak():
@@ -151,16 +175,19 @@ def cpu_run_frames(checker, frames, n_threads):
     return time.perf_counter() - t0
 
 
-def cpu_baseline(sample_frames=None):
+def cpu_baseline(sample_frames=None, budget_s=15.0):
     checker, kind = cpu_checker()
     cores = os.cpu_count() or 1
     rng = np.random.default_rng(2)
     frame = rng.integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
     t1 = cpu_run_frames(checker, [frame], 1)            # warm-up + per-frame cost
     if sample_frames is None:
-        # ~15 s of CPU work in total, at least one frame per core
-        sample_frames = int(max(cores, min(4 * cores, 15.0 / max(t1, 1e-3))))
-    frames = [frame] * sample_frames
+        # ~budget_s of CPU work in total, at least one frame per core
+        sample_frames = int(max(cores, min(4 * cores, budget_s / max(t1, 1e-3))))
+    distinct = min(sample_frames, B)
+    pool = rng.integers(0, 256, FRAME_ELEMS * distinct, dtype=np.uint8)
+    frames = [pool[(i % distinct) * FRAME_ELEMS:(i % distinct + 1) * FRAME_ELEMS]
+              for i in range(sample_frames)]
     dt = cpu_run_frames(checker, frames, cores)
     return {"value": sample_frames / dt, "unit": UNIT, "cores": cores, "kind": kind,
             "sample": "%d 1080p frames of the bench workload, one frame per task on %d threads "
@@ -174,8 +201,9 @@ def run_reference(args):
     checker, kind = cpu_checker()
     cores = os.cpu_count() or 1
     rng = np.random.default_rng(2)
-    frame = rng.integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
-    frames = [frame] * B
+    # 32 different frames (199 MB): the batch does not sit in the last-level cache
+    batch = rng.integers(0, 256, FRAME_ELEMS * B, dtype=np.uint8)
+    frames = [batch[i * FRAME_ELEMS:(i + 1) * FRAME_ELEMS] for i in range(B)]
     for _ in range(args.warmup):
         cpu_run_frames(checker, frames[:cores], cores)
     t = 0.0
@@ -187,10 +215,10 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "batch_frames": B},
+        "config": CONFIG,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
-                         "sample": "each step = the full 32-frame batch, one frame per task on "
-                                   "%d host threads" % cores},
+                         "sample": "each step = the full batch of 32 distinct frames, one frame "
+                                   "per task on %d host threads" % cores},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -227,14 +255,26 @@ def extra_kernels(dev, peak, with_cpu=True):
         frame_n = int(np.prod(dim))
         n = frame_n * batch
         host = make(n)
-        d_in = dev.upload(host)
-        d_out = dev.alloc(plan.out_size * batch)
-        ms = time_launches(dev, lambda: plan.launch(d_in, d_out, batch), 10, 3) / 10
+        # launches rotate over enough buffer pairs that their footprint is >= 3 x L2 (126 MB): a
+        # single 4K frame (99.5 MB in, 99.5 MB out) would otherwise be served partly from L2
+        pair = plan.in_size * batch + plan.out_size * batch
+        rot = int(max(1, min(8, -(-3 * 126_000_000 // pair))))
+        d_ins = [dev.upload(host) for _ in range(rot)]
+        d_outs = [dev.alloc(plan.out_size * batch) for _ in range(rot)]
+        it = [0]
+
+        def launch():
+            k = it[0] % rot
+            it[0] += 1
+            plan.launch(d_ins[k], d_outs[k], batch)
+
+        steps = 20
+        ms = time_launches(dev, launch, steps, 3) / steps
         gbs = n * bytes_per_elem / (ms * 1e-3) / 1e9
         out[name] = {"ms": ms, "GB/s": gbs, "frac_of_measured_peak": gbs / peak,
-                     "launches": plan.last_launch_count}
-        dev.free(d_in)
-        dev.free(d_out)
+                     "launches": plan.last_launch_count, "rotating_buffers": rot}
+        for p in d_ins + d_outs:
+            dev.free(p)
         plan.close()
         if cpu is not None and checker is not None:
             # bound the CPU sample to one 1080p-sized frame (the reference takes 0.06-0.4 s for it)
@@ -270,6 +310,14 @@ def extra_kernels(dev, peak, with_cpu=True):
             [3, 3840, 2160, 1], 8, 8, f32)
     run("dimchg_0_2_4k_f32", "dimchg", "0:2", "float32", [3, 3840, 2160, 1], 1, 8, f32,
         lambda c, x, d: c.dimchg(x, d, 0, 2))
+    # real video rows whose byte counts are not multiples of 16 (narrow-vector / odd-row paths)
+    u16 = lambda n: rng.integers(0, 65536, n, dtype=np.uint16)
+    run("transpose_0_2_1_1080p_rgb_u8_b32", "transpose", "0:2:1:3", "uint8", DIM, 32, 2, u8,
+        lambda c, x, d: c.transpose(x, d, (0, 2, 1, 3)))
+    run("transpose_2_1_0_227x227x3_f32_b64", "transpose", "2:1:0:3", "float32", [3, 227, 227, 1], 64, 8, f32)
+    run("transpose_1_2_0_225x113x3_u16_b256", "transpose", "1:2:0:3", "uint16", [3, 225, 113, 1], 256, 4, u16)
+    run("transpose_0_2_1_225x113x3_u16_b256", "transpose", "0:2:1:3", "uint16", [3, 225, 113, 1], 256, 4, u16)
+    run("transpose_1_0_2_1080p_gray_u8_b32", "transpose", "1:0:2:3", "uint8", [1, 1920, 1080, 1], 32, 2, u8)
     run("clamp_f32_1080p_b64", "clamp", "-33.3:77.7", "float32", DIM, 64, 8, f32,
         lambda c, x, d: c.clamp(x, -33.3, 77.7))
     run("stand_default_f32_1080p_b64_per_frame", "stand", "default", "float32", DIM, 64, 8, f32,
@@ -410,83 +458,295 @@ def aggregator_extras(dev, peak, with_cpu):
     return out
 
 
-def multi_stream_chain(device_id, n_streams=8, frames_per_stream=40):
-    """BASELINE configs[4] on ONE GPU: `n_streams` concurrent 1080p pipelines, each
-    tensor_converter -> tensor_transform typecast:float32 -> arithmetic add:-127.5,div:127.5 ->
-    transpose 1:2:0:3, one host thread and one set of elements (own CUDA streams) per pipeline.
-    Returns frames/s device-resident (frames pre-staged in HBM) and with the H2D of every
-    frame inside the timed region (the float CHW result stays on the device for the consumer)."""
-    from nnstreamer_b200 import Device, TensorConverter, TensorTransform, device_memory
+def python_stream_chain(device_id, n_streams=8, frames_per_stream=100):
+    """BASELINE configs[4] on ONE GPU driven from Python threads through the element mirrors
+    (nnstreamer_b200.TensorConverter / TensorTransform): what the stream-ordered memories buy a
+    caller that is NOT native code.  Device-resident frames, one thread and one set of elements
+    per pipeline; each thread waits once, for its last output."""
+    from nnstreamer_b200 import DeviceMemory, TensorConverter, TensorTransform
+    import ctypes as C
     caps = ("video/x-raw, format=(string)RGB, width=(int)%d, height=(int)%d, framerate=(fraction)30/1" % (W, H))
-    out = {}
-    for mode in ("device_resident", "h2d_per_frame"):
-        dev = Device(device_id)
-        pipes = []
-        for sidx in range(n_streams):
-            conv = TensorConverter(device_id=device_id)
-            c1 = conv.set_caps(caps)
-            t1 = TensorTransform(device_id=device_id, mode="typecast", option="float32")
-            c2 = t1.negotiate(c1)
-            t2 = TensorTransform(device_id=device_id, mode="arithmetic", option="add:-127.5,div:127.5")
-            c3 = t2.negotiate(c2)
-            t3 = TensorTransform(device_id=device_id, mode="transpose", option="1:2:0:3")
-            t3.negotiate(c3)
-            rng = np.random.default_rng(sidx)
-            if mode == "device_resident":
-                frame = device_memory(dev.upload(rng.integers(0, 256, FRAME_ELEMS, dtype=np.uint8)), FRAME_ELEMS)
-            else:
-                arr, _ptr = dev.pinned(FRAME_ELEMS, np.uint8)
-                arr[:] = rng.integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
-                frame = arr
-            pipes.append((conv, t1, t2, t3, frame))
+    pipes = []
+    for sidx in range(n_streams):
+        conv = TensorConverter(device_id=device_id)
+        c1 = conv.set_caps(caps)
+        t1 = TensorTransform(device_id=device_id, mode="typecast", option="float32")
+        t2 = TensorTransform(device_id=device_id, mode="arithmetic", option="add:-127.5,div:127.5")
+        t3 = TensorTransform(device_id=device_id, mode="transpose", option="1:2:0:3")
+        t3.negotiate(t2.negotiate(t1.negotiate(c1)))
+        x = np.random.default_rng(sidx).integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
+        m = t1.alloc(FRAME_ELEMS, on_device=True)
+        assert t1._lib.nnsb_transform_upload(t1.handle, C.byref(m), x.ctypes.data_as(C.c_void_p)) == 0
+        pipes.append((conv, t1, t2, t3, DeviceMemory(m)))
 
-        def run(pipe, n):
-            conv, t1, t2, t3, frame = pipe
-            for _ in range(n):
-                flow, m0 = conv.chain(frame)
-                flow, (m1,) = t1.transform([m0])
-                flow, (m2,) = t2.transform([m1])
-                flow, (m3,) = t3.transform([m2])
-                for m in (m0, m1, m2, m3):
-                    m.release()
+    def run(pipe, n):
+        conv, t1, t2, t3, frame = pipe
+        last = None
+        for _ in range(n):
+            flow, m0 = conv.chain(frame)
+            flow, (m1,) = t1.transform([m0])
+            flow, (m2,) = t2.transform([m1])
+            flow, (m3,) = t3.transform([m2])
+            for m in (m0, m1, m2):
+                m.release()
+            if last is not None:
+                last.release()
+            last = m3
+        last.sync()
+        last.release()
 
-        for p in pipes:
-            run(p, 3)
-        ths = [threading.Thread(target=run, args=(p, frames_per_stream)) for p in pipes]
-        t0 = time.perf_counter()
-        for t in ths:
-            t.start()
-        for t in ths:
-            t.join()
-        dt = time.perf_counter() - t0
-        fps = n_streams * frames_per_stream / dt
-        # algorithmic bytes per element along the chain: converter 0 (+1 when uploaded),
-        # typecast 5, arithmetic 8, transpose 8 (SURVEY.md 8d)
-        out[mode] = {"frames/s": fps, "GB/s": fps * FRAME_ELEMS * 21 / 1e9,
-                     "streams": n_streams, "frames_per_stream": frames_per_stream}
-        for conv, t1, t2, t3, frame in pipes:
-            for e in (conv, t1, t2, t3):
-                e.close()
-        dev.close()
-    return out
+    for p in pipes:
+        run(p, 3)
+    ths = [threading.Thread(target=run, args=(p, frames_per_stream)) for p in pipes]
+    t0 = time.perf_counter()
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    dt = time.perf_counter() - t0
+    fps = n_streams * frames_per_stream / dt
+    for conv, t1, t2, t3, frame in pipes:
+        frame.release()
+        for e in (conv, t1, t2, t3):
+            e.close()
+    return {"frames/s": fps, "GB/s": fps * FRAME_ELEMS * 21 / 1e9, "streams": n_streams,
+            "frames_per_stream": frames_per_stream,
+            "driver": "Python threads through the element mirrors, device-resident frames"}
 
 
-def native_stream_chain(device_id, n_streams=8, frames_per_stream=300):
-    """The same chain driven by tools/stream_bench (native threads through the C-ABI): what the
-    element mirrors cost without the Python interpreter in the per-frame loop."""
+STREAMS_PER_GPU = 8
+TOTAL_STREAMS = 64                  # BASELINE configs[4]
+
+
+def sharded_stream_chain(local_rank, rank, world, dist, reduce_device, frames_per_stream, check):
+    """BASELINE configs[4]: 64 concurrent 1080p streams through converter -> typecast -> arithmetic
+    -> transpose, 8 per GPU (nnstreamer_b200.sharding: stream s -> GPU s mod G), so N GPUs carry
+    8 N of them.  Every rank runs tools/stream_bench (native threads through the C-ABI, one per
+    stream) on ITS GPU; all ranks start their timed region at the same wall-clock instant, the
+    frames are summed over the ranks and divided by the slowest rank's time.  Three modes
+    (device-resident / H2D per frame / H2D + D2H per frame) x two widths (1920, and 1918 whose
+    padded rows the converter strips).  `check` (rank 0, inside the cpu_baseline leg) compares the
+    last output of stream 0 with the CPU reference chain."""
+    from nnstreamer_b200 import sharding
     exe = os.path.join(ROOT, "tools", "stream_bench")
     if not os.path.isfile(exe):
         return {"unavailable": "tools/stream_bench not built (python -c 'import __graft_entry__ as g; g.build()')"}
+    n_local = len(sharding.streams_of_rank(min(TOTAL_STREAMS, STREAMS_PER_GPU * world), world, rank))
     out = {}
-    for mode, key in (("resident", "device_resident"), ("h2d", "h2d_per_frame")):
-        try:
-            r = subprocess.run([exe, str(device_id), str(n_streams), str(frames_per_stream), mode],
-                               capture_output=True, text=True, timeout=300)
-            out[key] = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else \
-                {"error": r.stderr.strip()[-300:]}
-        except Exception as exc:                    # noqa: BLE001
-            out[key] = {"error": str(exc)}
+    import tempfile
+    tmp = tempfile.mkdtemp(prefix="nnsb_chain_")
+    for width in (1920, 1918):
+        entry = {"streams": n_local * world, "streams_per_gpu": n_local, "gpus": world,
+                 "frames_per_stream": frames_per_stream,
+                 "chain": "tensor_converter -> typecast:float32 -> arithmetic add:-127.5,div:127.5 "
+                          "-> transpose 1:2:0:3", "driver": "tools/stream_bench, one process per GPU, "
+                          "one native thread per stream"}
+        for mode in ("resident", "h2d", "h2d_d2h"):
+            dump = os.path.join(tmp, "w%d" % width) if (mode == "resident" and rank == 0
+                                                        and check is not None) else "-"
+            # same start instant on every rank: late enough for the slowest process to finish
+            # creating its CUDA context and warming up
+            start_at = sharding.max_over_ranks(time.time(), dist, reduce_device) + (3.0 if world == 1 else 8.0)
+            res = None
+            try:
+                r = subprocess.run([exe, str(local_rank), str(n_local), str(frames_per_stream), mode,
+                                    str(width), dump, "%.6f" % start_at],
+                                   capture_output=True, text=True, timeout=600)
+                if r.returncode == 0:
+                    res = json.loads(r.stdout.strip().splitlines()[-1])
+                else:
+                    entry[mode] = {"error": r.stderr.strip()[-300:]}
+            except Exception as exc:                # noqa: BLE001
+                entry[mode] = {"error": str(exc)}
+            ok = sharding.sum_over_ranks(1.0 if res else 0.0, dist, reduce_device)
+            if ok < world:
+                entry.setdefault(mode, {"error": "a rank failed"})
+                continue
+            frames = sharding.sum_over_ranks(n_local * frames_per_stream, dist, reduce_device)
+            slowest = sharding.max_over_ranks(res["seconds"], dist, reduce_device)
+            late = sharding.max_over_ranks(res["started_late_s"], dist, reduce_device)
+            h = int(res["stream0_last_output_fnv1a"], 16)
+            hashes = sharding.gather_over_ranks([float(h >> 32), float(h & 0xffffffff)], dist, reduce_device)
+            fps = frames / slowest
+            elems = 3 * width * H
+            bpe = 21 + (2 if (width % 4 and mode == "resident") else 0)
+            entry[mode] = {"frames/s": fps, "GB/s": fps * elems * bpe / 1e9,
+                           "slowest_rank_seconds": slowest, "this_rank_frames/s": res["frames/s"],
+                           "h2d_bytes_per_frame": res["h2d_bytes_per_frame"],
+                           "d2h_bytes_per_frame": res["d2h_bytes_per_frame"],
+                           "started_late_s_max": late,
+                           "all_ranks_same_output_as_rank0": all(x == hashes[0] for x in hashes)}
+            if dump != "-":
+                entry["parity_vs_oracle_stream0_last_frame"] = check(dump, width)
+                for ext in (".in", ".out"):
+                    try:
+                        os.remove(dump + ext)
+                    except OSError:
+                        pass
+        out["chain_64_streams_%dx1080" % width] = entry
+    try:
+        os.rmdir(tmp)
+    except OSError:
+        pass
     return out
+
+
+def chain_parity_check(dump, width):
+    """cpu_baseline leg only: last output of stream 0 vs the CPU reference chain on the same frame."""
+    try:
+        port = cpu_checker_port()
+        frame = np.fromfile(dump + ".in", dtype=np.uint8)
+        got = np.fromfile(dump + ".out", dtype=np.float32)
+        dense = port.stride_strip(frame, 3, width, H) if width % 4 else frame
+        f = port.arithmetic(dense, [3, width, H, 1], [("typecast", "float32"), ("add", -127.5), ("div", 127.5)])
+        want = port.transpose(f, [3, width, H, 1], (1, 2, 0, 3))
+        return bool(got.tobytes() == want.tobytes())
+    except Exception as exc:                        # noqa: BLE001
+        return "check failed: %s" % (str(exc)[:80],)
+
+
+def host_link_ceiling(dev, h_in_ptr, h_out_ptr, d_in, d_out, n, steps, barrier):
+    """What the host link of THIS rank delivers while every other rank does the same: bare
+    cudaMemcpyAsync of the step's upload (n bytes) on one stream and of its download (4 n bytes)
+    on another, from / to the same pinned buffers, no kernels.  ms per step."""
+    import ctypes as C
+    from nnstreamer_b200 import _lib as L
+    lib = L.lib()
+    s2 = C.c_void_p()
+    L.check(lib.nnsb_stream_create(dev.ctx, C.byref(s2)))
+
+    def step():
+        L.check(lib.nnsb_h2d_async(dev.stream, C.c_void_p(d_in), C.c_void_p(h_in_ptr), n))
+        L.check(lib.nnsb_d2h_async(s2, C.c_void_p(h_out_ptr), C.c_void_p(d_out), 4 * n))
+        L.check(lib.nnsb_stream_sync(dev.stream))
+        L.check(lib.nnsb_stream_sync(s2))
+
+    step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    barrier()
+    lib.nnsb_stream_destroy(s2)
+    return ms
+
+
+def consumer_on_device_e2e(local_rank, h_batch, steps, barrier):
+    """The same 32-frame batch end to end when the consumer is CUDA-aware:
+    tensor_converter frames-per-tensor=32 takes the 32 HOST frames (H2D inside the timed region),
+    tensor_transform runs the bench chain on the device, and a tensor_filter whose sub-plugin is a
+    CUDA kernel (this library's clamp, enqueued on the stream the filter hands it) consumes the
+    float32 tensor in HBM.  Nothing is downloaded.  Returns (ms per step, bytes up, bytes down)."""
+    import ctypes as C
+    from nnstreamer_b200 import Device, TensorConverter, TensorFilter, TensorTransform
+    from nnstreamer_b200 import _lib as L
+    lib = L.lib()
+    conv = TensorConverter(device_id=local_rank, frames_per_tensor=B)
+    c1 = conv.set_caps("video/x-raw, format=(string)RGB, width=(int)%d, height=(int)%d, "
+                       "framerate=(fraction)30/1" % (W, H))
+    t = TensorTransform(device_id=local_rank, mode="arithmetic", option=OPTION)
+    t.negotiate(c1)
+    aux = Device(local_rank)
+    out_dim = [C_, W, H, B]
+    plan = aux.plan("clamp", "-1.5:1.5", "float32", out_dim)
+    wrapped = {}
+
+    def invoke(inputs, outputs, cuda_stream):
+        if cuda_stream not in wrapped:
+            sw = C.c_void_p()
+            L.check(lib.nnsb_stream_wrap(aux.ctx, C.c_void_p(cuda_stream), C.byref(sw)))
+            wrapped[cuda_stream] = sw
+        plan.launch(inputs[0][0], outputs[0][0], 1, stream=wrapped[cuda_stream])
+        return 0
+
+    cfg = TensorFilter.make_config([("float32", out_dim)], rate=(30, 1))
+    filt = TensorFilter(invoke, cfg, cfg, device_id=local_rank)
+    frames = [h_batch[i * FRAME_ELEMS:(i + 1) * FRAME_ELEMS] for i in range(B)]
+
+    def step(prev):
+        tensor = None
+        for f in frames:
+            flow, tensor = conv.chain(f)
+        flow, (y,) = t.transform([tensor])
+        flow, (z,) = filt.transform([y])
+        if flow != 0:
+            raise RuntimeError("consumer-on-device step failed: %s" % lib.nnsb_last_error())
+        tensor.release()
+        y.release()
+        if prev is not None:
+            prev.release()
+        return z
+
+    z = step(None)
+    z = step(z)
+    z.sync()
+    barrier()
+    launches0 = t.kernel_launches
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        z = step(z)
+    z.sync()
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    barrier()
+    launches = (t.kernel_launches - launches0) + steps          # + one clamp launch per step
+    up, down, invokes = filt.counters
+    z.release()
+    for sw in wrapped.values():
+        lib.nnsb_stream_destroy(sw)
+    plan.close()
+    for e in (filt, t, conv):
+        e.close()
+    aux.close()
+    return ms, FRAME_ELEMS * B, up + down, launches
+
+
+def per_frame_mobilenet(dev, local_rank, with_cpu):
+    """BASELINE configs[0] as the reference runs it: frames-per-tensor=1, one 224x224 RGB frame per
+    buffer through the element (host memory in, host memory out).  Launch- and copy-latency
+    bound on a GPU; the one configuration where the CPU element is a fair opponent."""
+    from nnstreamer_b200 import TensorTransform
+    t = TensorTransform(device_id=local_rank, mode="arithmetic", option="typecast:float32,add:-127.5,div:127.5")
+    t.negotiate("other/tensor, dimension=(string)3:224:224:1, type=(string)uint8, framerate=(fraction)30/1")
+    n = 3 * 224 * 224
+    arr, ptr = dev.pinned(n, np.uint8)
+    arr[:] = np.random.default_rng(8).integers(0, 256, n, dtype=np.uint8)
+    import ctypes as C
+    from nnstreamer_b200 import _lib as L
+    ins = (L.Memory * 1)()
+    ins[0].data = ptr
+    ins[0].size = n
+    outs = (L.Memory * L.SIZE_LIMIT)()
+    n_out = C.c_uint32(0)
+    lib = L.lib()
+
+    def one():
+        if t.transform_raw(ins, 1, outs, n_out) != 0:
+            raise RuntimeError("per-frame transform failed")
+        lib.nnsb_memory_release(C.byref(outs[0]))
+
+    for _ in range(50):
+        one()
+    frames = 2000
+    t0 = time.perf_counter()
+    for _ in range(frames):
+        one()
+    dt = time.perf_counter() - t0
+    res = {"frames/s": frames / dt, "us_per_frame": dt / frames * 1e6, "frames": frames,
+           "api": "nnsb_transform_transform, one pinned host frame in, one pinned host frame out per call"}
+    if with_cpu:
+        checker = cpu_checker()[0]
+        ops = [("typecast", "float32"), ("add", -127.5), ("div", 127.5)]
+        x = np.array(arr)
+        checker.arithmetic(x, [3, 224, 224, 1], ops)
+        t0 = time.perf_counter()
+        for _ in range(200):
+            checker.arithmetic(x, [3, 224, 224, 1], ops)
+        dtc = time.perf_counter() - t0
+        res["cpu_reference_1_thread_frames/s"] = 200 / dtc
+    dev.pinned_free(ptr)
+    t.close()
+    return res
 
 
 def bind_to_gpu_numa_node(gpu_index):
@@ -599,59 +859,100 @@ def run_b200(args):
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
-    ms_e2e = (time.perf_counter() - t0) * 1e3
+    ms_e2e_rank = (time.perf_counter() - t0) * 1e3
     e2e_launches = elem.kernel_launches - launches_before
     barrier()
     clocks = sampler.stop() if rank == 0 else None
-    ms_e2e = max_over_ranks(ms_e2e)
+    reduce_device = "cuda" if dist is not None else "cpu"
+    ms_e2e = max_over_ranks(ms_e2e_rank)
+    e2e_per_rank = [v[0] / args.steps for v in
+                    sharding.gather_over_ranks([ms_e2e_rank], dist, reduce_device)]
+
+    # ---- what the host link gives every rank at the same time: the ceiling of e2e ----
+    h_out, h_out_ptr = dev.pinned(4 * n, np.uint8)
+    link_steps = max(3, min(args.steps, 10))
+    ms_link_rank = host_link_ceiling(dev, h_in_ptr, h_out_ptr, d_in, d_out, n, link_steps, barrier)
+    ms_link = max_over_ranks(ms_link_rank)
+    link_per_rank = [v[0] for v in sharding.gather_over_ranks([ms_link_rank], dist, reduce_device)]
+    dev.pinned_free(h_out_ptr)
+
+    # ---- same batch, consumer on the device: H2D only, nothing downloaded ----
+    cod_steps = max(3, min(args.steps, 10))
+    ms_cod_rank, cod_up, cod_filter_copies, cod_launches = consumer_on_device_e2e(
+        local_rank, h_in, cod_steps, barrier)
+    ms_cod = max_over_ranks(ms_cod_rank)
 
     # ---- CPU baseline (with a parity spot check of the bench data) and the other kernels ----
     parity = None
     cpu = None
     extras = None
-    if rank == 0:
-        if world == 1:
-            if not args.no_cpu_baseline:
-                # the cpu_baseline leg: the CPU code is timed, and the frame it computes anyway is
-                # compared with the first frame of the GPU's end-to-end result
-                cpu = cpu_baseline()
-                want = cpu_checker_port().arithmetic(h_in[:FRAME_ELEMS], DIM, ORACLE_OPS, True, 0)
-                parity = bool(e2e_first.tobytes() == want.tobytes())
-            if not args.no_extras:
-                dev.free(d_in)
-                dev.free(d_out)
-                d_in = d_out = None
-                extras = extra_kernels(dev, peak, with_cpu=not args.no_cpu_baseline)
-                extras["chain_8_streams_1080p_converter_typecast_arith_transpose"] = \
-                    multi_stream_chain(local_rank)
-                extras["chain_8_streams_1080p_native_driver"] = native_stream_chain(local_rank)
+    with_cpu = rank == 0 and not args.no_cpu_baseline
+    if with_cpu:
+        # the cpu_baseline leg: the CPU code is timed (shorter sample when other ranks wait), and
+        # the frame it computes anyway is compared with the first frame of the GPU's result
+        cpu = cpu_baseline(budget_s=15.0 if world == 1 else 6.0)
+        want = cpu_checker_port().arithmetic(h_in[:FRAME_ELEMS], DIM, ORACLE_OPS, True, 0)
+        parity = bool(e2e_first.tobytes() == want.tobytes())
+    if not args.no_extras:
+        dev.free(d_in)
+        dev.free(d_out)
+        d_in = d_out = None
+        elem.close()
+        # configs[4] on every N: all ranks take part (each drives its own GPU)
+        barrier()
+        chains = sharded_stream_chain(local_rank, rank, world, dist, reduce_device,
+                                      args.chain_frames, chain_parity_check if with_cpu else None)
+        if rank == 0:
+            extras = dict(chains)
+            if world == 1:
+                extras.update(extra_kernels(dev, peak, with_cpu=with_cpu))
+                extras["chain_8_streams_1080p_python_threads"] = python_stream_chain(local_rank)
+                extras["mobilenet_224_per_frame_element_e2e"] = per_frame_mobilenet(dev, local_rank, with_cpu)
 
     if rank == 0:
         ms_step = ms_dev / args.steps
         algo_bytes = n * ALGO_BYTES_PER_ELEM
         achieved = algo_bytes / (ms_step * 1e-3) / 1e9
+        e2e_ms_step = ms_e2e / args.steps
         line = {
             "metric": METRIC, "value": world * B * args.steps / (ms_dev * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_frames": B,
-                       "l2": "inputs larger than L2 (199 MB in + 796 MB out per step vs 126 MB L2)",
-                       "sharding": "one independent 32-frame stream per GPU, no collective"},
+            "config": CONFIG,
             "GB/s": world * achieved,
             "e2e": {"value": world * B * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": n, "d2h_bytes_per_step": 4 * n,
-                    "ms_per_step": ms_e2e / args.steps,
+                    "ms_per_step": e2e_ms_step,
+                    "ms_per_step_per_rank": e2e_per_rank,
+                    # bare cudaMemcpyAsync of the same bytes from the same pinned buffers, all
+                    # ranks at once, no kernels: the ceiling the host side sets for this step
+                    "host_link": {"ms_per_step": ms_link, "ms_per_step_per_rank": link_per_rank,
+                                  "GB/s_whole_box": world * 5 * n / (ms_link * 1e-3) / 1e9,
+                                  "frames/s_ceiling": world * B / (ms_link * 1e-3)},
+                    "frac_of_host_link": ms_link / e2e_ms_step,
                     "api": "nnsb_transform_transform (element mirror) on pinned host memories, "
                            "chunks pipelined on two streams; wall clock around synchronous calls"},
-            "gpu_launches": launches + e2e_launches,
-            "gpu_launches_detail": {"device_resident": launches, "e2e": e2e_launches},
+            # the same batch when the consumer is CUDA-aware (tensor_filter hand-off on the device):
+            # converter (H2D of 32 host frames) -> transform -> filter kernel, zero bytes downloaded
+            "e2e_consumer_on_device": {"value": world * B / (ms_cod * 1e-3), "unit": UNIT,
+                                       "ms_per_step": ms_cod, "h2d_bytes_per_step": cod_up,
+                                       "d2h_bytes_per_step": 0,
+                                       "bytes_copied_by_the_filter_element": cod_filter_copies,
+                                       "api": "nnsb_converter_chain x32 (host frames) -> "
+                                              "nnsb_transform_transform -> nnsb_filter_transform "
+                                              "(sub-plugin = clamp kernel on the filter's stream)"},
+            "gpu_launches": launches + e2e_launches + cod_launches,
+            "gpu_launches_detail": {"device_resident": launches, "e2e": e2e_launches,
+                                    "e2e_consumer_on_device": cod_launches},
             "host_affinity": numa,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8TBs": achieved / 8000.0,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
-                         # (profiles/r1_lut_chain_u8_f32_summary.md): 199.1 MB + 739.3 MB
-                         "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH, "peak_source": peak_src,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, read from the
+                         # committed ncu --set full capture of this kernel on this workload
+                         "traffic": ncu_traffic_bytes(),
+                         "traffic_source": os.path.relpath(NCU_RAW_CSV, ROOT),
+                         "peak_source": peak_src,
                          "kernel": "lut_chain_kernel<uint8,float,false,4> (k_chain.cuh)",
                          "algorithmic_bytes_per_launch": algo_bytes},
             "cpu_baseline": cpu,
@@ -661,6 +962,8 @@ def run_b200(args):
         if extras is not None:
             line["kernels"] = extras
         print(json.dumps(line))
+    if d_in is not None:
+        elem.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -674,6 +977,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--chain-frames", type=int, default=300,
+                    help="frames per stream of the configs[4] multi-stream chain")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the informational per-kernel table")
     ap.add_argument("--no-cpu-baseline", action="store_true",

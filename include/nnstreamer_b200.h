@@ -212,6 +212,15 @@ NNSB_API int nnsb_event_destroy (nnsb_event * e);
  * performs no cudaMalloc.  Blocks are 256-byte aligned. */
 NNSB_API int nnsb_dev_alloc (nnsb_ctx * ctx, size_t size, void **out);
 NNSB_API int nnsb_dev_free (nnsb_ctx * ctx, void *ptr);
+/* nnsb_dev_free returns the block to the pool at once: the memory must be idle (no queued GPU
+ * work still touches it).  The _async pair is stream-ordered like cudaMallocAsync: a block
+ * freed on `s` may be handed out again immediately to work on `s`, and to other streams only
+ * after the work queued on `s` at the time of the free has completed (the pool inserts the
+ * wait; the host never blocks). */
+NNSB_API int nnsb_dev_alloc_async (nnsb_stream * s, size_t size, void **out);
+NNSB_API int nnsb_dev_free_async (nnsb_stream * s, void *ptr);
+/* number of cudaMalloc calls this context has made so far (pool growth; tests) */
+NNSB_API uint64_t nnsb_ctx_device_mallocs (const nnsb_ctx * ctx);
 /* release cached blocks back to the driver */
 NNSB_API int nnsb_dev_trim (nnsb_ctx * ctx);
 NNSB_API int nnsb_dev_memset_async (nnsb_stream * s, void *dst, int value, size_t n);
@@ -312,16 +321,68 @@ NNSB_API int nnsb_merge_launch (nnsb_stream * s, uint32_t n, const void *const *
 #define NNSB_FLOW_NOT_SUPPORTED (-6)    /* GST_FLOW_NOT_SUPPORTED */
 #define NNSB_ENOENT (-2)                /* property value is NULL (e.g. `option` never set) */
 
-/* One GstMemory: a block of host or device memory.  Blocks produced by the elements are
- * `owned` (release them with nnsb_memory_release); blocks shared from the input
- * (gst_memory_ref, gsttensor_transform.c:1716) are not. */
+/* One GstMemory: a view of a block of host or device memory.
+ *
+ * Blocks produced by the elements are reference counted (GstMiniObject refcount of a
+ * GstMemory): `owned` = this view holds one reference, dropped by nnsb_memory_release; the
+ * block goes back to its pool with the last reference.  Views of caller-managed memory
+ * (block == NULL, owned == 0) are never freed here.
+ *
+ * Device memories are STREAM-ORDERED: an element returns as soon as its kernels are queued,
+ * and the block carries the CUDA event after which its contents are complete.  A consumer
+ *   - that is one of these elements waits on that event on its own stream (no host sync);
+ *   - that launches its own CUDA work calls nnsb_memory_wait (mem, stream) or takes the raw
+ *     event from nnsb_memory_export, and afterwards nnsb_memory_mark_use so the block is not
+ *     recycled under it;
+ *   - that reads the bytes from the host, or through a raw pointer on an unrelated stream,
+ *     calls nnsb_memory_sync first (what gst_memory_map does in the CUDA allocator glue).
+ * A caller-managed device input (block == NULL) must stay untouched until the outputs
+ * computed from it are ready. */
 typedef struct {
   void *data;
   size_t size;
   int32_t on_device;                    /* 0 = host, 1 = device memory of the element's GPU */
-  int32_t owned;
+  int32_t owned;                        /* 1 = holds a reference on `block` */
   void *owner;                          /* the context that allocated it */
+  void *block;                          /* opaque refcounted allocation, NULL = caller-managed */
 } nnsb_memory;
+
+/* What a CUDA-aware consumer needs to use a device memory in place: the
+ * hand-off to tensor_filter sub-plugins that want device pointers, e.g.
+ * ext/nnstreamer/tensor_filter/tensor_filter_tensorrt.cc:390, instead of the host round trip
+ * of gst_memory_map in tensor_filter.c:675. */
+typedef struct {
+  void *device_ptr;
+  size_t size;
+  int32_t device_id;
+  int32_t reserved;
+  void *ready_event;                    /* cudaEvent_t, NULL = contents are complete already */
+} nnsb_device_view;
+
+/* Memory life cycle.  No reference counterpart for the stream ordering; ref / share / release
+ * are gst_memory_ref, gst_memory_share (nnstreamer_plugin_api_impl.c:534, tensor_demux
+ * gsttensor_demux.c:516-522, tensor_mux gsttensor_mux.c:482) and gst_memory_unref. */
+/* a pooled block of `size` bytes; `s` (may be NULL) = the stream that will touch it first */
+NNSB_API int nnsb_memory_alloc (nnsb_ctx * ctx, size_t size, int on_device, nnsb_stream * s,
+    nnsb_memory * out);
+NNSB_API int nnsb_memory_ref (const nnsb_memory * mem, nnsb_memory * out);
+/* sub-range [offset, offset + size) of the same block; keeps the block alive on its own */
+NNSB_API int nnsb_memory_share (const nnsb_memory * mem, size_t offset, size_t size, nnsb_memory * out);
+NNSB_API int nnsb_memory_release (nnsb_memory * mem);
+/* stream `s` waits (on the GPU) until the contents are complete; no-op when they are */
+NNSB_API int nnsb_memory_wait (const nnsb_memory * mem, nnsb_stream * s);
+/* the calling thread waits until the contents are complete */
+NNSB_API int nnsb_memory_sync (const nnsb_memory * mem);
+/* "the work queued on `s` so far produces outs[0..n_out) and reads ins[0..n_in)": records one
+ * event; outs become ready at it, and ins are not recycled before it.  Either list may be empty. */
+NNSB_API int nnsb_memory_mark_io (nnsb_stream * s, nnsb_memory * outs, uint32_t n_out,
+    const nnsb_memory * ins, uint32_t n_in);
+NNSB_API int nnsb_memory_mark_ready (nnsb_memory * mem, nnsb_stream * s);
+NNSB_API int nnsb_memory_mark_use (const nnsb_memory * mem, nnsb_stream * s);
+/* device pointer + ready event of a device memory, for CUDA-aware consumers */
+NNSB_API int nnsb_memory_export (const nnsb_memory * mem, nnsb_device_view * view);
+/* the raw cudaStream_t behind a stream object (for consumers that launch their own work) */
+NNSB_API void *nnsb_stream_handle (nnsb_stream * s);
 
 typedef struct nnsb_transform nnsb_transform;
 
@@ -351,15 +412,16 @@ NNSB_API int nnsb_transform_transform_size (nnsb_transform * t, int direction, c
     size_t size, const char *othercaps, size_t *othersize);
 /* gst_tensor_transform_transform, :1667-1814: n_in input memories -> *n_out output memories
  * appended to out[] (capacity NNSB_SIZE_LIMIT).  Host inputs give (pinned) host outputs with
- * the copies pipelined against the kernels; device inputs give device outputs.  Returns an
- * NNSB_FLOW_* code. */
+ * the copies pipelined against the kernels, complete on return; device inputs give device
+ * outputs that are stream-ordered (see nnsb_memory: the call returns once the kernels are
+ * queued).  Tensors skipped by `apply` come out as new references to the input block
+ * (gst_memory_ref, :1716).  Returns an NNSB_FLOW_* code. */
 NNSB_API int nnsb_transform_transform (nnsb_transform * t, const nnsb_memory * in, uint32_t n_in,
     nnsb_memory * out, uint32_t *n_out);
 /* the negotiated configs (filter->in_config / out_config) */
 NNSB_API int nnsb_transform_get_config (nnsb_transform * t, int direction, nnsb_tensors_config * cfg);
 /* element-owned memory helpers (the CUDA GstAllocator's alloc / free) */
 NNSB_API int nnsb_transform_alloc (nnsb_transform * t, size_t size, int on_device, nnsb_memory * out);
-NNSB_API int nnsb_memory_release (nnsb_memory * mem);
 /* synchronous copies between a device memory of this element and host memory: what the CUDA
  * GstAllocator's mem_map / mem_unmap do for peers that are not CUDA-aware (gst_memory_map,
  * gsttensor_transform.c:1725,1761) */
@@ -494,20 +556,96 @@ NNSB_API int nnsb_split_get_out_caps (nnsb_split * s, uint32_t idx, char *out, s
 NNSB_API int nnsb_split_chain (nnsb_split * s, const nnsb_memory * in, nnsb_memory * outs,
     uint32_t max_out, uint32_t *n_out);
 
+/* ---------------------------------------------------------------------------------------
+ * Hand-off to tensor_filter without leaving HBM, and tensor_mux /
+ * tensor_demux over reference-counted device memories (rank 4).
+ * ------------------------------------------------------------------------------------- */
+#define NNSB_FLOW_DROPPED 100           /* GST_BASE_TRANSFORM_FLOW_DROPPED (GST_FLOW_CUSTOM_SUCCESS) */
+/* GstTensorMemory, tensor_typedef.h:219-223 -- `data` is a DEVICE pointer here */
+typedef struct {
+  void *data;
+  size_t size;
+} nnsb_tensor_memory;
+/* The v1 `invoke` of a tensor_filter sub-plugin (GstTensorFilterFramework,
+ * nnstreamer_plugin_api_filter.h:419-421) for a CUDA-aware framework: inputs and pre-allocated
+ * outputs are device memory, and the callback enqueues its work on `cuda_stream` (a
+ * cudaStream_t) WITHOUT synchronising -- the element has already made that stream wait for the
+ * producers of the inputs, and marks the outputs ready after whatever the callback queued.
+ * Returns 0 = ok, > 0 = drop this buffer, < 0 = error (tensor_filter.c:806-815). */
+typedef int (*nnsb_filter_invoke_fn) (void *private_data, const nnsb_tensor_memory * input,
+    uint32_t n_in, nnsb_tensor_memory * output, uint32_t n_out, void *cuda_stream);
+typedef struct nnsb_filter nnsb_filter;
+NNSB_API int nnsb_filter_new (int device_id, nnsb_filter ** out);
+NNSB_API int nnsb_filter_free (nnsb_filter * f);
+/* the framework's callback + its private_data (gst_tensor_filter_common_open_fw) */
+NNSB_API int nnsb_filter_set_framework (nnsb_filter * f, nnsb_filter_invoke_fn invoke, void *private_data);
+/* prop->input_meta / output_meta (getInputDimension / getOutputDimension of the model) */
+NNSB_API int nnsb_filter_set_info (nnsb_filter * f, const nnsb_tensors_config * in,
+    const nnsb_tensors_config * out);
+/* gst_tensor_filter_transform, tensor_filter.c:632-890: size checks (:719-735), output memories
+ * from the device pool (:737-757), invoke (:786).  Device inputs are used in place (zero bytes
+ * copied); host inputs are uploaded once (counted).  Outputs are stream-ordered device memories.
+ * Returns NNSB_FLOW_OK, NNSB_FLOW_DROPPED or NNSB_FLOW_ERROR. */
+NNSB_API int nnsb_filter_transform (nnsb_filter * f, const nnsb_memory * in, uint32_t n_in,
+    nnsb_memory * out, uint32_t *n_out);
+/* bytes this element has copied between host and device so far, and the invoke count */
+NNSB_API int nnsb_filter_copy_counters (nnsb_filter * f, uint64_t *h2d_bytes, uint64_t *d2h_bytes,
+    uint64_t *invokes);
+
+typedef struct nnsb_mux nnsb_mux;
+NNSB_API int nnsb_mux_new (nnsb_mux ** out);
+NNSB_API int nnsb_mux_free (nnsb_mux * m);
+/* gsttensor_mux.c:156-170: "silent", "sync-mode" (nosync|slowest|basepad|refresh), "sync-option"
+ * (stored; the collect-pads time synchronisation is not mirrored) */
+NNSB_API int nnsb_mux_set_property (nnsb_mux * m, const char *name, const char *value);
+NNSB_API int nnsb_mux_get_property (nnsb_mux * m, const char *name, char *buf, size_t buflen);
+/* fixed caps of the n sink pads in pad order -> other/tensors source caps (:390-412) */
+NNSB_API int nnsb_mux_set_caps (nnsb_mux * m, uint32_t n, const char *const *caps, char *out, size_t outlen);
+NNSB_API int nnsb_mux_get_config (nnsb_mux * m, nnsb_tensors_config * cfg);
+/* gst_tensor_mux_collected, :467,482: the memories of one collected set, in pad order, become
+ * the memories of one buffer -- new references, nothing is copied */
+NNSB_API int nnsb_mux_chain (nnsb_mux * m, const nnsb_memory * in, uint32_t n_in, nnsb_memory * out,
+    uint32_t *n_out);
+
+typedef struct nnsb_demux nnsb_demux;
+NNSB_API int nnsb_demux_new (nnsb_demux ** out);
+NNSB_API int nnsb_demux_free (nnsb_demux * d);
+/* gsttensor_demux.c:144-153,590-626: "silent", "tensorpick" ("0,1:2,2+0": groups split at
+ * ",.;/", indices inside a group at ":+") */
+NNSB_API int nnsb_demux_set_property (nnsb_demux * d, const char *name, const char *value);
+NNSB_API int nnsb_demux_get_property (nnsb_demux * d, const char *name, char *buf, size_t buflen);
+NNSB_API int nnsb_demux_set_caps (nnsb_demux * d, const char *caps);
+NNSB_API int nnsb_demux_num_outputs (nnsb_demux * d);
+/* caps of source pad src_<idx> (gst_tensor_demux_get_tensor_config, :288-330) */
+NNSB_API int nnsb_demux_get_out_caps (nnsb_demux * d, uint32_t idx, char *out, size_t outlen);
+/* gst_tensor_demux_chain, :468-560: source pad i receives counts[i] memories, stored back to
+ * back in outs[] -- references to the input blocks (:516-522); one blob holding several static
+ * tensors is cut into shares first (nnstreamer_plugin_api_impl.c:534). */
+NNSB_API int nnsb_demux_chain (nnsb_demux * d, const nnsb_memory * in, uint32_t n_in, nnsb_memory * outs,
+    uint32_t max_out, uint32_t *counts, uint32_t max_src, uint32_t *n_src);
+
 /* No counterpart in the reference (its CPU element simply mallocs).  The same stand kernels
  * as nnsb_plan_launch(), for callers that must not allocate while frames are flowing: a
  * pipeline whose GPU memory is already fully reserved by an inference runtime's pool, a
  * streaming thread that cannot tolerate the unbounded latency of cudaMalloc, or a plug-in
  * that is handed only a CUDA stream and device pointers.  No cudaMalloc / cudaFree / pool is
- * touched: the scratch is a fixed NNSB_NOALLOC_SCRATCH_BYTES array inside the loaded module
- * (so every GPU that loads the library holds that much memory until exit).
+ * touched: the scratch is a fixed NNSB_NOALLOC_SCRATCH_BYTES array inside the library's device
+ * image (a GPU holds that much memory from the moment the image is loaded on it until exit).
  *   d_in, d_out : `batch` tensors of shape `dim` back to back, on the CURRENT CUDA device
+ *   dim         : NNSB_RANK_LIMIT (8) entries, innermost first, unused ones set to 1 -- all
+ *                 eight are read
  *   out_type    : NNSB_TYPE_END keeps the input type (the option's default)
+ *   batch       : 1..65535 (NNSB_ERANGE above that)
  *   cuda_stream : a cudaStream_t, NULL = default stream
  * Fails with NNSB_ERANGE when batch x channels needs more scratch than the array holds.
- * The first call on a device resolves the array's device address: make it before any stream
- * capture.  All calls on a device share the array, so calls that may overlap on the GPU
- * race with each other; keep them on one stream. */
+ * WARM-UP: with CUDA's default lazy module loading the array and each kernel variant (input
+ * type x output type x mode x channel-count class) are put on the device by the first call that
+ * needs them, and that load does reserve device memory and take driver locks.  Make one call
+ * per device and per variant at initialisation -- before the other runtime takes the rest of
+ * the memory and before any stream capture (the first call on a device also resolves the
+ * array's device address) -- or run with CUDA_MODULE_LOADING=EAGER.  Later calls allocate
+ * nothing.  All calls on a device share the array, so calls that may overlap on the GPU race
+ * with each other; keep them on one stream. */
 #define NNSB_NOALLOC_SCRATCH_BYTES (1u << 20)
 NNSB_API int nnsb_stand_launch_noalloc (const void *d_in, void *d_out, int in_type,
     int out_type, const uint32_t *dim, int stand_mode, int per_channel, uint32_t batch,

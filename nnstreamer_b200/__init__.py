@@ -7,8 +7,9 @@ from . import _lib  # noqa: F401
 from ._lib import NnsbError, lib  # noqa: F401
 from .device import Device, Plan  # noqa: F401
 from .element import (BatchQueue, DeviceMemory, DirectVideoDecoder, TensorAggregator,  # noqa: F401
-                      TensorConverter, TensorMerge, TensorSplit, TensorTransform, device_memory)
+                      TensorConverter, TensorDemux, TensorFilter, TensorMerge, TensorMux,
+                      TensorSplit, TensorTransform, device_memory)
 
 __all__ = ["Device", "Plan", "NnsbError", "lib", "TensorTransform", "TensorConverter",
            "TensorAggregator", "DirectVideoDecoder", "TensorMerge", "TensorSplit", "BatchQueue",
-           "DeviceMemory"]
+           "DeviceMemory", "TensorFilter", "TensorMux", "TensorDemux", "device_memory"]

@@ -61,7 +61,21 @@ class Option(C.Structure):
 
 class Memory(C.Structure):
     _fields_ = [("data", C.c_void_p), ("size", C.c_size_t), ("on_device", C.c_int32),
-                ("owned", C.c_int32), ("owner", C.c_void_p)]
+                ("owned", C.c_int32), ("owner", C.c_void_p), ("block", C.c_void_p)]
+
+
+class DeviceView(C.Structure):
+    _fields_ = [("device_ptr", C.c_void_p), ("size", C.c_size_t), ("device_id", C.c_int32),
+                ("reserved", C.c_int32), ("ready_event", C.c_void_p)]
+
+
+class TensorMemory(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("size", C.c_size_t)]
+
+
+FILTER_INVOKE = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(TensorMemory), C.c_uint32,
+                            C.POINTER(TensorMemory), C.c_uint32, C.c_void_p)
+FLOW_DROPPED = 100
 
 
 class BufferTime(C.Structure):
@@ -160,6 +174,19 @@ _PROTOS = {
     "nnsb_transform_get_config": (C.c_int, [_VP, C.c_int, C.POINTER(TensorsConfig)]),
     "nnsb_transform_alloc": (C.c_int, [_VP, C.c_size_t, C.c_int, C.POINTER(Memory)]),
     "nnsb_memory_release": (C.c_int, [C.POINTER(Memory)]),
+    "nnsb_memory_alloc": (C.c_int, [_VP, C.c_size_t, C.c_int, _VP, C.POINTER(Memory)]),
+    "nnsb_memory_ref": (C.c_int, [C.POINTER(Memory), C.POINTER(Memory)]),
+    "nnsb_memory_share": (C.c_int, [C.POINTER(Memory), C.c_size_t, C.c_size_t, C.POINTER(Memory)]),
+    "nnsb_memory_wait": (C.c_int, [C.POINTER(Memory), _VP]),
+    "nnsb_memory_sync": (C.c_int, [C.POINTER(Memory)]),
+    "nnsb_memory_mark_io": (C.c_int, [_VP, C.POINTER(Memory), C.c_uint32, C.POINTER(Memory), C.c_uint32]),
+    "nnsb_memory_mark_ready": (C.c_int, [C.POINTER(Memory), _VP]),
+    "nnsb_memory_mark_use": (C.c_int, [C.POINTER(Memory), _VP]),
+    "nnsb_memory_export": (C.c_int, [C.POINTER(Memory), C.POINTER(DeviceView)]),
+    "nnsb_stream_handle": (_VP, [_VP]),
+    "nnsb_dev_alloc_async": (C.c_int, [_VP, C.c_size_t, C.POINTER(_VP)]),
+    "nnsb_dev_free_async": (C.c_int, [_VP, _VP]),
+    "nnsb_ctx_device_mallocs": (C.c_uint64, [_VP]),
     "nnsb_transform_download": (C.c_int, [_VP, _VP, C.POINTER(Memory)]),
     "nnsb_transform_upload": (C.c_int, [_VP, C.POINTER(Memory), _VP]),
     "nnsb_transform_kernel_launches": (C.c_int, [_VP, C.POINTER(C.c_uint64)]),
@@ -212,6 +239,31 @@ _PROTOS = {
     "nnsb_split_get_out_caps": (C.c_int, [_VP, C.c_uint32, C.c_char_p, C.c_size_t]),
     "nnsb_split_chain": (C.c_int, [_VP, C.POINTER(Memory), C.POINTER(Memory), C.c_uint32,
                                    C.POINTER(C.c_uint32)]),
+    "nnsb_filter_new": (C.c_int, [C.c_int, C.POINTER(_VP)]),
+    "nnsb_filter_free": (C.c_int, [_VP]),
+    "nnsb_filter_set_framework": (C.c_int, [_VP, FILTER_INVOKE, _VP]),
+    "nnsb_filter_set_info": (C.c_int, [_VP, C.POINTER(TensorsConfig), C.POINTER(TensorsConfig)]),
+    "nnsb_filter_transform": (C.c_int, [_VP, C.POINTER(Memory), C.c_uint32, C.POINTER(Memory),
+                                        C.POINTER(C.c_uint32)]),
+    "nnsb_filter_copy_counters": (C.c_int, [_VP, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                            C.POINTER(C.c_uint64)]),
+    "nnsb_mux_new": (C.c_int, [C.POINTER(_VP)]),
+    "nnsb_mux_free": (C.c_int, [_VP]),
+    "nnsb_mux_set_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p]),
+    "nnsb_mux_get_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "nnsb_mux_set_caps": (C.c_int, [_VP, C.c_uint32, C.POINTER(C.c_char_p), C.c_char_p, C.c_size_t]),
+    "nnsb_mux_get_config": (C.c_int, [_VP, C.POINTER(TensorsConfig)]),
+    "nnsb_mux_chain": (C.c_int, [_VP, C.POINTER(Memory), C.c_uint32, C.POINTER(Memory),
+                                 C.POINTER(C.c_uint32)]),
+    "nnsb_demux_new": (C.c_int, [C.POINTER(_VP)]),
+    "nnsb_demux_free": (C.c_int, [_VP]),
+    "nnsb_demux_set_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p]),
+    "nnsb_demux_get_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "nnsb_demux_set_caps": (C.c_int, [_VP, C.c_char_p]),
+    "nnsb_demux_num_outputs": (C.c_int, [_VP]),
+    "nnsb_demux_get_out_caps": (C.c_int, [_VP, C.c_uint32, C.c_char_p, C.c_size_t]),
+    "nnsb_demux_chain": (C.c_int, [_VP, C.POINTER(Memory), C.c_uint32, C.POINTER(Memory), C.c_uint32,
+                                   C.POINTER(C.c_uint32), C.c_uint32, C.POINTER(C.c_uint32)]),
     "nnsb_queue_create": (C.c_int, [_VP, _VP, C.c_uint32, C.POINTER(_VP)]),
     "nnsb_queue_destroy": (C.c_int, [_VP]),
     "nnsb_queue_push": (C.c_int, [_VP, _VP, C.c_int, C.POINTER(C.c_int)]),

@@ -12,13 +12,27 @@
  *   - code that is only handed a CUDA stream and device pointers by its host application
  *     and owns no nnsb_ctx in which a pool could live.
  * For them this file offers ONE entry point that never calls cudaMalloc, cudaFree or any
- * other allocating routine: the scratch is the fixed array below, which is part of the
- * loaded module.  Every GPU that loads this library therefore holds
- * NNSB_NOALLOC_SCRATCH_BYTES (1 MiB) of device memory until the process exits, whether the
- * entry point is ever used or not.
+ * other allocating routine: the scratch is the fixed array below, which is part of this
+ * library's device image.  A GPU holds those NNSB_NOALLOC_SCRATCH_BYTES (1 MiB) from the
+ * moment the image is loaded onto it until the process exits.
  *
- * The kernels are exactly those of the pooled path (k_stand.cuh, launch_stand), with the
- * same launch geometry, so the results are bit-identical to nnsb_plan_launch().
+ * When that moment is matters to exactly the users listed above.  CUDA loads device code
+ * lazily by default (CUDA_MODULE_LOADING=LAZY since 12.2): the array is materialised by the
+ * first cudaGetSymbolAddress on a device -- i.e. by the FIRST CALL of this entry point there --
+ * and every kernel variant (input type x output type x channel-count class x mode) is loaded
+ * by its first launch.  Those loads reserve device memory and take driver locks, which is
+ * precisely what the frame path must avoid.  So: make one warm-up call per device and per
+ * variant you will use during initialisation, before the other runtime reserves the rest of
+ * the memory and before any stream capture; or start the process with
+ * CUDA_MODULE_LOADING=EAGER, which moves all of it to library load time.  After that, calls
+ * allocate nothing (tests/test_zz_no_alloc.py compares cudaMemGetInfo around warmed-up calls).
+ *
+ * The kernels are exactly those of the pooled path (k_stand.cuh, launch_stand).  With the
+ * pooled path's launch geometry the results are bit-identical to nnsb_plan_launch(); when
+ * that geometry's block partials do not fit the array the entry point uses a smaller grid
+ * (four blocks per SM), i.e. another summation order, and the results then agree with
+ * nnsb_plan_launch() only within stand's tolerance (both are checked against the CPU
+ * reference in the tests).
  */
 #include <cuda_runtime.h>
 
@@ -110,9 +124,13 @@ nnsb_stand_launch_noalloc (const void *d_in, void *d_out, int in_type, int out_t
   if (stand_mode != NNSB_STAND_DEFAULT && stand_mode != NNSB_STAND_DC_AVERAGE)
     return nnsb_set_error (NNSB_EINVAL, "nnsb_stand_launch_noalloc: invalid stand mode %d", stand_mode);
   if (!nnsb_dim_is_valid (dim))
-    return nnsb_set_error (NNSB_EINVAL, "nnsb_stand_launch_noalloc: invalid dimension");
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_stand_launch_noalloc: invalid dimension "
+        "(all NNSB_RANK_LIMIT entries are read; unused ones must be 1)");
   if (batch == 0)
     return NNSB_OK;
+  if (batch > 65535)
+    return nnsb_set_error (NNSB_ERANGE, "nnsb_stand_launch_noalloc: batch %u exceeds 65535 "
+        "(one grid row per tensor); split the batch", batch);
 
   int dev = -1;
   cudaError_t e = cudaGetDevice (&dev);

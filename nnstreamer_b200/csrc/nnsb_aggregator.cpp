@@ -366,19 +366,13 @@ produce (nnsb_aggregator * a, const char *d_src, size_t frame_size, const nnsb_m
   const size_t out_size = frame_size * a->frames_out;
   const bool do_concat = needs_concat (a, frame);
   if (!do_concat && pass && pass->on_device) {
-    /* gst_pad_push of the incoming buffer itself: no copy */
-    *out = *pass;
-    out->owned = 0;
-    return NNSB_FLOW_OK;
+    /* gst_pad_push of the incoming buffer itself: no copy, one more reference */
+    return nnsb_memory_ref (pass, out) == NNSB_OK ? NNSB_FLOW_OK : NNSB_FLOW_ERROR;
   }
   if (!do_concat && adopt) {
     /* a staged copy of a host buffer is already the output */
-    out->data = adopt;
-    out->size = out_size;
-    out->on_device = 1;
-    out->owned = 1;
-    out->owner = a->ctx;
-    return NNSB_FLOW_OK;
+    return nnsb_memory_adopt (a->ctx, adopt, out_size, 1, out) == NNSB_OK ? NNSB_FLOW_OK
+        : NNSB_FLOW_ERROR;
   }
   void *d_out = nullptr;
   if (nnsb_dev_alloc (a->ctx, out_size, &d_out) != NNSB_OK)
@@ -397,11 +391,11 @@ produce (nnsb_aggregator * a, const char *d_src, size_t frame_size, const nnsb_m
     nnsb_dev_free (a->ctx, d_out);
     return NNSB_FLOW_ERROR;
   }
-  out->data = d_out;
-  out->size = out_size;
-  out->on_device = 1;
-  out->owned = 1;
-  out->owner = a->ctx;
+  if (nnsb_memory_adopt (a->ctx, d_out, out_size, 1, out) != NNSB_OK) {
+    nnsb_stream_sync (a->stream);
+    nnsb_dev_free (a->ctx, d_out);
+    return NNSB_FLOW_ERROR;
+  }
   return NNSB_FLOW_OK;
 }
 
@@ -479,6 +473,9 @@ nnsb_aggregator_chain (nnsb_aggregator * a, const nnsb_memory * in, const nnsb_b
     return NNSB_FLOW_ERROR;
   }
   if (ensure_device (a) != NNSB_OK)
+    return NNSB_FLOW_ERROR;
+  /* a device input may still be in flight on its producer's stream */
+  if (in->on_device && nnsb_memory_wait (in, a->stream) != NNSB_OK)
     return NNSB_FLOW_ERROR;
   const uint32_t frames_in = a->frames_in, frames_out = a->frames_out;
   const size_t buf_size = in->size;

@@ -192,7 +192,11 @@ nnsb_direct_video_decode (nnsb_direct_video * dv, const nnsb_tensors_config * co
   int r = NNSB_OK;
   void *staged = nullptr;
   const void *d_in = in->data;
-  if (!in->on_device) {
+  if (in->on_device)
+    r = nnsb_memory_wait (in, dv->stream);      /* may still be in flight on its producer */
+  if (r == NNSB_OK && reuse && out->on_device)
+    r = nnsb_memory_wait (out, dv->stream);
+  if (r == NNSB_OK && !in->on_device) {
     /* host tensor: stage it; the padding is then done on the device or by the copy engine */
     r = nnsb_dev_alloc (dv->ctx, row * rows, &staged);
     if (r == NNSB_OK)
@@ -215,12 +219,9 @@ nnsb_direct_video_decode (nnsb_direct_video * dv, const nnsb_tensors_config * co
       nnsb_dev_free (dv->ctx, d_out);
     return NNSB_FLOW_ERROR;
   }
-  if (!reuse) {
-    out->data = d_out;
-    out->size = size;
-    out->on_device = 1;
-    out->owned = 1;
-    out->owner = dv->ctx;
+  if (!reuse && nnsb_memory_adopt (dv->ctx, d_out, size, 1, out) != NNSB_OK) {
+    nnsb_dev_free (dv->ctx, d_out);
+    return NNSB_FLOW_ERROR;
   }
   return NNSB_FLOW_OK;
 }

@@ -419,28 +419,7 @@ nnsb_transform_alloc (nnsb_transform * t, size_t size, int on_device, nnsb_memor
   int r = ensure_device (t);
   if (r)
     return r;
-  void *p = nullptr;
-  r = on_device ? nnsb_dev_alloc (t->ctx, size, &p) : nnsb_pinned_alloc (t->ctx, size, &p);
-  if (r)
-    return r;
-  out->data = p;
-  out->size = size;
-  out->on_device = on_device ? 1 : 0;
-  out->owned = 1;
-  out->owner = t->ctx;
-  return NNSB_OK;
-}
-
-extern "C" int
-nnsb_memory_release (nnsb_memory * mem)
-{
-  if (!mem || !mem->data || !mem->owned)
-    return NNSB_OK;
-  nnsb_ctx *ctx = (nnsb_ctx *) mem->owner;
-  int r = mem->on_device ? nnsb_dev_free (ctx, mem->data) : nnsb_pinned_free (ctx, mem->data);
-  mem->data = nullptr;
-  mem->owned = 0;
-  return r;
+  return nnsb_memory_alloc (t->ctx, size, on_device, t->stream[0], out);
 }
 
 extern "C" int
@@ -449,6 +428,8 @@ nnsb_transform_download (nnsb_transform * t, void *host_dst, const nnsb_memory *
   if (!t || !host_dst || !dev_src || !dev_src->on_device)
     return nnsb_set_error (NNSB_EINVAL, "nnsb_transform_download: invalid argument");
   int r = ensure_device (t);
+  if (!r)
+    r = nnsb_memory_wait (dev_src, t->stream[0]);
   if (!r)
     r = nnsb_d2h_async (t->stream[0], host_dst, dev_src->data, dev_src->size);
   if (!r)
@@ -462,6 +443,8 @@ nnsb_transform_upload (nnsb_transform * t, const nnsb_memory * dev_dst, const vo
   if (!t || !host_src || !dev_dst || !dev_dst->on_device)
     return nnsb_set_error (NNSB_EINVAL, "nnsb_transform_upload: invalid argument");
   int r = ensure_device (t);
+  if (!r)
+    r = nnsb_memory_wait (dev_dst, t->stream[0]);
   if (!r)
     r = nnsb_h2d_async (t->stream[0], dev_dst->data, host_src, dev_dst->size);
   if (!r)
@@ -587,7 +570,7 @@ nnsb_transform_transform (nnsb_transform * t, const nnsb_memory * in, uint32_t n
     size_t off = 0;
     mems.clear ();
     for (uint32_t i = 0; i < t->in_config.num_tensors; i++) {
-      nnsb_memory m = in[0];
+      nnsb_memory m = in[0];            /* a borrowed view of the blob (same block) */
       const size_t sz = nnsb_info_size (&t->in_config.info[i]);
       m.data = (char *) in[0].data + off;
       m.size = sz;
@@ -618,9 +601,19 @@ nnsb_transform_transform (nnsb_transform * t, const nnsb_memory * in, uint32_t n
 
   int res = NNSB_FLOW_OK;
   uint32_t produced = 0;
+  /* device tensors of this buffer: everything queued on stream[0] is covered by ONE event after
+   * the loop (outputs ready at it, inputs not recycled before it) -- no host synchronisation */
+  nnsb_memory dev_ins[NNSB_SIZE_LIMIT];
+  uint32_t dev_outs[NNSB_SIZE_LIMIT];
+  uint32_t n_dev = 0;
   for (uint32_t i = 0; i < num_tensors && res == NNSB_FLOW_OK; i++) {
     nnsb_tensor_info in_info = t->in_config.info[i], out_info = t->out_config.info[i];
     const nnsb_memory & im = mems[i];
+
+    if (im.on_device && nnsb_memory_wait (&im, t->stream[0]) != NNSB_OK) {
+      res = NNSB_FLOW_ERROR;
+      break;
+    }
 
     if (!in_apply (t, i)) {
       /* :1708-1721 */
@@ -645,8 +638,13 @@ nnsb_transform_transform (nnsb_transform * t, const nnsb_memory * in, uint32_t n
         }
         out[produced++] = om;
       } else {
-        nnsb_memory shared = im;        /* gst_memory_ref */
-        shared.owned = 0;
+        /* gst_memory_ref (:1716): another reference to the same block -- for a tensor that sits
+         * inside a multi-tensor blob, a share of its byte range */
+        nnsb_memory shared;
+        if (nnsb_memory_share (&im, 0, im.size, &shared) != NNSB_OK) {
+          res = NNSB_FLOW_ERROR;
+          break;
+        }
         out[produced++] = shared;
       }
       continue;
@@ -723,7 +721,9 @@ nnsb_transform_transform (nnsb_transform * t, const nnsb_memory * in, uint32_t n
       r = nnsb_plan_launch (plan, inptr, outptr, 1, t->stream[0]);
       if (!r) {
         t->launches += (uint64_t) nnsb_plan_last_launch_count (plan);
-        r = nnsb_stream_sync (t->stream[0]);
+        dev_ins[n_dev] = im;
+        dev_outs[n_dev] = produced - 1;
+        n_dev++;
       }
     } else {
       r = run_host_tensor (t, plan, inptr, outptr);
@@ -731,8 +731,17 @@ nnsb_transform_transform (nnsb_transform * t, const nnsb_memory * in, uint32_t n
     if (r != NNSB_OK)
       res = NNSB_FLOW_ERROR;
   }
+  if (n_dev) {
+    nnsb_memory marked[NNSB_SIZE_LIMIT];
+    for (uint32_t k = 0; k < n_dev; k++)
+      marked[k] = out[dev_outs[k]];
+    if (nnsb_memory_mark_io (t->stream[0], marked, n_dev, dev_ins, n_dev) != NNSB_OK)
+      res = NNSB_FLOW_ERROR;
+  }
   *n_out = produced;
   if (res != NNSB_FLOW_OK) {
+    /* the failed buffer's blocks must be idle before they go back to the pool */
+    nnsb_stream_sync (t->stream[0]);
     for (uint32_t i = 0; i < produced; i++)
       nnsb_memory_release (&out[i]);
     *n_out = 0;
@@ -756,9 +765,23 @@ struct nnsb_converter
   size_t frame_size = 0;                /* GST_VIDEO_INFO_SIZE: padded */
   size_t row_bytes = 0, pitch = 0, rows = 0;
   size_t dense_frame = 0;               /* C*W*H */
-  void *d_batch = nullptr;              /* current batch buffer (device) */
+  nnsb_memory batch;                    /* current batch buffer (device block), data == NULL: none */
+  uint32_t batch_cap = 0;               /* frames the block was allocated for */
   uint32_t filled = 0;
 };
+
+static void
+converter_drop_batch (nnsb_converter * c)
+{
+  if (c->batch.data) {
+    if (c->stream)
+      nnsb_stream_sync (c->stream);
+    nnsb_memory_release (&c->batch);
+  }
+  memset (&c->batch, 0, sizeof (c->batch));
+  c->batch_cap = 0;
+  c->filled = 0;
+}
 
 extern "C" int
 nnsb_converter_new (int device_id, nnsb_converter ** out)
@@ -770,6 +793,7 @@ nnsb_converter_new (int device_id, nnsb_converter ** out)
     return nnsb_set_error (NNSB_ENOMEM, "nnsb_converter_new: out of memory");
   c->device_id = device_id;
   config_init (&c->config);
+  memset (&c->batch, 0, sizeof (c->batch));
   *out = c;
   return NNSB_OK;
 }
@@ -779,8 +803,7 @@ nnsb_converter_free (nnsb_converter * c)
 {
   if (!c)
     return NNSB_OK;
-  if (c->d_batch)
-    nnsb_dev_free (c->ctx, c->d_batch);
+  converter_drop_batch (c);
   if (c->stream)
     nnsb_stream_destroy (c->stream);
   if (c->ctx)
@@ -800,7 +823,36 @@ nnsb_converter_set_property (nnsb_converter * c, const char *name, const char *v
     long v = strtol (value, &end, 10);
     if (end == value || *end || v < 1)
       return nnsb_set_error (NNSB_EINVAL, "frames-per-tensor: expected an unsigned integer >= 1");
-    c->frames_per_tensor = (uint32_t) v;
+    const uint32_t fpt = (uint32_t) v;
+    if (fpt != c->frames_per_tensor && c->batch.data && c->filled) {
+      /* A batch is partly filled and was sized for the old count.  The reference's GstAdapter
+       * just keeps the bytes (gsttensor_converter.c:945-1009); here the frames move into a block
+       * of the new size.  If more frames are waiting than the new tensor can take together with
+       * the next one, the oldest fpt-1 are kept (the reference would emit several tensors from
+       * one chain call, which this one-output-per-call interface cannot). */
+      const uint32_t keep = c->filled < fpt ? c->filled : fpt - 1;
+      nnsb_memory fresh;
+      memset (&fresh, 0, sizeof (fresh));
+      int r = NNSB_OK;
+      if (keep) {
+        r = nnsb_memory_alloc (c->ctx, c->dense_frame * fpt, 1, c->stream, &fresh);
+        if (!r)
+          r = nnsb_d2d_async (c->stream, fresh.data, c->batch.data, c->dense_frame * keep);
+        if (!r)
+          r = nnsb_stream_sync (c->stream);
+        if (r) {
+          nnsb_memory_release (&fresh);
+          return r;
+        }
+      }
+      converter_drop_batch (c);
+      c->batch = fresh;
+      c->batch_cap = keep ? fpt : 0;
+      c->filled = keep;
+    } else if (fpt != c->frames_per_tensor && c->batch.data) {
+      converter_drop_batch (c);
+    }
+    c->frames_per_tensor = fpt;
     if (c->configured)
       c->config.info[0].dim[3] = c->frames_per_tensor;
     return NNSB_OK;
@@ -885,7 +937,7 @@ nnsb_converter_set_caps (nnsb_converter * c, const char *video_caps, char *out, 
   c->frame_size = c->pitch * c->rows;                   /* GST_VIDEO_INFO_SIZE for packed RGB / GRAY8 */
   c->dense_frame = c->row_bytes * c->rows;
   c->configured = true;
-  c->filled = 0;
+  converter_drop_batch (c);             /* new caps: frames of the old geometry are gone */
   if (!config_validate (c->config))
     return nnsb_set_error (NNSB_EINVAL, "Failed to configure tensors info with gst cap (%s)", video_caps);
   if (out)
@@ -936,19 +988,29 @@ nnsb_converter_chain (nnsb_converter * c, const nnsb_memory * frame, nnsb_memory
   if (c->frames_per_tensor == 1 && frame->on_device && !c->remove_padding) {
     /* nothing to strip, nothing to batch: the frame IS the tensor (the reference pushes the
      * incoming buffer itself when remove_padding is FALSE, gsttensor_converter.c:1062,1107-1109) */
-    *out = *frame;
-    out->owned = 0;
+    if (nnsb_memory_ref (frame, out) != NNSB_OK)
+      return NNSB_FLOW_ERROR;
     *produced = 1;
     return NNSB_FLOW_OK;
   }
   const size_t batch_bytes = c->dense_frame * c->frames_per_tensor;
-  if (!c->d_batch) {
-    if (nnsb_dev_alloc (c->ctx, batch_bytes, &c->d_batch) != NNSB_OK)
+  if (!c->batch.data) {
+    if (nnsb_memory_alloc (c->ctx, batch_bytes, 1, c->stream, &c->batch) != NNSB_OK)
       return NNSB_FLOW_ERROR;
+    c->batch_cap = c->frames_per_tensor;
     c->filled = 0;
   }
-  char *dst = (char *) c->d_batch + (size_t) c->filled * c->dense_frame;
-  int r;
+  if (c->filled >= c->batch_cap || c->batch_cap != c->frames_per_tensor) {
+    nnsb_set_error (NNSB_FLOW_ERROR, "tensor_converter: batch buffer of %u frames cannot take frame %u",
+        c->batch_cap, c->filled);
+    return NNSB_FLOW_ERROR;
+  }
+  char *dst = (char *) c->batch.data + (size_t) c->filled * c->dense_frame;
+  int r = NNSB_OK;
+  if (frame->on_device)
+    r = nnsb_memory_wait (frame, c->stream);
+  if (r != NNSB_OK)
+    return NNSB_FLOW_ERROR;
   if (c->remove_padding) {
     /* the row loop of :1087-1100, done by the copy engine (host frame) or K8 (device frame) */
     if (frame->on_device)
@@ -962,16 +1024,24 @@ nnsb_converter_chain (nnsb_converter * c, const nnsb_memory * frame, nnsb_memory
   if (r != NNSB_OK)
     return NNSB_FLOW_ERROR;
   c->filled++;
-  /* the source frame may be reused by the caller after we return */
-  if (nnsb_stream_sync (c->stream) != NNSB_OK)
-    return NNSB_FLOW_ERROR;
-  if (c->filled == c->frames_per_tensor) {
-    out->data = c->d_batch;
+  const bool complete = c->filled == c->frames_per_tensor;
+  if (frame->on_device) {
+    /* stream-ordered: the frame's block is not recycled before the copy has read it, and the
+     * batch becomes ready with its last frame */
+    if (nnsb_memory_mark_io (c->stream, &c->batch, complete ? 1 : 0, frame, 1) != NNSB_OK)
+      return NNSB_FLOW_ERROR;
+    if (!frame->block && nnsb_stream_sync (c->stream) != NNSB_OK)
+      return NNSB_FLOW_ERROR;   /* caller-managed device frame: it may be reused on return */
+  } else {
+    /* a host frame may be reused by the caller as soon as we return */
+    if (nnsb_stream_sync (c->stream) != NNSB_OK)
+      return NNSB_FLOW_ERROR;
+  }
+  if (complete) {
+    *out = c->batch;
     out->size = batch_bytes;
-    out->on_device = 1;
-    out->owned = 1;
-    out->owner = c->ctx;
-    c->d_batch = nullptr;
+    memset (&c->batch, 0, sizeof (c->batch));
+    c->batch_cap = 0;
     c->filled = 0;
     *produced = 1;
   }

@@ -44,6 +44,10 @@ nnsb_cell nnsb_cast_operand (const nnsb_arith_op * op, int type);
 
 /* clamp bounds / stand: nothing to precompile */
 
+/* wraps a raw allocation of `ctx` (nnsb_dev_alloc / nnsb_pinned_alloc) into an owned,
+ * reference-counted memory (nnsb_runtime.cu); on failure the allocation stays raw */
+int nnsb_memory_adopt (nnsb_ctx * ctx, void *ptr, size_t size, int on_device, nnsb_memory * out);
+
 #ifdef __cplusplus
 }
 #endif

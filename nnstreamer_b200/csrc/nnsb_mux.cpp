@@ -285,6 +285,7 @@ nnsb_merge_chain (nnsb_merge * m, const nnsb_memory * in, uint32_t n, nnsb_memor
     out_size += in[k].size;             /* outSize += mInfo[i].size, :494 */
     if (in[k].on_device) {
       d_in[k] = in[k].data;
+      r = nnsb_memory_wait (&in[k], m->stream);   /* may still be in flight on its producer */
     } else {
       void *d = nullptr;
       r = nnsb_dev_alloc (m->ctx, in[k].size, &d);
@@ -309,11 +310,10 @@ nnsb_merge_chain (nnsb_merge * m, const nnsb_memory * in, uint32_t n, nnsb_memor
       nnsb_dev_free (m->ctx, d_out);
     return NNSB_FLOW_ERROR;
   }
-  out->data = d_out;
-  out->size = out_size;
-  out->on_device = 1;
-  out->owned = 1;
-  out->owner = m->ctx;
+  if (nnsb_memory_adopt (m->ctx, d_out, out_size, 1, out) != NNSB_OK) {
+    nnsb_dev_free (m->ctx, d_out);
+    return NNSB_FLOW_ERROR;
+  }
   return NNSB_FLOW_OK;
 }
 
@@ -505,7 +505,7 @@ nnsb_split_chain (nnsb_split * s, const nnsb_memory * in, nnsb_memory * outs, ui
     return NNSB_FLOW_ERROR;
   const size_t es = nnsb_element_size (s->sink_config.info[0].type);
   size_t offset = 0;
-  int r = NNSB_OK;
+  int r = in->on_device ? nnsb_memory_wait (in, s->stream) : NNSB_OK;
   for (size_t i = 0; i < s->seg.size () && r == NNSB_OK; i++) {
     const size_t size = (size_t) nnsb_element_count (s->seg[i].data ()) * es;
     bool picked = s->pick.empty ();
@@ -524,13 +524,13 @@ nnsb_split_chain (nnsb_split * s, const nnsb_memory * in, nnsb_memory * outs, ui
         const char *src = (const char *) in->data + offset;
         r = in->on_device ? nnsb_d2d_async (s->stream, d, src, size)
             : nnsb_h2d_async (s->stream, d, src, size);
-        nnsb_memory & o = outs[*n_out];
-        o.data = d;
-        o.size = size;
-        o.on_device = 1;
-        o.owned = 1;
-        o.owner = s->ctx;
-        (*n_out)++;
+        if (nnsb_memory_adopt (s->ctx, d, size, 1, &outs[*n_out]) == NNSB_OK) {
+          (*n_out)++;
+        } else {
+          nnsb_stream_sync (s->stream);
+          nnsb_dev_free (s->ctx, d);
+          r = NNSB_FLOW_ERROR;
+        }
       }
     }
     offset += size;

@@ -30,16 +30,55 @@ using namespace nnsb;
 /* ------------------------------------------------------------------------------------- */
 /* objects                                                                                 */
 /* ------------------------------------------------------------------------------------- */
+/* A recorded CUDA event shared by everything that depends on the same point of a stream: the
+ * "ready" mark of the blocks a launch produced and the "last use" mark of the blocks it read.
+ * Events are pooled per device for the life of the process (creating one costs microseconds). */
+struct nnsb_evt
+{
+  cudaEvent_t e;
+  cudaStream_t stream;          /* the stream it was recorded on */
+  int device;
+  int refs;                     /* guarded by g_evt_mu */
+};
+
+/* a cached block and the events that must have completed before another stream may touch it */
+struct Cached
+{
+  void *ptr;
+  std::vector<nnsb_evt *> pending;
+};
+
+struct LiveInfo
+{
+  size_t bucket;
+  bool is_block;                /* wrapped by an nnsb_block (survives nnsb_ctx_destroy) */
+};
+
 struct nnsb_ctx
 {
   int device;
   int sm_count;
   int blocks_per_sm;            /* 0 = per-kernel default; NNSB_BLOCKS_PER_SM overrides */
   std::mutex mu;
-  std::map<size_t, std::vector<void *> > dev_free;     /* bucket -> cached blocks */
-  std::map<void *, size_t> dev_live;                  /* block -> bucket */
+  int refs;                     /* creator + live blocks; guarded by mu */
+  bool closing;                 /* nnsb_ctx_destroy was called: nothing is cached any more */
+  uint64_t n_dev_malloc;
+  std::map<size_t, std::vector<Cached> > dev_free;    /* bucket -> cached blocks (oldest first) */
+  std::map<size_t, int> dev_count;                    /* bucket -> blocks obtained from cudaMalloc */
+  std::map<void *, LiveInfo> dev_live;                /* block -> bucket */
   std::map<size_t, std::vector<void *> > pin_free;
-  std::map<void *, size_t> pin_live;
+  std::map<void *, LiveInfo> pin_live;
+};
+
+/* One reference-counted allocation behind any number of nnsb_memory views. */
+struct nnsb_block
+{
+  nnsb_ctx *ctx;
+  void *base;
+  int on_device;
+  int refs;                     /* guarded by ctx->mu */
+  nnsb_evt *ready;              /* contents complete after this event (NULL = now) */
+  std::vector<nnsb_evt *> uses; /* at most one per stream: work that still reads the block */
 };
 
 struct nnsb_stream
@@ -111,6 +150,84 @@ bucket_of (size_t size)
 }
 
 /* ------------------------------------------------------------------------------------- */
+/* pooled events                                                                           */
+/* ------------------------------------------------------------------------------------- */
+static std::mutex g_evt_mu;
+static std::map<int, std::vector<nnsb_evt *> > g_evt_free;      /* device -> idle events */
+
+/* a new event recorded on `stream` (device `device` must be current); one reference */
+static nnsb_evt *
+evt_record (int device, cudaStream_t stream)
+{
+  nnsb_evt *ev = nullptr;
+  {
+    std::lock_guard<std::mutex> lk (g_evt_mu);
+    auto & v = g_evt_free[device];
+    if (!v.empty ()) {
+      ev = v.back ();
+      v.pop_back ();
+    }
+  }
+  if (!ev) {
+    cudaEvent_t e;
+    if (cudaEventCreateWithFlags (&e, cudaEventDisableTiming) != cudaSuccess) {
+      cudaGetLastError ();
+      return nullptr;
+    }
+    ev = new (std::nothrow) nnsb_evt ();
+    if (!ev) {
+      cudaEventDestroy (e);
+      return nullptr;
+    }
+    ev->e = e;
+    ev->device = device;
+  }
+  ev->stream = stream;
+  ev->refs = 1;
+  if (cudaEventRecord (ev->e, stream) != cudaSuccess) {
+    cudaGetLastError ();
+    std::lock_guard<std::mutex> lk (g_evt_mu);
+    g_evt_free[device].push_back (ev);
+    return nullptr;
+  }
+  return ev;
+}
+
+static nnsb_evt *
+evt_ref (nnsb_evt * ev)
+{
+  if (ev) {
+    std::lock_guard<std::mutex> lk (g_evt_mu);
+    ev->refs++;
+  }
+  return ev;
+}
+
+static void
+evt_unref (nnsb_evt * ev)
+{
+  if (!ev)
+    return;
+  std::lock_guard<std::mutex> lk (g_evt_mu);
+  if (--ev->refs == 0)
+    g_evt_free[ev->device].push_back (ev);
+}
+
+/* true when work on `stream` (or anybody, if have_stream is false) may touch what the event guards */
+static bool
+evt_satisfied (nnsb_evt * ev, bool have_stream, cudaStream_t stream)
+{
+  if (have_stream && ev->stream == stream)
+    return true;                /* same stream: ordered by construction */
+  cudaError_t e = cudaEventQuery (ev->e);
+  if (e == cudaSuccess)
+    return true;
+  if (e != cudaErrorNotReady)
+    cudaGetLastError ();
+  return false;
+}
+
+/* ------------------------------------------------------------------------------------- */
 /* context / stream / event                                                                */
 /* ------------------------------------------------------------------------------------- */
 extern "C" int
@@ -147,11 +264,22 @@ nnsb_ctx_create (int device_id, nnsb_ctx ** out)
   ctx->device = device_id;
   ctx->sm_count = prop.multiProcessorCount;
   ctx->blocks_per_sm = 0;
+  ctx->refs = 1;
+  ctx->closing = false;
+  ctx->n_dev_malloc = 0;
   const char *env = getenv ("NNSB_BLOCKS_PER_SM");
   if (env && atoi (env) > 0)
     ctx->blocks_per_sm = atoi (env);
   *out = ctx;
   return NNSB_OK;
+}
+
+static void
+drop_pending (Cached & c)
+{
+  for (nnsb_evt * ev : c.pending)
+    evt_unref (ev);
+  c.pending.clear ();
 }
 
 extern "C" int
@@ -160,16 +288,38 @@ nnsb_dev_trim (nnsb_ctx * ctx)
   int r = bind (ctx);
   if (r)
     return r;
-  std::lock_guard<std::mutex> lk (ctx->mu);
-  for (auto & kv : ctx->dev_free)
-    for (void *p : kv.second)
-      cudaFree (p);
-  ctx->dev_free.clear ();
-  for (auto & kv : ctx->pin_free)
+  std::map<size_t, std::vector<Cached> > dev;
+  std::map<size_t, std::vector<void *> > pin;
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    dev.swap (ctx->dev_free);
+    pin.swap (ctx->pin_free);
+    for (auto & kv : dev)
+      ctx->dev_count[kv.first] -= (int) kv.second.size ();
+  }
+  /* cudaFree waits for the work still touching the block */
+  for (auto & kv : dev)
+    for (Cached & c : kv.second) {
+      drop_pending (c);
+      cudaFree (c.ptr);
+    }
+  for (auto & kv : pin)
     for (void *p : kv.second)
       cudaFreeHost (p);
-  ctx->pin_free.clear ();
   return NNSB_OK;
+}
+
+/* drops one reference; the context goes away with the last one (mu must NOT be held) */
+static void
+ctx_unref (nnsb_ctx * ctx)
+{
+  bool last;
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    last = --ctx->refs == 0;
+  }
+  if (last)
+    delete ctx;
 }
 
 extern "C" int
@@ -179,14 +329,41 @@ nnsb_ctx_destroy (nnsb_ctx * ctx)
     return NNSB_OK;
   if (bind (ctx) == NNSB_OK) {
     cudaDeviceSynchronize ();
+    std::vector<void *> dev, pin;
+    {
+      std::lock_guard<std::mutex> lk (ctx->mu);
+      ctx->closing = true;
+      /* raw allocations belong to whoever created the context; blocks still referenced by a
+       * memory somewhere downstream stay alive until their last nnsb_memory_release */
+      for (auto it = ctx->dev_live.begin (); it != ctx->dev_live.end ();) {
+        if (!it->second.is_block) {
+          dev.push_back (it->first);
+          it = ctx->dev_live.erase (it);
+        } else
+          ++it;
+      }
+      for (auto it = ctx->pin_live.begin (); it != ctx->pin_live.end ();) {
+        if (!it->second.is_block) {
+          pin.push_back (it->first);
+          it = ctx->pin_live.erase (it);
+        } else
+          ++it;
+      }
+    }
     nnsb_dev_trim (ctx);
-    for (auto & kv : ctx->dev_live)
-      cudaFree (kv.first);
-    for (auto & kv : ctx->pin_live)
-      cudaFreeHost (kv.first);
+    for (void *p : dev)
+      cudaFree (p);
+    for (void *p : pin)
+      cudaFreeHost (p);
   }
-  delete ctx;
+  ctx_unref (ctx);
   return NNSB_OK;
+}
+
+extern "C" uint64_t
+nnsb_ctx_device_mallocs (const nnsb_ctx * ctx)
+{
+  return ctx ? ctx->n_dev_malloc : 0;
 }
 
 extern "C" int
@@ -348,6 +525,117 @@ nnsb_event_destroy (nnsb_event * e)
 /* ------------------------------------------------------------------------------------- */
 /* memory                                                                                  */
 /* ------------------------------------------------------------------------------------- */
+/* How many blocks of one size a context may obtain from cudaMalloc before it starts reusing
+ * blocks whose last GPU work is still in flight (the pool then makes the new user's stream
+ * wait for that work; the host never blocks).  Three blocks let producer, consumer and the
+ * next frame overlap. */
+static const int POOL_DEPTH_BEFORE_WAIT = 3;
+
+/* Takes a device block of `bucket` bytes.  have_stream: the block will first be touched by
+ * work on `stream`. */
+static int
+dev_take (nnsb_ctx * ctx, size_t b, bool have_stream, cudaStream_t stream, void **out, bool as_block)
+{
+  std::vector<nnsb_evt *> must_wait;
+  void *p = nullptr;
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    auto it = ctx->dev_free.find (b);
+    if (it != ctx->dev_free.end () && !it->second.empty ()) {
+      std::vector<Cached> & v = it->second;
+      /* newest first: a block nothing in flight touches (or only this stream does) */
+      for (size_t i = v.size (); i-- > 0 && !p;) {
+        bool ok = true;
+        for (nnsb_evt * ev : v[i].pending)
+          if (!evt_satisfied (ev, have_stream, stream)) {
+            ok = false;
+            break;
+          }
+        if (ok) {
+          p = v[i].ptr;
+          drop_pending (v[i]);
+          v.erase (v.begin () + (long) i);
+        }
+      }
+      if (!p && ctx->dev_count[b] >= POOL_DEPTH_BEFORE_WAIT) {
+        /* every cached block is still in use by queued work: take the oldest and wait for it */
+        p = v.front ().ptr;
+        must_wait.swap (v.front ().pending);
+        v.erase (v.begin ());
+      }
+    }
+    if (p)
+      ctx->dev_live[p] = LiveInfo { b, as_block };
+  }
+  if (p) {
+    for (nnsb_evt * ev : must_wait) {
+      if (have_stream) {
+        if (ev->stream != stream)
+          cudaStreamWaitEvent (stream, ev->e, 0);
+      } else {
+        cudaEventSynchronize (ev->e);
+      }
+      evt_unref (ev);
+    }
+    *out = p;
+    return NNSB_OK;
+  }
+  cudaError_t e = cudaMalloc (&p, b);
+  if (e != cudaSuccess) {
+    /* give cached blocks back and retry once */
+    cudaGetLastError ();
+    nnsb_dev_trim (ctx);
+    e = cudaMalloc (&p, b);
+    if (e != cudaSuccess) {
+      cudaGetLastError ();
+      return nnsb_set_error (NNSB_ENOMEM, "cudaMalloc (%zu) failed: %s", b, cudaGetErrorString (e));
+    }
+  }
+  std::lock_guard<std::mutex> lk (ctx->mu);
+  ctx->dev_live[p] = LiveInfo { b, as_block };
+  ctx->dev_count[b] += 1;
+  ctx->n_dev_malloc += 1;
+  *out = p;
+  return NNSB_OK;
+}
+
+/* Returns a device block to the pool (or to the driver when the context is closing).
+ * `pending` is consumed. */
+static int
+dev_give (nnsb_ctx * ctx, void *ptr, std::vector<nnsb_evt *> & pending)
+{
+  bool free_now = false;
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    auto it = ctx->dev_live.find (ptr);
+    if (it == ctx->dev_live.end ()) {
+      for (nnsb_evt * ev : pending)
+        evt_unref (ev);
+      pending.clear ();
+      return nnsb_set_error (NNSB_EINVAL, "%p was not allocated by this context", ptr);
+    }
+    const size_t b = it->second.bucket;
+    ctx->dev_live.erase (it);
+    if (ctx->closing) {
+      free_now = true;
+      ctx->dev_count[b] -= 1;
+    } else {
+      Cached c;
+      c.ptr = ptr;
+      c.pending.swap (pending);
+      ctx->dev_free[b].push_back (c);
+    }
+  }
+  if (free_now) {
+    for (nnsb_evt * ev : pending)
+      evt_unref (ev);
+    pending.clear ();
+    if (cudaSetDevice (ctx->device) == cudaSuccess)
+      cudaFree (ptr);           /* waits for the work still touching it */
+  }
+  return NNSB_OK;
+}
+
 extern "C" int
 nnsb_dev_alloc (nnsb_ctx * ctx, size_t size, void **out)
 {
@@ -357,33 +645,7 @@ nnsb_dev_alloc (nnsb_ctx * ctx, size_t size, void **out)
   int r = bind (ctx);
   if (r)
     return r;
-  const size_t b = bucket_of (size);
-  {
-    std::lock_guard<std::mutex> lk (ctx->mu);
-    auto it = ctx->dev_free.find (b);
-    if (it != ctx->dev_free.end () && !it->second.empty ()) {
-      void *p = it->second.back ();
-      it->second.pop_back ();
-      ctx->dev_live[p] = b;
-      *out = p;
-      return NNSB_OK;
-    }
-  }
-  void *p = nullptr;
-  cudaError_t e = cudaMalloc (&p, b);
-  if (e != cudaSuccess) {
-    /* give cached blocks back and retry once */
-    nnsb_dev_trim (ctx);
-    e = cudaMalloc (&p, b);
-    if (e != cudaSuccess) {
-      cudaGetLastError ();
-      return nnsb_set_error (NNSB_ENOMEM, "cudaMalloc (%zu) failed: %s", b, cudaGetErrorString (e));
-    }
-  }
-  std::lock_guard<std::mutex> lk (ctx->mu);
-  ctx->dev_live[p] = b;
-  *out = p;
-  return NNSB_OK;
+  return dev_take (ctx, bucket_of (size), false, nullptr, out, false);
 }
 
 extern "C" int
@@ -393,12 +655,86 @@ nnsb_dev_free (nnsb_ctx * ctx, void *ptr)
     return NNSB_OK;
   if (!ctx)
     return nnsb_set_error (NNSB_EINVAL, "nnsb_dev_free: null context");
+  std::vector<nnsb_evt *> none;
+  return dev_give (ctx, ptr, none);
+}
+
+extern "C" int
+nnsb_dev_alloc_async (nnsb_stream * s, size_t size, void **out)
+{
+  if (!out || !s)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_dev_alloc_async: null argument");
+  *out = nullptr;
+  int r = bind (s->ctx);
+  if (r)
+    return r;
+  return dev_take (s->ctx, bucket_of (size), true, s->s, out, false);
+}
+
+extern "C" int
+nnsb_dev_free_async (nnsb_stream * s, void *ptr)
+{
+  if (!ptr)
+    return NNSB_OK;
+  if (!s)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_dev_free_async: null stream");
+  int r = bind (s->ctx);
+  if (r)
+    return r;
+  std::vector<nnsb_evt *> pending;
+  nnsb_evt *ev = evt_record (s->ctx->device, s->s);
+  if (!ev) {
+    /* no event to be had: fall back to waiting here */
+    cudaStreamSynchronize (s->s);
+  } else {
+    pending.push_back (ev);
+  }
+  return dev_give (s->ctx, ptr, pending);
+}
+
+static int
+pinned_take (nnsb_ctx * ctx, size_t b, void **out, bool as_block)
+{
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    auto it = ctx->pin_free.find (b);
+    if (it != ctx->pin_free.end () && !it->second.empty ()) {
+      void *p = it->second.back ();
+      it->second.pop_back ();
+      ctx->pin_live[p] = LiveInfo { b, as_block };
+      *out = p;
+      return NNSB_OK;
+    }
+  }
+  void *p = nullptr;
+  cudaError_t e = cudaHostAlloc (&p, b, cudaHostAllocDefault);
+  if (e != cudaSuccess) {
+    cudaGetLastError ();
+    return nnsb_set_error (NNSB_ENOMEM, "cudaHostAlloc (%zu) failed: %s", b, cudaGetErrorString (e));
+  }
   std::lock_guard<std::mutex> lk (ctx->mu);
-  auto it = ctx->dev_live.find (ptr);
-  if (it == ctx->dev_live.end ())
-    return nnsb_set_error (NNSB_EINVAL, "nnsb_dev_free: %p was not allocated by this context", ptr);
-  ctx->dev_free[it->second].push_back (ptr);
-  ctx->dev_live.erase (it);
+  ctx->pin_live[p] = LiveInfo { b, as_block };
+  *out = p;
+  return NNSB_OK;
+}
+
+static int
+pinned_give (nnsb_ctx * ctx, void *ptr)
+{
+  bool free_now = false;
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    auto it = ctx->pin_live.find (ptr);
+    if (it == ctx->pin_live.end ())
+      return nnsb_set_error (NNSB_EINVAL, "nnsb_pinned_free: %p was not allocated by this context", ptr);
+    if (ctx->closing)
+      free_now = true;
+    else
+      ctx->pin_free[it->second.bucket].push_back (ptr);
+    ctx->pin_live.erase (it);
+  }
+  if (free_now && cudaSetDevice (ctx->device) == cudaSuccess)
+    cudaFreeHost (ptr);
   return NNSB_OK;
 }
 
@@ -411,28 +747,7 @@ nnsb_pinned_alloc (nnsb_ctx * ctx, size_t size, void **out)
   int r = bind (ctx);
   if (r)
     return r;
-  const size_t b = bucket_of (size);
-  {
-    std::lock_guard<std::mutex> lk (ctx->mu);
-    auto it = ctx->pin_free.find (b);
-    if (it != ctx->pin_free.end () && !it->second.empty ()) {
-      void *p = it->second.back ();
-      it->second.pop_back ();
-      ctx->pin_live[p] = b;
-      *out = p;
-      return NNSB_OK;
-    }
-  }
-  void *p = nullptr;
-  cudaError_t e = cudaHostAlloc (&p, b, cudaHostAllocDefault);
-  if (e != cudaSuccess) {
-    cudaGetLastError ();
-    return nnsb_set_error (NNSB_ENOMEM, "cudaHostAlloc (%zu) failed: %s", b, cudaGetErrorString (e));
-  }
-  std::lock_guard<std::mutex> lk (ctx->mu);
-  ctx->pin_live[p] = b;
-  *out = p;
-  return NNSB_OK;
+  return pinned_take (ctx, bucket_of (size), out, false);
 }
 
 extern "C" int
@@ -442,13 +757,315 @@ nnsb_pinned_free (nnsb_ctx * ctx, void *ptr)
     return NNSB_OK;
   if (!ctx)
     return nnsb_set_error (NNSB_EINVAL, "nnsb_pinned_free: null context");
-  std::lock_guard<std::mutex> lk (ctx->mu);
-  auto it = ctx->pin_live.find (ptr);
-  if (it == ctx->pin_live.end ())
-    return nnsb_set_error (NNSB_EINVAL, "nnsb_pinned_free: %p was not allocated by this context", ptr);
-  ctx->pin_free[it->second].push_back (ptr);
-  ctx->pin_live.erase (it);
+  return pinned_give (ctx, ptr);
+}
+
+/* ------------------------------------------------------------------------------------- */
+/* nnsb_memory: reference-counted, stream-ordered views                                    */
+/* ------------------------------------------------------------------------------------- */
+extern "C" int
+nnsb_memory_alloc (nnsb_ctx * ctx, size_t size, int on_device, nnsb_stream * s, nnsb_memory * out)
+{
+  if (!out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_alloc: null argument");
+  memset (out, 0, sizeof (*out));
+  int r = bind (ctx);
+  if (r)
+    return r;
+  nnsb_block *blk = new (std::nothrow) nnsb_block ();
+  if (!blk)
+    return nnsb_set_error (NNSB_ENOMEM, "nnsb_memory_alloc: out of memory");
+  void *p = nullptr;
+  const size_t b = bucket_of (size);
+  r = on_device ? dev_take (ctx, b, s != nullptr, s ? s->s : nullptr, &p, true)
+      : pinned_take (ctx, b, &p, true);
+  if (r) {
+    delete blk;
+    return r;
+  }
+  blk->ctx = ctx;
+  blk->base = p;
+  blk->on_device = on_device ? 1 : 0;
+  blk->refs = 1;
+  blk->ready = nullptr;
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    ctx->refs++;
+  }
+  out->data = p;
+  out->size = size;
+  out->on_device = blk->on_device;
+  out->owned = 1;
+  out->owner = ctx;
+  out->block = blk;
   return NNSB_OK;
+}
+
+/* wraps a raw allocation of `ctx` (nnsb_dev_alloc / nnsb_pinned_alloc) into an owned memory */
+extern "C" int
+nnsb_memory_adopt (nnsb_ctx * ctx, void *ptr, size_t size, int on_device, nnsb_memory * out)
+{
+  if (!ctx || !ptr || !out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_adopt: null argument");
+  nnsb_block *blk = new (std::nothrow) nnsb_block ();
+  if (!blk)
+    return nnsb_set_error (NNSB_ENOMEM, "nnsb_memory_adopt: out of memory");
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    auto & live = on_device ? ctx->dev_live : ctx->pin_live;
+    auto it = live.find (ptr);
+    if (it == live.end ()) {
+      delete blk;
+      return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_adopt: %p was not allocated by this context", ptr);
+    }
+    it->second.is_block = true;
+    ctx->refs++;
+  }
+  blk->ctx = ctx;
+  blk->base = ptr;
+  blk->on_device = on_device ? 1 : 0;
+  blk->refs = 1;
+  blk->ready = nullptr;
+  memset (out, 0, sizeof (*out));
+  out->data = ptr;
+  out->size = size;
+  out->on_device = blk->on_device;
+  out->owned = 1;
+  out->owner = ctx;
+  out->block = blk;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_memory_ref (const nnsb_memory * mem, nnsb_memory * out)
+{
+  if (!mem || !out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_ref: null argument");
+  nnsb_memory m = *mem;
+  nnsb_block *blk = (nnsb_block *) mem->block;
+  if (blk) {
+    std::lock_guard<std::mutex> lk (blk->ctx->mu);
+    blk->refs++;
+    m.owned = 1;
+  } else {
+    m.owned = 0;                /* caller-managed memory: a plain view */
+  }
+  *out = m;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_memory_share (const nnsb_memory * mem, size_t offset, size_t size, nnsb_memory * out)
+{
+  if (!mem || !out)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_share: null argument");
+  if (offset > mem->size || size > mem->size - offset)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_share: [%zu, +%zu) is outside a memory of %zu bytes",
+        offset, size, mem->size);
+  int r = nnsb_memory_ref (mem, out);
+  if (r)
+    return r;
+  out->data = (char *) mem->data + offset;
+  out->size = size;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_memory_release (nnsb_memory * mem)
+{
+  if (!mem || !mem->data || !mem->owned)
+    return NNSB_OK;
+  nnsb_block *blk = (nnsb_block *) mem->block;
+  mem->data = nullptr;
+  mem->owned = 0;
+  mem->block = nullptr;
+  if (!blk)
+    return NNSB_OK;
+  nnsb_ctx *ctx = blk->ctx;
+  bool last;
+  {
+    std::lock_guard<std::mutex> lk (ctx->mu);
+    last = --blk->refs == 0;
+  }
+  if (!last)
+    return NNSB_OK;
+  int r;
+  if (blk->on_device) {
+    std::vector<nnsb_evt *> pending;
+    pending.swap (blk->uses);
+    if (blk->ready)
+      pending.push_back (blk->ready);
+    r = dev_give (ctx, blk->base, pending);
+  } else {
+    for (nnsb_evt * ev : blk->uses)
+      evt_unref (ev);
+    evt_unref (blk->ready);
+    r = pinned_give (ctx, blk->base);
+  }
+  delete blk;
+  ctx_unref (ctx);
+  return r;
+}
+
+extern "C" int
+nnsb_memory_wait (const nnsb_memory * mem, nnsb_stream * s)
+{
+  if (!mem || !s)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_wait: null argument");
+  nnsb_block *blk = (nnsb_block *) mem->block;
+  if (!blk)
+    return NNSB_OK;
+  nnsb_evt *ev;
+  {
+    std::lock_guard<std::mutex> lk (blk->ctx->mu);
+    ev = evt_ref (blk->ready);
+  }
+  if (!ev)
+    return NNSB_OK;
+  int r = NNSB_OK;
+  if (ev->stream != s->s) {
+    r = bind (s->ctx);
+    if (!r) {
+      cudaError_t e = cudaStreamWaitEvent (s->s, ev->e, 0);
+      if (e != cudaSuccess)
+        r = nnsb_set_error (NNSB_ECUDA, "cudaStreamWaitEvent failed: %s", cudaGetErrorString (e));
+    }
+  }
+  evt_unref (ev);
+  return r;
+}
+
+extern "C" int
+nnsb_memory_sync (const nnsb_memory * mem)
+{
+  if (!mem)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_sync: null argument");
+  nnsb_block *blk = (nnsb_block *) mem->block;
+  if (!blk)
+    return NNSB_OK;
+  nnsb_evt *ev;
+  {
+    std::lock_guard<std::mutex> lk (blk->ctx->mu);
+    ev = evt_ref (blk->ready);
+  }
+  if (!ev)
+    return NNSB_OK;
+  cudaError_t e = cudaEventSynchronize (ev->e);
+  evt_unref (ev);
+  if (e != cudaSuccess)
+    return nnsb_set_error (NNSB_ECUDA, "cudaEventSynchronize failed: %s", cudaGetErrorString (e));
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_memory_mark_io (nnsb_stream * s, nnsb_memory * outs, uint32_t n_out, const nnsb_memory * ins,
+    uint32_t n_in)
+{
+  if (!s || (n_out && !outs) || (n_in && !ins))
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_mark_io: null argument");
+  bool any = false;
+  for (uint32_t i = 0; i < n_out && !any; i++)
+    any = outs[i].block != nullptr;
+  for (uint32_t i = 0; i < n_in && !any; i++)
+    any = ins[i].block != nullptr;
+  if (!any)
+    return NNSB_OK;
+  int r = bind (s->ctx);
+  if (r)
+    return r;
+  nnsb_evt *ev = evt_record (s->ctx->device, s->s);
+  if (!ev) {
+    /* no event to be had: make everything true the slow way */
+    CUDA_TRY (cudaStreamSynchronize (s->s));
+    for (uint32_t i = 0; i < n_out; i++) {
+      nnsb_block *blk = (nnsb_block *) outs[i].block;
+      if (!blk)
+        continue;
+      std::lock_guard<std::mutex> lk (blk->ctx->mu);
+      evt_unref (blk->ready);
+      blk->ready = nullptr;
+    }
+    return NNSB_OK;
+  }
+  for (uint32_t i = 0; i < n_out; i++) {
+    nnsb_block *blk = (nnsb_block *) outs[i].block;
+    if (!blk)
+      continue;
+    std::lock_guard<std::mutex> lk (blk->ctx->mu);
+    if (blk->ready == ev)
+      continue;                 /* two views of one block */
+    evt_unref (blk->ready);
+    blk->ready = evt_ref (ev);
+  }
+  for (uint32_t i = 0; i < n_in; i++) {
+    nnsb_block *blk = (nnsb_block *) ins[i].block;
+    if (!blk)
+      continue;
+    std::lock_guard<std::mutex> lk (blk->ctx->mu);
+    bool placed = false;
+    for (auto & u : blk->uses) {
+      if (u == ev) {
+        placed = true;
+        break;
+      }
+      if (u->stream == ev->stream) {
+        /* a later point of the same stream covers the earlier one */
+        evt_unref (u);
+        u = evt_ref (ev);
+        placed = true;
+        break;
+      }
+    }
+    if (!placed)
+      blk->uses.push_back (evt_ref (ev));
+  }
+  evt_unref (ev);
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_memory_mark_ready (nnsb_memory * mem, nnsb_stream * s)
+{
+  return nnsb_memory_mark_io (s, mem, mem ? 1 : 0, nullptr, 0);
+}
+
+extern "C" int
+nnsb_memory_mark_use (const nnsb_memory * mem, nnsb_stream * s)
+{
+  return nnsb_memory_mark_io (s, nullptr, 0, mem, mem ? 1 : 0);
+}
+
+extern "C" int
+nnsb_memory_export (const nnsb_memory * mem, nnsb_device_view * view)
+{
+  if (!mem || !view)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_export: null argument");
+  if (!mem->on_device || !mem->data)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_memory_export: not a device memory");
+  memset (view, 0, sizeof (*view));
+  view->device_ptr = mem->data;
+  view->size = mem->size;
+  view->device_id = -1;
+  nnsb_block *blk = (nnsb_block *) mem->block;
+  if (blk) {
+    std::lock_guard<std::mutex> lk (blk->ctx->mu);
+    view->device_id = blk->ctx->device;
+    /* valid for as long as the caller holds its reference on the memory */
+    view->ready_event = blk->ready ? (void *) blk->ready->e : nullptr;
+  } else {
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes (&attr, mem->data) == cudaSuccess)
+      view->device_id = attr.device;
+    else
+      cudaGetLastError ();
+  }
+  return NNSB_OK;
+}
+
+extern "C" void *
+nnsb_stream_handle (nnsb_stream * s)
+{
+  return s ? (void *) s->s : nullptr;
 }
 
 #define STREAM_PROLOGUE(name) \

@@ -18,18 +18,64 @@ _CAPS_BUF = 4096
 
 
 class DeviceMemory:
-    """A device-resident GstMemory stand-in (pointer + size), optionally owned."""
+    """A device-resident GstMemory stand-in: a reference-counted, stream-ordered view of a pooled
+    block (or of caller-managed device memory)."""
 
     def __init__(self, mem):
         self.mem = mem
 
     @property
     def ptr(self):
+        """gst_memory_map: waits until the producer's kernels have finished, then the pointer."""
+        L.check(L.lib().nnsb_memory_sync(C.byref(self.mem)))
+        return self.mem.data
+
+    @property
+    def ptr_async(self):
+        """The pointer without waiting: only for work ordered after `wait(stream)`."""
         return self.mem.data
 
     @property
     def size(self):
         return self.mem.size
+
+    def wait(self, stream):
+        """Make `stream` (an nnsb_stream handle) wait on the GPU for the contents."""
+        L.check(L.lib().nnsb_memory_wait(C.byref(self.mem), stream))
+
+    def sync(self):
+        L.check(L.lib().nnsb_memory_sync(C.byref(self.mem)))
+
+    def mark_use(self, stream):
+        L.check(L.lib().nnsb_memory_mark_use(C.byref(self.mem), stream))
+
+    def mark_ready(self, stream):
+        L.check(L.lib().nnsb_memory_mark_ready(C.byref(self.mem), stream))
+
+    def ref(self):
+        out = L.Memory()
+        L.check(L.lib().nnsb_memory_ref(C.byref(self.mem), C.byref(out)))
+        return DeviceMemory(out)
+
+    def share(self, offset, size):
+        """gst_memory_share: a sub-range that keeps the block alive on its own."""
+        out = L.Memory()
+        L.check(L.lib().nnsb_memory_share(C.byref(self.mem), int(offset), int(size), C.byref(out)))
+        return DeviceMemory(out)
+
+    def export(self):
+        """(device pointer, size, device id, cudaEvent_t or None) for CUDA-aware consumers."""
+        v = L.DeviceView()
+        L.check(L.lib().nnsb_memory_export(C.byref(self.mem), C.byref(v)))
+        return v.device_ptr, v.size, v.device_id, v.ready_event
+
+    @property
+    def __cuda_array_interface__(self):
+        """uint8 view for torch / cupy (`torch.as_tensor(mem, device="cuda")`); the producer's event
+        is waited for here because the interface cannot carry one."""
+        self.sync()
+        return {"shape": (int(self.mem.size),), "typestr": "|u1", "data": (int(self.mem.data), False),
+                "version": 3, "strides": None}
 
     def release(self):
         L.lib().nnsb_memory_release(C.byref(self.mem))
@@ -42,6 +88,7 @@ def _host_memory(arr):
     m.on_device = 0
     m.owned = 0
     m.owner = None
+    m.block = None
     return m
 
 
@@ -52,6 +99,7 @@ def device_memory(ptr, size):
     m.on_device = 1
     m.owned = 0
     m.owner = None
+    m.block = None
     return DeviceMemory(m)
 
 
@@ -528,6 +576,217 @@ class TensorSplit:
             C.memmove(C.byref(o), C.byref(outs[i]), C.sizeof(L.Memory))
             mems.append(DeviceMemory(o))
         return flow, mems
+
+
+class TensorFilter:
+    """tensor_filter's transform with a CUDA-aware framework behind it: `invoke(inputs, outputs,
+    cuda_stream)` receives lists of (device pointer, size) and the raw cudaStream_t it must
+    enqueue its work on (no synchronisation inside); returns 0, >0 (drop) or <0 (error)."""
+
+    def __init__(self, invoke, in_config, out_config, device_id=0):
+        self._lib = L.lib()
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_filter_new(int(device_id), C.byref(self.handle)))
+        self._invoke = invoke
+
+        def trampoline(_priv, inp, n_in, outp, n_out, stream):
+            try:
+                ins = [(inp[i].data, inp[i].size) for i in range(n_in)]
+                outs = [(outp[i].data, outp[i].size) for i in range(n_out)]
+                return int(self._invoke(ins, outs, stream) or 0)
+            except Exception:                       # noqa: BLE001 -- must not unwind into C
+                import traceback
+                traceback.print_exc()
+                return -1
+
+        self._cb = L.FILTER_INVOKE(trampoline)      # keep the thunk alive
+        L.check(self._lib.nnsb_filter_set_framework(self.handle, self._cb, None))
+        L.check(self._lib.nnsb_filter_set_info(self.handle, C.byref(in_config), C.byref(out_config)))
+
+    @staticmethod
+    def make_config(infos, rate=(0, 1)):
+        """infos: list of (type name, dim list)."""
+        cfg = L.TensorsConfig()
+        cfg.num_tensors = len(infos)
+        for i, (t, d) in enumerate(infos):
+            cfg.info[i] = L.make_info(t, d)
+        cfg.rate_n, cfg.rate_d = rate
+        return cfg
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_filter_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def transform(self, memories):
+        n = len(memories)
+        ins = (L.Memory * max(1, n))()
+        keep = []
+        for i, m in enumerate(memories):
+            if isinstance(m, DeviceMemory):
+                ins[i] = m.mem
+            else:
+                a = np.ascontiguousarray(m)
+                keep.append(a)
+                ins[i] = _host_memory(a)
+        outs = (L.Memory * L.SIZE_LIMIT)()
+        n_out = C.c_uint32(0)
+        flow = self._lib.nnsb_filter_transform(self.handle, ins, n, outs, C.byref(n_out))
+        res = []
+        for i in range(n_out.value):
+            o = L.Memory()
+            C.memmove(C.byref(o), C.byref(outs[i]), C.sizeof(L.Memory))
+            res.append(DeviceMemory(o))
+        return flow, res
+
+    @property
+    def counters(self):
+        """(bytes uploaded, bytes downloaded, invoke calls) by this element so far."""
+        a, b, c = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        L.check(self._lib.nnsb_filter_copy_counters(self.handle, C.byref(a), C.byref(b), C.byref(c)))
+        return int(a.value), int(b.value), int(c.value)
+
+
+def _as_memory_array(memories):
+    n = len(memories)
+    ins = (L.Memory * max(1, n))()
+    keep = []
+    for i, m in enumerate(memories):
+        if isinstance(m, DeviceMemory):
+            ins[i] = m.mem
+        else:
+            a = np.ascontiguousarray(m)
+            keep.append(a)
+            ins[i] = _host_memory(a)
+    return ins, keep
+
+
+def _wrap_out(m):
+    """An output memory of mux / demux: device -> DeviceMemory, host view -> the ctypes Memory."""
+    o = L.Memory()
+    C.memmove(C.byref(o), C.byref(m), C.sizeof(L.Memory))
+    return DeviceMemory(o) if o.on_device else o
+
+
+class TensorMux:
+    """tensor_mux: the memories of all sink pads, in pad order, become one other/tensors buffer
+    (references, nothing is copied)."""
+
+    def __init__(self, **props):
+        self._lib = L.lib()
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_mux_new(C.byref(self.handle)))
+        for k, v in props.items():
+            self.set_property(k.replace("_", "-"), v)
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_mux_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_property(self, name, value):
+        if isinstance(value, bool):
+            value = "true" if value else "false"
+        L.check(self._lib.nnsb_mux_set_property(self.handle, name.encode(), str(value).encode()))
+
+    def get_property(self, name):
+        buf = C.create_string_buffer(256)
+        code = self._lib.nnsb_mux_get_property(self.handle, name.encode(), buf, 256)
+        if code == L.ENOENT:
+            return None
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def set_caps(self, caps_list):
+        arr = (C.c_char_p * len(caps_list))(*[c.encode() for c in caps_list])
+        buf = C.create_string_buffer(_CAPS_BUF)
+        code = self._lib.nnsb_mux_set_caps(self.handle, len(caps_list), arr, buf, _CAPS_BUF)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def chain(self, memories):
+        ins, _keep = _as_memory_array(memories)
+        outs = (L.Memory * L.SIZE_LIMIT)()
+        n_out = C.c_uint32(0)
+        flow = self._lib.nnsb_mux_chain(self.handle, ins, len(memories), outs, C.byref(n_out))
+        return flow, [_wrap_out(outs[i]) for i in range(n_out.value)]
+
+
+class TensorDemux:
+    """tensor_demux: `tensorpick` groups -> one list of memory references per source pad."""
+
+    def __init__(self, **props):
+        self._lib = L.lib()
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_demux_new(C.byref(self.handle)))
+        for k, v in props.items():
+            self.set_property(k.replace("_", "-"), v)
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_demux_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_property(self, name, value):
+        if isinstance(value, bool):
+            value = "true" if value else "false"
+        L.check(self._lib.nnsb_demux_set_property(self.handle, name.encode(), str(value).encode()))
+
+    def get_property(self, name):
+        buf = C.create_string_buffer(1024)
+        code = self._lib.nnsb_demux_get_property(self.handle, name.encode(), buf, 1024)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def set_caps(self, caps):
+        L.check(self._lib.nnsb_demux_set_caps(self.handle, caps.encode()))
+
+    @property
+    def num_outputs(self):
+        return self._lib.nnsb_demux_num_outputs(self.handle)
+
+    def out_caps(self, idx):
+        buf = C.create_string_buffer(_CAPS_BUF)
+        code = self._lib.nnsb_demux_get_out_caps(self.handle, int(idx), buf, _CAPS_BUF)
+        if code < 0:
+            L.check(code)
+        return buf.value.decode()
+
+    def chain(self, memories):
+        """Returns (flow, [[memories of src_0], [memories of src_1], ...])."""
+        ins, _keep = _as_memory_array(memories)
+        room = 64
+        outs = (L.Memory * room)()
+        counts = (C.c_uint32 * L.SIZE_LIMIT)()
+        n_src = C.c_uint32(0)
+        flow = self._lib.nnsb_demux_chain(self.handle, ins, len(memories), outs, room, counts,
+                                          L.SIZE_LIMIT, C.byref(n_src))
+        pads, k = [], 0
+        for i in range(n_src.value):
+            pads.append([_wrap_out(outs[k + j]) for j in range(counts[i])])
+            k += counts[i]
+        return flow, pads
 
 
 class BatchQueue:

@@ -44,6 +44,18 @@ def sum_over_ranks(value, dist, device="cpu"):
     return float(t.item())
 
 
+def gather_over_ranks(values, dist, device="cpu"):
+    """All-gather of a short list of floats: returns one list per rank, in rank order."""
+    vals = [float(v) for v in values]
+    if dist is None:
+        return [vals]
+    import torch
+    t = torch.tensor(vals, dtype=torch.float64, device=device)
+    outs = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(outs, t)
+    return [[float(x) for x in o.tolist()] for o in outs]
+
+
 def aggregate_throughput(units_per_rank, seconds_this_rank, dist, device="cpu"):
     """Whole-job throughput: all units processed by all ranks / slowest rank's time."""
     total_units = sum_over_ranks(units_per_rank, dist, device)

@@ -105,6 +105,66 @@ def test_cfg4_stand_1080p_batch16_per_frame(dev, port, option, per_channel):
     assert np.all(np.abs(y[:FRAME].astype(np.float64) - w) <= 1e-6 * np.abs(w) + 1e-6)
 
 
+def _stand_close_chunked(got, want, scale, chunk=1 << 24):
+    """|gpu - reference| <= 1e-6 |reference| + 1e-6 scale, without a float64 copy of 400 M values."""
+    worst = 0.0
+    for a in range(0, got.size, chunk):
+        g = got[a:a + chunk].astype(np.float64)
+        w = want[a:a + chunk].astype(np.float64)
+        err = np.abs(g - w) - (1e-6 * np.abs(w) + 1e-6 * scale)
+        worst = max(worst, float(err.max()))
+    assert worst <= 0.0, "beyond tolerance by %g" % worst
+
+
+def _cfg4_frames(batch, seed):
+    """`batch` 1080p float32 frames whose offset and spread differ from frame to frame, so
+    statistics taken over the wrong range (one frame instead of all, or the reverse) show up."""
+    rng = np.random.default_rng(seed)
+    x = rng.random(FRAME * batch, dtype=np.float32)
+    x = x.reshape(batch, FRAME)
+    x *= np.linspace(1.0, 30.0, batch, dtype=np.float32)[:, None]
+    x += np.linspace(-5.0, 50.0, batch, dtype=np.float32)[:, None]
+    return x.reshape(-1)
+
+
+@pytest.mark.parametrize("option,mode,per_channel", [("default", "default", False),
+                                                     ("dc-average,per-channel:true", "dc-average", True)])
+def test_cfg4_stand_1080p_batch64_per_frame_vs_reference(dev, port, option, mode, per_channel):
+    """configs[3] at its stated size: 64 queued 1080p f32 frames in one set of launches; every
+    frame against the CPU reference's sequential loops (tensor_data.c:314-493)."""
+    B = 64
+    x = _cfg4_frames(B, 41)
+    plan = dev.plan("stand", option, "float32", [C, W, H, 1])
+    y = plan.run_host(x, batch=B)
+    plan.close()
+    for f in range(B):
+        want = port.stand(x[f * FRAME:(f + 1) * FRAME], [C, W, H, 1], mode, None, per_channel)
+        _stand_close_chunked(y[f * FRAME:(f + 1) * FRAME], want, 60.0 if mode == "dc-average" else 1.0)
+
+
+@pytest.mark.parametrize("option,mode,per_channel", [
+    ("default", "default", False), ("default,per-channel:true", "default", True),
+    ("dc-average", "dc-average", False), ("dc-average,per-channel:true", "dc-average", True)])
+def test_cfg4_stand_one_tensor_3_1920_1080_64_vs_reference(dev, port, option, mode, per_channel):
+    """The reference's own semantics for a batched tensor: ONE tensor 3:1920:1080:64, statistics
+    over all 398 M elements (per channel: 133 M each) -- where a one-pass variance would drift."""
+    B = 64
+    dim = [C, W, H, B]
+    x = _cfg4_frames(B, 43)
+    plan = dev.plan("stand", option, "float32", dim)
+    y = plan.run_host(x)
+    nch = 3 if per_channel else 1
+    mean, std = plan.stand_stats(1, nch)
+    plan.close()
+    omean, ostd = port.stand_stats(x, dim, per_channel)
+    # the reference's running mean over 4e8 terms carries its own rounding (random walk ~1e-12)
+    np.testing.assert_allclose(mean, omean, rtol=1e-9)
+    if mode == "default":
+        np.testing.assert_allclose(std, ostd, rtol=1e-9)
+    want = port.stand(x, dim, mode, None, per_channel)
+    _stand_close_chunked(y, want, 100.0 if mode == "dc-average" else 1.0)
+
+
 def test_cfg5_chain_converter_typecast_arith_transpose(dev, port):
     """configs[4], one stream: 1918x1080 RGB (padded rows) -> converter -> typecast -> arithmetic
     -> transpose, all on the device; equals the oracle chain on the same frame."""

@@ -25,6 +25,7 @@ def test_stream_assignment_is_a_partition():
 def test_reductions_without_a_process_group():
     assert sharding.max_over_ranks(1.5, None) == 1.5
     assert sharding.aggregate_throughput(32, 0.5, None) == 64.0
+    assert sharding.gather_over_ranks([3, 4.5], None) == [[3.0, 4.5]]
 
 
 def _worker(rank, world, port, q):
@@ -38,6 +39,8 @@ def _worker(rank, world, port, q):
         seconds = 0.010 * (rank + 1)
         slowest = sharding.max_over_ranks(seconds, dist)
         agg = sharding.aggregate_throughput(len(mine) * 32, seconds, dist)
+        gathered = sharding.gather_over_ranks([rank, seconds], dist)
+        assert gathered == [[0.0, 0.010], [1.0, 0.020]]
         sharding.barrier(dist)
         q.put((rank, mine, slowest, agg))
     finally:
