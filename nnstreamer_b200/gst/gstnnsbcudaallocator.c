@@ -5,10 +5,18 @@
  * (gsttensor_transform.c:1758) and follows the precedent of tensor_allocator.c:101-128 (an
  * allocator wrapper installed by the element).  Tensors stay resident on the device between
  * chained CUDA-aware elements: such a peer recognises the memory by its type string
- * (GST_NNSB_CUDA_MEMORY_TYPE) and takes the device pointer with gst_nnsb_cuda_memory_get().
- * Any other element simply maps the memory: mem_map then copies device -> pinned host once,
- * mem_unmap after a WRITE map copies back.  NOT compiled in this repository's image (no
- * GStreamer); see README.md in this directory.
+ * (GST_NNSB_CUDA_MEMORY_TYPE) and takes the device view with gst_nnsb_cuda_memory_get() -- the
+ * view carries the block whose "ready" event the peer's stream waits on, so nothing
+ * synchronises with the host.  Any other element simply maps the memory: mem_map waits for
+ * the producer, copies device -> pinned host once; mem_unmap after a WRITE map copies back.
+ *
+ * Life time: every GstMemory holds its own reference on the device block (nnsb_memory_ref /
+ * nnsb_memory_share), the block keeps its context alive, and the allocator has a context and a
+ * stream of its own -- so a memory that is still held downstream when the element that
+ * produced it is finalized stays valid.
+ *
+ * Not compiled in this repository's image (no GStreamer): `make syntax` in this directory
+ * checks it against declaration stubs; see README.md.
  */
 #include <string.h>
 #include "gstnnsbcudaallocator.h"
@@ -16,7 +24,8 @@
 typedef struct _GstNnsbCudaAllocator
 {
   GstAllocator parent;
-  nnsb_transform *owner;        /* element whose context/pools back the memories */
+  nnsb_ctx *ctx;                /* pools for memories allocated through gst_allocator_alloc */
+  nnsb_stream *stream;          /* copy stream of mem_map / mem_unmap */
 } GstNnsbCudaAllocator;
 
 typedef struct _GstNnsbCudaAllocatorClass
@@ -26,6 +35,7 @@ typedef struct _GstNnsbCudaAllocatorClass
 
 G_DEFINE_TYPE (GstNnsbCudaAllocator, gst_nnsb_cuda_allocator, GST_TYPE_ALLOCATOR);
 
+/* takes over the reference held by `dev` */
 static GstMemory *
 _new_memory (GstAllocator * allocator, GstMemory * parent, const nnsb_memory * dev, gsize maxsize,
     gsize offset, gsize size)
@@ -33,8 +43,7 @@ _new_memory (GstAllocator * allocator, GstMemory * parent, const nnsb_memory * d
   GstNnsbCudaMemory *m = g_new0 (GstNnsbCudaMemory, 1);
   gst_memory_init (GST_MEMORY_CAST (m), 0, allocator, parent, maxsize, 255, offset, size);
   m->dev = *dev;
-  if (parent)
-    m->dev.owned = 0;           /* sub-memories borrow the root's block */
+  memset (&m->host, 0, sizeof (m->host));
   g_mutex_init (&m->lock);
   return GST_MEMORY_CAST (m);
 }
@@ -44,7 +53,8 @@ _alloc (GstAllocator * allocator, gsize size, GstAllocationParams * params)
 {
   GstNnsbCudaAllocator *self = (GstNnsbCudaAllocator *) allocator;
   nnsb_memory dev;
-  if (nnsb_transform_alloc (self->owner, size, 1, &dev) != NNSB_OK) {
+  (void) params;
+  if (nnsb_memory_alloc (self->ctx, size, 1, self->stream, &dev) != NNSB_OK) {
     GST_ERROR_OBJECT (allocator, "device allocation of %" G_GSIZE_FORMAT " bytes failed: %s", size,
         nnsb_last_error ());
     return NULL;
@@ -56,11 +66,9 @@ static void
 _free (GstAllocator * allocator, GstMemory * mem)
 {
   GstNnsbCudaMemory *m = (GstNnsbCudaMemory *) mem;
-  if (m->host) {
-    nnsb_memory h = { m->host, mem->maxsize, 0, 1, m->dev.owner };
-    nnsb_memory_release (&h);
-  }
-  nnsb_memory_release (&m->dev);        /* no-op for sub-memories (owned == 0) */
+  (void) allocator;
+  nnsb_memory_release (&m->host);
+  nnsb_memory_release (&m->dev);        /* the block returns to its pool with the last reference */
   g_mutex_clear (&m->lock);
   g_free (m);
 }
@@ -72,21 +80,24 @@ _map (GstMemory * mem, gsize maxsize, GstMapFlags flags)
   GstNnsbCudaMemory *m = (GstNnsbCudaMemory *) mem;
   GstNnsbCudaAllocator *self = (GstNnsbCudaAllocator *) mem->allocator;
   gpointer ret = NULL;
+  (void) maxsize;
   g_mutex_lock (&m->lock);
-  if (!m->host) {
-    nnsb_memory h;
-    if (nnsb_transform_alloc (self->owner, mem->maxsize, 0, &h) == NNSB_OK)
-      m->host = h.data;
-  }
-  if (m->host) {
+  if (!m->host.data)
+    nnsb_memory_alloc (self->ctx, m->dev.size, 0, NULL, &m->host);
+  if (m->host.data) {
+    gboolean ok = TRUE;
     if (!m->host_valid && (flags & GST_MAP_READ)) {
-      /* device -> pinned host, stream-ordered then synchronised */
-      if (nnsb_transform_download (self->owner, m->host, &m->dev) == NNSB_OK)
-        m->host_valid = TRUE;
+      /* wait (on the GPU) for the producer, device -> pinned host, then wait for the copy */
+      ok = nnsb_memory_wait (&m->dev, self->stream) == NNSB_OK
+          && nnsb_d2h_async (self->stream, m->host.data, m->dev.data, m->dev.size) == NNSB_OK
+          && nnsb_stream_sync (self->stream) == NNSB_OK;
+      m->host_valid = ok;
     }
-    if (flags & GST_MAP_WRITE)
-      m->host_dirty = TRUE;
-    ret = m->host;
+    if (ok) {
+      if (flags & GST_MAP_WRITE)
+        m->host_dirty = TRUE;
+      ret = m->host.data;
+    }
   }
   g_mutex_unlock (&m->lock);
   return ret;
@@ -99,7 +110,12 @@ _unmap (GstMemory * mem)
   GstNnsbCudaAllocator *self = (GstNnsbCudaAllocator *) mem->allocator;
   g_mutex_lock (&m->lock);
   if (m->host_dirty) {
-    nnsb_transform_upload (self->owner, &m->dev, m->host);
+    /* the upload is stream-ordered: the block is "ready" again once it has landed, and the
+     * pinned source must not change until then -- wait here, a WRITE map is the slow path */
+    if (nnsb_memory_wait (&m->dev, self->stream) == NNSB_OK
+        && nnsb_h2d_async (self->stream, m->dev.data, m->host.data, m->dev.size) == NNSB_OK)
+      nnsb_memory_mark_ready (&m->dev, self->stream);
+    nnsb_stream_sync (self->stream);
     m->host_dirty = FALSE;
     m->host_valid = TRUE;
   }
@@ -113,12 +129,24 @@ _share (GstMemory * mem, gssize offset, gssize size)
 {
   GstNnsbCudaMemory *m = (GstNnsbCudaMemory *) mem;
   GstMemory *parent = mem->parent ? mem->parent : mem;
-  nnsb_memory dev = m->dev;
+  nnsb_memory dev;
   if (size == -1)
-    size = mem->size - offset;
-  dev.data = (char *) m->dev.data + offset;
-  dev.size = size;
-  return _new_memory (mem->allocator, parent, &dev, mem->maxsize, mem->offset + offset, size);
+    size = (gssize) mem->size - offset;
+  if (nnsb_memory_share (&m->dev, (size_t) offset, (size_t) size, &dev) != NNSB_OK)
+    return NULL;
+  return _new_memory (mem->allocator, parent, &dev, mem->maxsize, mem->offset + (gsize) offset,
+      (gsize) size);
+}
+
+static void
+_finalize (GObject * object)
+{
+  GstNnsbCudaAllocator *self = (GstNnsbCudaAllocator *) object;
+  if (self->stream)
+    nnsb_stream_destroy (self->stream);
+  if (self->ctx)
+    nnsb_ctx_destroy (self->ctx);
+  G_OBJECT_CLASS (gst_nnsb_cuda_allocator_parent_class)->finalize (object);
 }
 
 static void
@@ -127,6 +155,7 @@ gst_nnsb_cuda_allocator_class_init (GstNnsbCudaAllocatorClass * klass)
   GstAllocatorClass *ac = GST_ALLOCATOR_CLASS (klass);
   ac->alloc = _alloc;
   ac->free = _free;
+  G_OBJECT_CLASS (klass)->finalize = _finalize;
 }
 
 static void
@@ -141,10 +170,15 @@ gst_nnsb_cuda_allocator_init (GstNnsbCudaAllocator * self)
 }
 
 GstAllocator *
-gst_nnsb_cuda_allocator_new (nnsb_transform * owner)
+gst_nnsb_cuda_allocator_new (int device_id)
 {
   GstNnsbCudaAllocator *self = g_object_new (gst_nnsb_cuda_allocator_get_type (), NULL);
-  self->owner = owner;
+  if (nnsb_ctx_create (device_id, &self->ctx) != NNSB_OK
+      || nnsb_stream_create (self->ctx, &self->stream) != NNSB_OK) {
+    GST_ERROR_OBJECT (self, "no usable GPU %d: %s", device_id, nnsb_last_error ());
+    gst_object_unref (self);
+    return NULL;
+  }
   return GST_ALLOCATOR_CAST (self);
 }
 
@@ -166,6 +200,6 @@ gst_nnsb_cuda_memory_get (GstMemory * mem, nnsb_memory * out)
   if (!gst_is_nnsb_cuda_memory (mem))
     return FALSE;
   *out = ((GstNnsbCudaMemory *) mem)->dev;
-  out->owned = 0;
+  out->owned = 0;               /* borrowed: the GstMemory keeps the reference */
   return TRUE;
 }

@@ -5,8 +5,10 @@
  * (gst/nnstreamer/elements/gsttensor_transform.c:128-280); every vfunc forwards to the element
  * mirror of include/nnstreamer_b200.h, which holds the option grammar, the caps logic and the
  * CUDA kernels.  Caps cross the boundary as strings (gst_caps_to_string / _from_string).
- * NOT compiled in this repository's image (no GStreamer); see README.md in this directory.
+ * Not compiled in this repository's image (no GStreamer): `make syntax` in this directory checks
+ * it against declaration stubs; see README.md.
  */
+#include <stdlib.h>
 #include <string.h>
 #include <gst/gst.h>
 #include <gst/base/gstbasetransform.h>
@@ -21,7 +23,8 @@ typedef struct _GstTensorTransformB200
 {
   GstBaseTransform element;
   nnsb_transform *core;
-  GstAllocator *cuda_alloc;
+  GstAllocator *cuda_alloc;     /* created at the first buffer, on the GPU `device-id` names */
+  int device_id;
 } GstTensorTransformB200;
 
 typedef struct _GstTensorTransformB200Class
@@ -30,7 +33,7 @@ typedef struct _GstTensorTransformB200Class
 } GstTensorTransformB200Class;
 
 enum { PROP_0, PROP_SILENT, PROP_MODE, PROP_OPTION, PROP_ACCELERATION, PROP_APPLY,
-  PROP_TRANSPOSE_RANK_LIMIT, PROP_DEVICE_ID };
+  PROP_TRANSPOSE_RANK_LIMIT };
 
 GST_DEBUG_CATEGORY_STATIC (gst_tensor_transform_debug);
 #define GST_CAT_DEFAULT gst_tensor_transform_debug
@@ -172,6 +175,7 @@ static gboolean
 transform_size (GstBaseTransform * trans, GstPadDirection direction, GstCaps * caps, gsize size,
     GstCaps * othercaps, gsize * othersize)
 {
+  (void) trans; (void) direction; (void) caps; (void) size; (void) othercaps;
   *othersize = 0;               /* memories are appended in transform(), :2169-2186 */
   return TRUE;
 }
@@ -198,6 +202,11 @@ transform (GstBaseTransform * trans, GstBuffer * inbuf, GstBuffer * outbuf)
 
   if (n > NNSB_SIZE_LIMIT)
     return GST_FLOW_ERROR;
+  if (!self->cuda_alloc) {
+    self->cuda_alloc = gst_nnsb_cuda_allocator_new (self->device_id);
+    if (!self->cuda_alloc)
+      return GST_FLOW_ERROR;
+  }
   for (i = 0; i < n; i++) {
     GstMemory *mem = gst_buffer_peek_memory (inbuf, i);
     if (gst_nnsb_cuda_memory_get (mem, &in[i]))
@@ -207,21 +216,28 @@ transform (GstBaseTransform * trans, GstBuffer * inbuf, GstBuffer * outbuf)
       goto done;
     }
     mapped[i] = TRUE;
+    memset (&in[i], 0, sizeof (in[i]));
     in[i].data = maps[i].data;
     in[i].size = maps[i].size;
-    in[i].on_device = 0;
-    in[i].owned = 0;
-    in[i].owner = NULL;
   }
   flow = nnsb_transform_transform (self->core, in, n, out, &n_out);
   if (flow == NNSB_FLOW_OK) {
     for (i = 0; i < n_out; i++) {
       GstMemory *mem;
-      if (!out[i].owned) {
-        /* tensor not selected by `apply`: share the input memory (:1716) */
-        mem = gst_memory_ref (gst_buffer_peek_memory (inbuf, i));
-      } else if (out[i].on_device) {
+      if (out[i].on_device) {
+        /* a transformed tensor, or -- for a tensor `apply` skipped -- another reference to the
+         * input's device block (:1716); either way the new GstMemory takes the reference over */
         mem = gst_nnsb_cuda_memory_wrap (self->cuda_alloc, &out[i]);
+      } else if (!out[i].owned) {
+        /* host tensor not selected by `apply`: a view into the mapped input.  With one memory
+         * per tensor that is a ref of memory i; when one input blob carried several tensors it
+         * is a share of the blob at the tensor's offset (nnstreamer_plugin_api_impl.c:534) */
+        if (n == 1 && n_out > 1) {
+          const gssize off = (const char *) out[i].data - (const char *) in[0].data;
+          mem = gst_memory_share (gst_buffer_peek_memory (inbuf, 0), off, (gssize) out[i].size);
+        } else {
+          mem = gst_memory_ref (gst_buffer_peek_memory (inbuf, i));
+        }
       } else {
         nnsb_memory *keep = g_new (nnsb_memory, 1);
         *keep = out[i];
@@ -295,16 +311,22 @@ gst_tensor_transform_b200_class_init (GstTensorTransformB200Class * klass)
 static void
 gst_tensor_transform_b200_init (GstTensorTransformB200 * self)
 {
-  nnsb_transform_new (0, &self->core);
-  self->cuda_alloc = gst_nnsb_cuda_allocator_new (self->core);
+  const char *dev = getenv ("NNSB_DEVICE_ID");  /* one pipeline branch per GPU */
+  self->device_id = dev ? atoi (dev) : 0;
+  self->cuda_alloc = NULL;
+  nnsb_transform_new (self->device_id, &self->core);
 }
+
+GType gst_tensor_converter_b200_get_type (void);  /* gsttensor_converter_b200.c */
 
 static gboolean
 plugin_init (GstPlugin * plugin)
 {
-  /* same element name and rank as registerer/nnstreamer.c:80-86,109 */
+  /* same element names and rank as registerer/nnstreamer.c:80-86,109 */
   return gst_element_register (plugin, "tensor_transform", GST_RANK_NONE,
-      gst_tensor_transform_b200_get_type ());
+      gst_tensor_transform_b200_get_type ())
+      && gst_element_register (plugin, "tensor_converter", GST_RANK_NONE,
+      gst_tensor_converter_b200_get_type ());
 }
 
 #ifndef PACKAGE
