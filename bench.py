@@ -868,6 +868,31 @@ def run_b200(args):
     e2e_per_rank = [v[0] / args.steps for v in
                     sharding.gather_over_ranks([ms_e2e_rank], dist, reduce_device)]
 
+    # ---- the same step with a PAGEABLE source (an upstream GstMemory is malloc'd memory): the
+    #      element stages it through its pinned ring with helper threads ----
+    pageable = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        x_page = np.array(h_in)                         # ordinary numpy allocation
+        ins_p = (L.Memory * 1)()
+        ins_p[0].data = x_page.ctypes.data
+        ins_p[0].size = n
+        outs_p = (L.Memory * L.SIZE_LIMIT)()
+
+        def page_step():
+            if elem.transform_raw(ins_p, 1, outs_p, n_out) != 0:
+                raise RuntimeError("transform (pageable) failed: %s" % L.lib().nnsb_last_error())
+            L.lib().nnsb_memory_release(C.byref(outs_p[0]))
+
+        page_step()
+        psteps = max(3, min(args.steps, 10))
+        t0 = time.perf_counter()
+        for _ in range(psteps):
+            page_step()
+        ms_page = (time.perf_counter() - t0) * 1e3 / psteps
+        pageable = {"frames/s": B / (ms_page * 1e-3), "ms_per_step": ms_page,
+                    "frac_of_pinned_source_e2e": (ms_e2e_rank / args.steps) / ms_page,
+                    "staging": "4 pinned slots, 2 helper threads (NNSB_STAGING_THREADS)"}
+
     # ---- what the host link gives every rank at the same time: the ceiling of e2e ----
     h_out, h_out_ptr = dev.pinned(4 * n, np.uint8)
     link_steps = max(3, min(args.steps, 10))
@@ -908,6 +933,7 @@ def run_b200(args):
                 extras.update(extra_kernels(dev, peak, with_cpu=with_cpu))
                 extras["chain_8_streams_1080p_python_threads"] = python_stream_chain(local_rank)
                 extras["mobilenet_224_per_frame_element_e2e"] = per_frame_mobilenet(dev, local_rank, with_cpu)
+                extras["e2e_pageable_source"] = pageable
 
     if rank == 0:
         ms_step = ms_dev / args.steps

@@ -1,0 +1,490 @@
+/*
+ * k_stand_fused.cu -- stand (standardisation) of a BATCH of float32 tensors with ONE read of
+ * the input from HBM: a persistent, warp-specialised kernel that keeps each tensor resident in
+ * shared memory between its statistics pass and its normalisation pass.
+ *
+ * Reference semantics: gst_tensor_transform_stand (gsttensor_transform.c:1512-1619) +
+ * gst_tensor_data_raw_average / _std [_per_channel] (tensor_data.c:314-493), see k_stand.cuh.
+ *
+ * Why: the three-launch scheme (k_stand.cuh) reads the input twice -- 12 B of DRAM traffic per
+ * element for 8 algorithmic bytes -- and is therefore capped at 2/3 of the HBM roof.  A 1080p
+ * RGB float32 frame is 24.9 MB; split over the 148 SMs that is 168 KB per SM, which FITS in the
+ * 227 KB of shared memory of one CTA.  So:
+ *
+ *   grid    one CTA per SM, launched cooperatively (all CTAs must be co-resident: they wait for
+ *           one another); CTA b owns the same slice of every tensor of the batch: tiles
+ *           [first_b, first_b + n_b) of TILE = 3072 elements (12 KB; a multiple of 1..4 channels
+ *           and of the thread strides below, so a thread's channel phase never changes).
+ *   ring    NSLOT = 18 tile slots of shared memory, one `full` and one `empty` mbarrier each.
+ *   warp 0  (producer) one elected thread issues cp.async.bulk global -> shared for the tiles of
+ *           tensor f, f+1, ... in order as slots become empty, and -- LOOKAHEAD tiles ahead -- a
+ *           cp.async.bulk.prefetch.L2 so that HBM keeps streaming into L2 while the ring is
+ *           full (during the cross-CTA hand-shake below); L2 is the second buffer.
+ *   6 warps (statistics) read every tile once as it lands: fp64 sum (x - K) and sum (x - K)^2
+ *           per channel, K = first element of the channel (same shifted one-pass formula as
+ *           k_stand.cuh).  After the last tile of tensor f: block reduction, the CTA's partial
+ *           goes to global scratch, a release-store of a flag publishes it; every CTA then
+ *           acquires all flags, folds the 148 partials in a fixed order (all CTAs compute the
+ *           same bits) -> {mean, 1/std} into shared memory -> arrive on `ready[f & 1]`.
+ *   12 warps (normalisation) wait for `ready`, read the tiles of tensor f from shared memory
+ *           again, fp64 (x - mean) * (1 / std), |.|, convert, 128-bit stores to global, and free
+ *           the slot (arrive on `empty`): the producer refills it with tensor f+1.
+ *
+ * DRAM traffic: one read + one write = the algorithmic 8 B/element.  The statistics warps run
+ * one tensor ahead of the normalisation warps, so the only serial gap per tensor is the flag
+ * hand-shake (~1.5 us), during which the L2 prefetch keeps HBM busy.
+ *
+ * Restrictions (else the three-launch path is used, nnsb_runtime.cu): float32 in and out,
+ * 1..4 channels, frame_elems % 4 == 0, 16-byte aligned bases, 4 <= tiles per CTA <= NSLOT - 2.
+ * Summation order differs from k_stand.cuh (tiles instead of a grid-stride), so results agree
+ * with it within stand's tolerance, not bit for bit; the normalisation arithmetic is identical.
+ */
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+
+#include "nnsb_device.cuh"
+#include "nnsb_kernels.h"
+
+namespace nnsb {
+
+namespace {
+
+constexpr int TILE = 3072;                      /* elements per tile */
+constexpr int TILE_BYTES = TILE * 4;
+constexpr int TILE_VECS = TILE / 4;             /* float4 per tile: 768 */
+constexpr int NSLOT = 18;
+constexpr int STATS_WARPS = 6, APPLY_WARPS = 12;
+constexpr int STATS_THREADS = STATS_WARPS * 32;         /* 192: 4 vectors per tile and thread */
+constexpr int APPLY_THREADS = APPLY_WARPS * 32;         /* 384: 2 vectors per tile and thread */
+constexpr int THREADS = 32 + STATS_THREADS + APPLY_THREADS;
+constexpr int MAX_CTAS = 160;
+constexpr int PUB_SLOTS = 4;                    /* scratch slots cycled by tensor index */
+constexpr int LOOKAHEAD = 16;                   /* tiles the L2 prefetch runs ahead of the ring */
+
+__device__ __forceinline__ uint32_t smem_u32 (const void *p)
+{
+  return (uint32_t) __cvta_generic_to_shared (p);
+}
+__device__ __forceinline__ void mbar_init (uint64_t *bar, uint32_t count)
+{
+  asm volatile ("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r" (smem_u32 (bar)), "r" (count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx (uint64_t *bar, uint32_t bytes)
+{
+  asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+      :: "r" (smem_u32 (bar)), "r" (bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive (uint64_t *bar)
+{
+  asm volatile ("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r" (smem_u32 (bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait (uint64_t *bar, uint32_t parity)
+{
+  const uint32_t addr = smem_u32 (bar);
+  uint32_t done;
+  do {
+    asm volatile (
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r" (done) : "r" (addr), "r" (parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void bulk_g2s (void *smem_dst, const void *gmem_src, uint32_t bytes,
+    uint64_t *bar)
+{
+  asm volatile ("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      :: "r" (smem_u32 (smem_dst)), "l" (gmem_src), "r" (bytes), "r" (smem_u32 (bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_prefetch_l2 (const void *gmem_src, uint32_t bytes)
+{
+  asm volatile ("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l" (gmem_src), "r" (bytes) : "memory");
+}
+__device__ __forceinline__ void st_release_u32 (uint32_t *p, uint32_t v)
+{
+  asm volatile ("st.release.gpu.global.u32 [%0], %1;" :: "l" (p), "r" (v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_u32 (const uint32_t *p)
+{
+  uint32_t v;
+  asm volatile ("ld.acquire.gpu.global.u32 %0, [%1];" : "=r" (v) : "l" (p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void named_barrier (int id, int threads)
+{
+  asm volatile ("bar.sync %0, %1;" :: "r" (id), "r" (threads) : "memory");
+}
+
+struct FusedArgs
+{
+  const float *in;
+  float *out;
+  uint64_t frame_elems;
+  uint32_t batch;
+  uint32_t n_tiles;             /* tiles per tensor (the last one may be short) */
+  uint32_t tiles_lo, n_hi;      /* CTAs [0, n_hi) own tiles_lo + 1 tiles, the others tiles_lo */
+  uint32_t *flags;              /* [PUB_SLOTS][gridDim.x], zero on entry */
+  double *partial;              /* [PUB_SLOTS][gridDim.x][4][2] */
+  double *stats;                /* [batch][nch][2] = {mean, std}, for nnsb_plan_stand_stats */
+  int default_mode;
+};
+
+struct __align__ (16) Shared
+{
+  uint64_t full[NSLOT], empty[NSLOT];
+  uint64_t ready[2];            /* {mean, 1/std} of tensor f is in ms[f & 1] */
+  double ms[2][4][2];           /* mean, 1/std per channel */
+  double red[2][4][STATS_WARPS];
+  double fold[2][4][MAX_CTAS];
+};
+
+template <int NCH>
+__global__ void __launch_bounds__ (THREADS, 1)
+stand_fused_kernel (FusedArgs a)
+{
+  extern __shared__ __align__ (128) unsigned char smem_raw[];
+  float *ring = reinterpret_cast<float *> (smem_raw);
+  Shared &sh = *reinterpret_cast<Shared *> (smem_raw + (size_t) NSLOT * TILE_BYTES);
+
+  const uint32_t cta = blockIdx.x, n_cta = gridDim.x;
+  const uint32_t my_tiles = a.tiles_lo + (cta < a.n_hi ? 1u : 0u);
+  const uint32_t first_tile = cta * a.tiles_lo + (cta < a.n_hi ? cta : a.n_hi);
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NSLOT; s++) {
+      mbar_init (&sh.full[s], 1);
+      mbar_init (&sh.empty[s], APPLY_WARPS);
+    }
+    mbar_init (&sh.ready[0], 1);
+    mbar_init (&sh.ready[1], 1);
+    asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads ();
+
+  /* elements of tile t of a tensor */
+  auto tile_elems = [&] (uint32_t t) -> uint32_t {
+    const uint64_t start = (uint64_t) t * TILE;
+    const uint64_t left = a.frame_elems - start;
+    return left < (uint64_t) TILE ? (uint32_t) left : (uint32_t) TILE;
+  };
+
+  if (warp == 0) {
+    /* ------------------------------ producer ------------------------------ */
+    if (lane == 0 && my_tiles) {
+      const uint64_t total = (uint64_t) a.batch * my_tiles;     /* tiles this CTA moves */
+      uint64_t pf = 0;                                          /* next tile to prefetch into L2 */
+      for (uint64_t q = 0; q < total; q++) {
+        /* keep the L2 prefetch LOOKAHEAD tiles ahead of the shared-memory loads */
+        const uint64_t pf_end = q + LOOKAHEAD < total ? q + LOOKAHEAD : total;
+        if (pf < q)
+          pf = q;
+        for (; pf < pf_end; pf++) {
+          const uint32_t f = (uint32_t) (pf / my_tiles), j = (uint32_t) (pf % my_tiles);
+          const uint32_t t = first_tile + j;
+          bulk_prefetch_l2 (a.in + (uint64_t) f * a.frame_elems + (uint64_t) t * TILE, tile_elems (t) * 4);
+        }
+        const uint32_t s = (uint32_t) (q % NSLOT);
+        const uint32_t round = (uint32_t) (q / NSLOT);
+        if (round)
+          mbar_wait (&sh.empty[s], (round - 1) & 1);
+        const uint32_t f = (uint32_t) (q / my_tiles), j = (uint32_t) (q % my_tiles);
+        const uint32_t t = first_tile + j;
+        const uint32_t bytes = tile_elems (t) * 4;
+        mbar_expect_tx (&sh.full[s], bytes);
+        bulk_g2s (ring + (size_t) s * TILE, a.in + (uint64_t) f * a.frame_elems + (uint64_t) t * TILE,
+            bytes, &sh.full[s]);
+      }
+    }
+    return;
+  }
+
+  if (warp <= STATS_WARPS) {
+    /* ------------------------------ statistics ------------------------------ */
+    const uint32_t tid = threadIdx.x - 32;                      /* 0..191 */
+    const uint32_t swarp = tid >> 5;
+    /* vector v = tid + i * 192 of a tile: its lane k belongs to channel (c0 + k) % NCH; 192 and
+     * TILE are multiples of 3 and 4, so c0 depends on the thread only */
+    const uint32_t c0 = (tid * 4) % NCH;
+    for (uint32_t f = 0; f < a.batch; f++) {
+      const float *base = a.in + (uint64_t) f * a.frame_elems;
+      double kk[NCH], a1[NCH], a2[NCH];
+#pragma unroll
+      for (int r = 0; r < NCH; r++) {
+        kk[r] = (double) __ldg (base + (c0 + r) % NCH);
+        a1[r] = 0.0;
+        a2[r] = 0.0;
+      }
+      for (uint32_t j = 0; j < my_tiles; j++) {
+        const uint64_t q = (uint64_t) f * my_tiles + j;
+        const uint32_t s = (uint32_t) (q % NSLOT);
+        mbar_wait (&sh.full[s], (uint32_t) (q / NSLOT) & 1);
+        const float4 *tile = reinterpret_cast<const float4 *> (ring + (size_t) s * TILE);
+        const uint32_t nv = tile_elems (first_tile + j) / 4;
+        float4 x[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const uint32_t v = tid + i * STATS_THREADS;
+          x[i] = v < nv ? tile[v] : make_float4 (0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const uint32_t v = tid + i * STATS_THREADS;
+          if (v < nv) {
+            const float e[4] = { x[i].x, x[i].y, x[i].z, x[i].w };
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+              const double d = __dsub_rn ((double) e[k], kk[k % NCH]);
+              a1[k % NCH] += d;
+              a2[k % NCH] = fma (d, d, a2[k % NCH]);
+            }
+          }
+        }
+      }
+      /* actual-channel order, then a fixed-order block reduction */
+#pragma unroll
+      for (int c = 0; c < NCH; c++) {
+        double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+        for (int r = 0; r < NCH; r++)
+          if ((c0 + r) % NCH == (uint32_t) c) {
+            s1 = a1[r];
+            s2 = a2[r];
+          }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          s1 += __shfl_xor_sync (0xffffffffu, s1, o);
+          s2 += __shfl_xor_sync (0xffffffffu, s2, o);
+        }
+        if (lane == 0) {
+          sh.red[0][c][swarp] = s1;
+          sh.red[1][c][swarp] = s2;
+        }
+      }
+      named_barrier (1, STATS_THREADS);
+      const uint32_t pub = f % PUB_SLOTS;
+      if (tid < NCH) {
+        double t1 = 0.0, t2 = 0.0;
+#pragma unroll
+        for (int w = 0; w < STATS_WARPS; w++) {
+          t1 += sh.red[0][tid][w];
+          t2 += sh.red[1][tid][w];
+        }
+        double *p = a.partial + (((size_t) pub * n_cta + cta) * 4 + tid) * 2;
+        p[0] = t1;
+        p[1] = t2;
+        __threadfence ();
+      }
+      named_barrier (1, STATS_THREADS);
+      if (tid == 0)
+        st_release_u32 (a.flags + (size_t) pub * n_cta + cta, f + 1);
+      /* gather: thread i waits for CTA i, then pulls its partial into shared memory */
+      for (uint32_t i = tid; i < n_cta; i += STATS_THREADS) {
+        const uint32_t *fl = a.flags + (size_t) pub * n_cta + i;
+        while (ld_acquire_u32 (fl) != f + 1)
+          __nanosleep (20);
+        const double *p = a.partial + (((size_t) pub * n_cta + i) * 4) * 2;
+#pragma unroll
+        for (int c = 0; c < NCH; c++) {
+          sh.fold[0][c][i] = __ldcg (p + c * 2);
+          sh.fold[1][c][i] = __ldcg (p + c * 2 + 1);
+        }
+      }
+      named_barrier (1, STATS_THREADS);
+      if (tid < NCH) {
+        /* every CTA folds the same numbers in the same order: identical statistics everywhere */
+        double s1 = 0.0, s2 = 0.0;
+        for (uint32_t i = 0; i < n_cta; i++) {
+          s1 += sh.fold[0][tid][i];
+          s2 += sh.fold[1][tid][i];
+        }
+        const double n = (double) (a.frame_elems / NCH);
+        const double k0 = (double) __ldg (base + tid);
+        const double mean = k0 + s1 / n;
+        double sd = 0.0;
+        if (a.default_mode) {
+          const double var = (s2 - s1 * (s1 / n)) / n;
+          /* tensor_data.c:438,488: std = (sum != 0) ? sqrt (sum) : 1e-10 */
+          sd = (var > 0.0) ? sqrt (var) : 1e-10;
+        }
+        /* ms[f & 1] was last read by the normalisation of tensor f - 2, which finished before
+         * the slots of tensor f could be filled */
+        sh.ms[f & 1][tid][0] = mean;
+        sh.ms[f & 1][tid][1] = a.default_mode ? __drcp_rn (sd) : 0.0;
+        if (cta == 0) {
+          a.stats[((size_t) f * NCH + tid) * 2 + 0] = mean;
+          a.stats[((size_t) f * NCH + tid) * 2 + 1] = sd;
+        }
+      }
+      named_barrier (1, STATS_THREADS);
+      if (tid == 0)
+        mbar_arrive (&sh.ready[f & 1]);
+    }
+    return;
+  }
+
+  /* ------------------------------ normalisation ------------------------------ */
+  {
+    const uint32_t tid = threadIdx.x - 32 - STATS_THREADS;      /* 0..383 */
+    const uint32_t c0 = (tid * 4) % NCH;                        /* 384 is a multiple of 3 and 4 too */
+    for (uint32_t f = 0; f < a.batch; f++) {
+      mbar_wait (&sh.ready[f & 1], (f >> 1) & 1);
+      double mean[NCH], rsd[NCH];
+#pragma unroll
+      for (int r = 0; r < NCH; r++) {
+        mean[r] = sh.ms[f & 1][(c0 + r) % NCH][0];
+        rsd[r] = sh.ms[f & 1][(c0 + r) % NCH][1];
+      }
+      float *obase = a.out + (uint64_t) f * a.frame_elems;
+      for (uint32_t j = 0; j < my_tiles; j++) {
+        const uint64_t q = (uint64_t) f * my_tiles + j;
+        const uint32_t s = (uint32_t) (q % NSLOT);
+        const float4 *tile = reinterpret_cast<const float4 *> (ring + (size_t) s * TILE);
+        const uint32_t t = first_tile + j;
+        const uint32_t nv = tile_elems (t) / 4;
+        float4 *dst = reinterpret_cast<float4 *> (obase + (uint64_t) t * TILE);
+        float4 x[2];
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+          const uint32_t v = tid + i * APPLY_THREADS;
+          x[i] = v < nv ? tile[v] : make_float4 (0.f, 0.f, 0.f, 0.f);
+        }
+        /* the values are in registers: the slot can be refilled while we compute and store */
+        __syncwarp ();
+        if (lane == 0)
+          mbar_arrive (&sh.empty[s]);
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+          const uint32_t v = tid + i * APPLY_THREADS;
+          if (v < nv) {
+            const float e[4] = { x[i].x, x[i].y, x[i].z, x[i].w };
+            float y[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+              const double d = __dsub_rn ((double) e[k], mean[k % NCH]);
+              y[k] = a.default_mode ? (float) fabs (__dmul_rn (d, rsd[k % NCH])) : (float) d;
+            }
+            uint32_t w[4] = { __float_as_uint (y[0]), __float_as_uint (y[1]), __float_as_uint (y[2]),
+              __float_as_uint (y[3]) };
+            asm volatile ("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+                :: "l" (dst + v), "r" (w[0]), "r" (w[1]), "r" (w[2]), "r" (w[3]) : "memory");
+          }
+        }
+      }
+    }
+  }
+}
+
+size_t
+shared_bytes ()
+{
+  return (size_t) NSLOT * TILE_BYTES + sizeof (Shared);
+}
+
+struct Geometry
+{
+  uint32_t n_tiles, grid, tiles_lo, n_hi;
+};
+
+bool
+geometry (size_t frame_elems, const LaunchCfg &cfg, Geometry *g)
+{
+  if (cfg.sm_count < 1 || cfg.sm_count > MAX_CTAS)
+    return false;
+  const uint64_t n_tiles = (frame_elems + TILE - 1) / TILE;
+  uint64_t grid = (uint64_t) cfg.sm_count;
+  if (n_tiles < grid * 4)
+    return false;               /* too little work per CTA: the hand-shake would dominate */
+  const uint64_t lo = n_tiles / grid, hi = n_tiles % grid;
+  if (lo + (hi ? 1 : 0) > (uint64_t) NSLOT - 2)
+    return false;               /* the slice must fit in the ring with two slots to spare */
+  g->n_tiles = (uint32_t) n_tiles;
+  g->grid = (uint32_t) grid;
+  g->tiles_lo = (uint32_t) lo;
+  g->n_hi = (uint32_t) hi;
+  return true;
+}
+
+template <int NCH> int
+launch_n (const FusedArgs &args, uint32_t grid, cudaStream_t stream)
+{
+  static int configured[64];
+  int dev = 0;
+  cudaGetDevice (&dev);
+  const size_t smem = shared_bytes ();
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute (stand_fused_kernel<NCH>,
+        cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    if (e != cudaSuccess)
+      return (int) e;
+    configured[dev] = 1;
+  }
+  FusedArgs a = args;
+  void *params[] = { &a };
+  return (int) cudaLaunchCooperativeKernel ((const void *) stand_fused_kernel<NCH>, dim3 (grid),
+      dim3 (THREADS), params, smem, stream);
+}
+
+}  // namespace
+
+bool
+stand_fused_supported (int in_type, int out_type, const void *in, const void *out, size_t frame_elems,
+    uint32_t nch, uint32_t batch, const LaunchCfg &cfg)
+{
+  Geometry g;
+  if (in_type != NNSB_FLOAT32 || out_type != NNSB_FLOAT32)
+    return false;
+  if (nch < 1 || nch > 4 || batch < 2 || frame_elems % 4 != 0 || frame_elems % nch != 0)
+    return false;
+  if (((uintptr_t) in | (uintptr_t) out) & 15)
+    return false;
+  return geometry (frame_elems, cfg, &g);
+}
+
+size_t
+stand_fused_scratch_bytes (const LaunchCfg &cfg)
+{
+  /* flags, then partials (256-byte aligned) */
+  const size_t flags = ((size_t) PUB_SLOTS * cfg.sm_count * sizeof (uint32_t) + 255) / 256 * 256;
+  return flags + (size_t) PUB_SLOTS * cfg.sm_count * 4 * 2 * sizeof (double);
+}
+
+int
+launch_stand_fused (int stand_mode, const void *in, void *out, size_t frame_elems, uint32_t nch,
+    uint32_t batch, void *scratch, double *stats, const LaunchCfg &cfg, cudaStream_t stream,
+    int *n_launches)
+{
+  Geometry g;
+  if (!geometry (frame_elems, cfg, &g))
+    return (int) cudaErrorInvalidValue;
+  const size_t flag_bytes = ((size_t) PUB_SLOTS * cfg.sm_count * sizeof (uint32_t) + 255) / 256 * 256;
+  cudaError_t e = cudaMemsetAsync (scratch, 0, flag_bytes, stream);
+  if (e != cudaSuccess)
+    return (int) e;
+  FusedArgs a;
+  a.in = (const float *) in;
+  a.out = (float *) out;
+  a.frame_elems = frame_elems;
+  a.batch = batch;
+  a.n_tiles = g.n_tiles;
+  a.tiles_lo = g.tiles_lo;
+  a.n_hi = g.n_hi;
+  a.flags = (uint32_t *) scratch;
+  a.partial = (double *) ((char *) scratch + flag_bytes);
+  a.stats = stats;
+  a.default_mode = stand_mode == NNSB_STAND_DEFAULT;
+  int err;
+  switch (nch) {
+    case 1: err = launch_n<1> (a, g.grid, stream); break;
+    case 2: err = launch_n<2> (a, g.grid, stream); break;
+    case 3: err = launch_n<3> (a, g.grid, stream); break;
+    case 4: err = launch_n<4> (a, g.grid, stream); break;
+    default: err = (int) cudaErrorInvalidValue; break;
+  }
+  if (n_launches)
+    *n_launches = 1;
+  return err;
+}
+
+}  // namespace nnsb

@@ -10,11 +10,14 @@
  * Same property names / value strings, same caps strings, same flow-return conventions; each
  * function cites the reference lines it follows.
  */
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "nnsb_caps.h"
@@ -156,12 +159,17 @@ ensure_device (nnsb_transform * t)
   int r = nnsb_ctx_create (t->device_id, &t->ctx);
   if (r)
     return r;
-  for (int i = 0; i < 2 && !r; i++) {
-    r = nnsb_stream_create (t->ctx, &t->stream[i]);
-    if (!r)
-      r = nnsb_event_create (t->ctx, &t->ev[i]);
-  }
-  return r;
+  /* device-resident buffers need one stream; the second one (host-buffer path: chunks alternate
+   * between two streams) is created on first use -- idle streams still occupy connections */
+  return nnsb_stream_create (t->ctx, &t->stream[0]);
+}
+
+static int
+ensure_second_stream (nnsb_transform * t)
+{
+  if (t->stream[1])
+    return NNSB_OK;
+  return nnsb_stream_create (t->ctx, &t->stream[1]);
 }
 
 extern "C" int
@@ -478,10 +486,131 @@ plan_for (nnsb_transform * t, unsigned idx, const nnsb_tensor_info * in_info)
   return s.plan;
 }
 
+/* Pinned staging for PAGEABLE host inputs (north_star: "pinned-host staging with
+ * cudaMemcpyAsync").  An upstream GstMemory is ordinary malloc'd memory: cudaMemcpyAsync from it
+ * is staged by the driver and blocks the caller, so the H2D || kernel || D2H pipeline below
+ * would collapse into a sequence.  Instead helper threads memcpy chunk k+1.. of the source into
+ * a small ring of pinned slots while the copy engine moves chunk k; a slot is refilled only
+ * after the H2D that read it has completed (one event per slot). */
+struct Stager
+{
+  static const int RING = 4;
+  nnsb_ctx *ctx = nullptr;
+  const char *src = nullptr;
+  size_t total = 0, chunk = 0, n_chunks = 0;
+  void *slot[RING] = { nullptr, nullptr, nullptr, nullptr };
+  nnsb_event *ev[RING] = { nullptr, nullptr, nullptr, nullptr };
+  std::mutex mu;
+  std::condition_variable cv;
+  std::vector<char> staged;             /* chunk k sits in slot k % RING */
+  size_t issued = 0;                    /* chunks whose H2D has been queued (event recorded) */
+  bool abort = false;
+  std::vector<std::thread> workers;
+
+  size_t bytes_of (size_t k) const { return (k + 1) * chunk <= total ? chunk : total - k * chunk; }
+
+  void work (size_t first, size_t step)
+  {
+    for (size_t k = first; k < n_chunks; k += step) {
+      if (k >= RING) {
+        /* the H2D of chunk k - RING read this slot: wait until it has been queued, then done */
+        {
+          std::unique_lock<std::mutex> lk (mu);
+          cv.wait (lk, [&] { return abort || issued > k - RING; });
+          if (abort)
+            return;
+        }
+        if (nnsb_event_sync (ev[k % RING]) != NNSB_OK) {
+          std::lock_guard<std::mutex> lk (mu);
+          abort = true;
+          cv.notify_all ();
+          return;
+        }
+      }
+      memcpy (slot[k % RING], src + k * chunk, bytes_of (k));
+      {
+        std::lock_guard<std::mutex> lk (mu);
+        staged[k] = 1;
+      }
+      cv.notify_all ();
+    }
+  }
+
+  int start (nnsb_ctx * c, const char *source, size_t total_bytes, size_t chunk_bytes)
+  {
+    ctx = c;
+    src = source;
+    total = total_bytes;
+    chunk = chunk_bytes;
+    n_chunks = (total + chunk - 1) / chunk;
+    staged.assign (n_chunks, 0);
+    for (int i = 0; i < RING; i++) {
+      int r = nnsb_pinned_alloc (ctx, chunk, &slot[i]);
+      if (!r)
+        r = nnsb_event_create (ctx, &ev[i]);
+      if (r)
+        return r;
+    }
+    size_t n_threads = 2;
+    const char *env = getenv ("NNSB_STAGING_THREADS");
+    if (env && atoi (env) > 0)
+      n_threads = (size_t) atoi (env);
+    if (n_threads > RING)
+      n_threads = RING;
+    if (n_threads > n_chunks)
+      n_threads = n_chunks;
+    for (size_t i = 0; i < n_threads; i++)
+      workers.emplace_back (&Stager::work, this, i, n_threads);
+    return NNSB_OK;
+  }
+
+  /* blocks until chunk k is in its slot; nullptr after a failure */
+  const void *wait_chunk (size_t k)
+  {
+    std::unique_lock<std::mutex> lk (mu);
+    cv.wait (lk, [&] { return abort || staged[k]; });
+    return abort ? nullptr : slot[k % RING];
+  }
+
+  /* the H2D of chunk k has just been queued on `s` */
+  int chunk_issued (size_t k, nnsb_stream * s)
+  {
+    int r = nnsb_event_record (ev[k % RING], s);
+    std::lock_guard<std::mutex> lk (mu);
+    if (r)
+      abort = true;
+    issued = k + 1;
+    cv.notify_all ();
+    return r;
+  }
+
+  void finish (bool failed)
+  {
+    {
+      std::lock_guard<std::mutex> lk (mu);
+      if (failed)
+        abort = true;
+    }
+    cv.notify_all ();
+    for (auto & w : workers)
+      w.join ();
+    workers.clear ();
+    for (int i = 0; i < RING; i++) {
+      if (ev[i])
+        nnsb_event_destroy (ev[i]);
+      if (slot[i])
+        nnsb_pinned_free (ctx, slot[i]);
+      ev[i] = nullptr;
+      slot[i] = nullptr;
+    }
+  }
+};
+
 /* One tensor whose input and output live in host memory: upload, transform, download.
  * Element-wise modes are split into chunks handled alternately by two streams, so the H2D
  * copy of chunk k+1, the kernel of chunk k and the D2H copy of chunk k-1 overlap (PCIe is
- * full duplex: wall time ~ max (H2D, D2H) instead of their sum). */
+ * full duplex: wall time ~ max (H2D, D2H) instead of their sum).  A pageable source goes
+ * through the pinned staging ring above. */
 static int
 run_host_tensor (nnsb_transform * t, nnsb_plan * plan, const char *h_in, char *h_out)
 {
@@ -501,19 +630,36 @@ run_host_tensor (nnsb_transform * t, nnsb_plan * plan, const char *h_in, char *h
   const uint64_t n = es_out ? out_size / es_out : 0;
   const size_t es_in = n ? in_size / n : 1;
   const size_t pipeline_min = 8u << 20;
+  /* small tensors: the driver's own staging of a pageable source is as good as ours */
+  const bool stage = in_size >= (4u << 20) && !nnsb_host_is_pinned (h_in);
+  Stager stager;
 
-  if (nnsb_plan_is_elementwise (plan) && in_size + out_size >= pipeline_min) {
+  if (nnsb_plan_is_elementwise (plan) && in_size + out_size >= pipeline_min
+      && ensure_second_stream (t) == NNSB_OK) {
     const uint64_t g = nnsb_plan_chunk_granule (plan);
     /* ~16 chunks, each a multiple of the granule, at least 1 MiB of traffic */
     uint64_t chunk = (n / 16 + g - 1) / g * g;
     const uint64_t min_chunk = ((1u << 20) / (es_in + es_out) + g - 1) / g * g;
     if (chunk < min_chunk)
       chunk = min_chunk;
+    if (stage)
+      r = stager.start (t->ctx, h_in, in_size, chunk * es_in);
     int k = 0;
-    for (uint64_t first = 0; first < n && !r; first += chunk, k ^= 1) {
+    size_t ci = 0;
+    for (uint64_t first = 0; first < n && !r; first += chunk, k ^= 1, ci++) {
       const uint64_t cnt = (n - first < chunk) ? n - first : chunk;
       nnsb_stream *s = t->stream[k];
-      r = nnsb_h2d_async (s, (char *) d_in + first * es_in, h_in + first * es_in, cnt * es_in);
+      const void *src = h_in + first * es_in;
+      if (stage) {
+        src = stager.wait_chunk (ci);
+        if (!src) {
+          r = nnsb_set_error (NNSB_ECUDA, "tensor_transform: staging of a pageable input failed");
+          break;
+        }
+      }
+      r = nnsb_h2d_async (s, (char *) d_in + first * es_in, src, cnt * es_in);
+      if (!r && stage)
+        r = stager.chunk_issued (ci, s);
       if (!r)
         r = nnsb_plan_launch_elems (plan, d_in, d_out, first, cnt, s);
       if (!r)
@@ -526,7 +672,22 @@ run_host_tensor (nnsb_transform * t, nnsb_plan * plan, const char *h_in, char *h
       r = r2 ? r2 : r3;
   } else {
     nnsb_stream *s = t->stream[0];
-    r = nnsb_h2d_async (s, d_in, h_in, in_size);
+    if (stage) {
+      const size_t piece = 4u << 20;
+      r = stager.start (t->ctx, h_in, in_size, piece);
+      for (size_t ci = 0; ci * piece < in_size && !r; ci++) {
+        const void *src = stager.wait_chunk (ci);
+        if (!src) {
+          r = nnsb_set_error (NNSB_ECUDA, "tensor_transform: staging of a pageable input failed");
+          break;
+        }
+        r = nnsb_h2d_async (s, (char *) d_in + ci * piece, src, stager.bytes_of (ci));
+        if (!r)
+          r = stager.chunk_issued (ci, s);
+      }
+    } else {
+      r = nnsb_h2d_async (s, d_in, h_in, in_size);
+    }
     if (!r)
       r = nnsb_plan_launch (plan, d_in, d_out, 1, s);
     if (!r) {
@@ -537,6 +698,8 @@ run_host_tensor (nnsb_transform * t, nnsb_plan * plan, const char *h_in, char *h
     if (!r)
       r = r2;
   }
+  if (stage)
+    stager.finish (r != NNSB_OK);
   nnsb_dev_free (t->ctx, d_in);
   nnsb_dev_free (t->ctx, d_out);
   return r;

@@ -58,6 +58,17 @@ int launch_stand (int in_type, int out_type, int stand_mode, const void *in, voi
     size_t frame_elems, uint32_t nch, uint32_t batch, double *scratch, double *stats,
     const LaunchCfg & cfg, cudaStream_t stream, int *n_launches);
 
+/* Single-read stand for batches of float32 tensors whose per-SM slice fits in shared memory
+ * (k_stand_fused.cu): one cooperative, persistent launch instead of three.  `scratch`:
+ * stand_fused_scratch_bytes() of device memory (contents undefined); `stats`: batch * nch * 2
+ * doubles {mean, std}. */
+bool stand_fused_supported (int in_type, int out_type, const void *in, const void *out,
+    size_t frame_elems, uint32_t nch, uint32_t batch, const LaunchCfg &cfg);
+size_t stand_fused_scratch_bytes (const LaunchCfg &cfg);
+int launch_stand_fused (int stand_mode, const void *in, void *out, size_t frame_elems, uint32_t nch,
+    uint32_t batch, void *scratch, double *stats, const LaunchCfg &cfg, cudaStream_t stream,
+    int *n_launches);
+
 /* K3/K4: rank-N permutation copy (transpose :1443, dimchg :1120).
  * out index (innermost first) i has extent size[i] and input stride in_stride[i] (elements
  * of es bytes); the output is dense.  `batch` tensors of frame_elems elements each. */

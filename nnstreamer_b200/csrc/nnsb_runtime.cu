@@ -115,6 +115,8 @@ struct nnsb_plan
   size_t scratch_doubles;
   double *d_stats;
   size_t stats_doubles;
+  int no_fused;                 /* NNSB_STAND_NO_FUSED: always the three-launch scheme */
+  int stand_fused_used;         /* the last launch took the single-read kernel */
   int last_launches;
 };
 
@@ -230,9 +232,21 @@ evt_satisfied (nnsb_evt * ev, bool have_stream, cudaStream_t stream)
 /* ------------------------------------------------------------------------------------- */
 /* context / stream / event                                                                */
 /* ------------------------------------------------------------------------------------- */
+/* Elements own their streams, and a pipeline of a few branches easily has more of them than the
+ * 8 hardware connections CUDA opens by default; streams that share a connection wait for each
+ * other's event waits.  Ask for 32 unless the user chose a number (read when the CUDA context
+ * is created, so this must run before the process's first CUDA call to have any effect). */
+static void
+prefer_more_connections ()
+{
+  static std::once_flag once;
+  std::call_once (once, [] { setenv ("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); });
+}
+
 extern "C" int
 nnsb_device_count (int *count)
 {
+  prefer_more_connections ();
   if (!count)
     return nnsb_set_error (NNSB_EINVAL, "nnsb_device_count: null argument");
   *count = 0;
@@ -246,6 +260,7 @@ nnsb_ctx_create (int device_id, nnsb_ctx ** out)
   if (!out)
     return nnsb_set_error (NNSB_EINVAL, "nnsb_ctx_create: null argument");
   *out = nullptr;
+  prefer_more_connections ();
   int count = 0;
   CUDA_TRY (cudaGetDeviceCount (&count));
   if (device_id < 0 || device_id >= count)
@@ -525,10 +540,14 @@ nnsb_event_destroy (nnsb_event * e)
 /* ------------------------------------------------------------------------------------- */
 /* memory                                                                                  */
 /* ------------------------------------------------------------------------------------- */
-/* How many blocks of one size a context may obtain from cudaMalloc before it starts reusing
- * blocks whose last GPU work is still in flight (the pool then makes the new user's stream
- * wait for that work; the host never blocks).  Three blocks let producer, consumer and the
- * next frame overlap. */
+/* How many blocks of one size a context may obtain from cudaMalloc before an allocation has to
+ * wait for a block whose last GPU work is still in flight.  That wait is taken on the HOST
+ * (cudaEventSynchronize on the oldest block's events): it is the back-pressure of the pipeline.
+ * Without it a producer thread runs arbitrarily far ahead of the GPU, and deep queues on more
+ * streams than the device has hardware connections serialise behind each other (measured:
+ * 8 x 4 elements queued 300 frames deep ran at 13 k frames/s; bounded to three frames in flight
+ * per element the same chain is HBM-bound).  Three blocks let producer, consumer and the next
+ * frame overlap. */
 static const int POOL_DEPTH_BEFORE_WAIT = 3;
 
 /* Takes a device block of `bucket` bytes.  have_stream: the block will first be touched by
@@ -569,12 +588,8 @@ dev_take (nnsb_ctx * ctx, size_t b, bool have_stream, cudaStream_t stream, void 
   }
   if (p) {
     for (nnsb_evt * ev : must_wait) {
-      if (have_stream) {
-        if (ev->stream != stream)
-          cudaStreamWaitEvent (stream, ev->e, 0);
-      } else {
-        cudaEventSynchronize (ev->e);
-      }
+      if (!(have_stream && ev->stream == stream))
+        cudaEventSynchronize (ev->e);           /* back-pressure: see POOL_DEPTH_BEFORE_WAIT */
       evt_unref (ev);
     }
     *out = p;
@@ -1062,6 +1077,20 @@ nnsb_memory_export (const nnsb_memory * mem, nnsb_device_view * view)
   return NNSB_OK;
 }
 
+/* 1 when `p` is page-locked (or managed) memory the copy engine can read directly, 0 when it is
+ * ordinary pageable memory: cudaMemcpyAsync from such a source is staged by the driver and
+ * blocks the calling thread */
+extern "C" int
+nnsb_host_is_pinned (const void *p)
+{
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes (&attr, p) != cudaSuccess) {
+    cudaGetLastError ();
+    return 0;
+  }
+  return attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged;
+}
+
 extern "C" void *
 nnsb_stream_handle (nnsb_stream * s)
 {
@@ -1297,6 +1326,7 @@ nnsb_plan_create (nnsb_ctx * ctx, const nnsb_option * opt, const nnsb_tensor_inf
         return nnsb_set_error (NNSB_EINVAL, "stand: cannot identify mode");
       }
       plan->stand_nch = opt->stand_per_channel ? in_info->dim[0] : 1;
+      plan->no_fused = getenv ("NNSB_STAND_NO_FUSED") != nullptr;
       break;
     case NNSB_MODE_CLAMP:
       break;
@@ -1449,7 +1479,8 @@ nnsb_plan_describe (const nnsb_plan * plan, char *buf, size_t buflen)
           (int) plan->chain.desc.nch, plan->chain.fast_f32 ? ", float32 fast path" : "");
       break;
     case NNSB_MODE_STAND:
-      len = snprintf (buf, buflen, "stand: %u channel(s)", plan->stand_nch);
+      len = snprintf (buf, buflen, "stand: %u channel(s)%s", plan->stand_nch,
+          plan->stand_fused_used ? ", single-read fused kernel" : "");
       break;
     case NNSB_MODE_CLAMP:
       len = snprintf (buf, buflen, "clamp");
@@ -1520,6 +1551,24 @@ nnsb_plan_launch (nnsb_plan * plan, const void *d_in, void *d_out, uint32_t batc
       break;
     case NNSB_MODE_STAND:
     {
+      if (!plan->no_fused && stand_fused_supported (plan->in_info.type, plan->out_info.type, d_in,
+              d_out, plan->frame_elems, plan->stand_nch, batch, cfg)) {
+        /* batches of float32 frames that fit the SMs' shared memory: one read of the input */
+        r = grow (plan->ctx, &plan->d_scratch, &plan->scratch_doubles,
+            (stand_fused_scratch_bytes (cfg) + 7) / 8);
+        if (r)
+          return r;
+        r = grow (plan->ctx, &plan->d_stats, &plan->stats_doubles, (size_t) batch * plan->stand_nch * 2);
+        if (r)
+          return r;
+        int nl = 0;
+        err = launch_stand_fused (plan->opt.stand_mode, d_in, d_out, plan->frame_elems,
+            plan->stand_nch, batch, plan->d_scratch, plan->d_stats, cfg, s->s, &nl);
+        plan->last_launches = nl;
+        plan->stand_fused_used = 1;
+        break;
+      }
+      plan->stand_fused_used = 0;
       const size_t need_scratch = stand_scratch_doubles (batch, plan->stand_nch,
           plan->frame_elems, cfg);
       const size_t need_stats = (size_t) batch * plan->stand_nch * 2;

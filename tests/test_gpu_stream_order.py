@@ -125,12 +125,14 @@ def test_steady_state_reuses_pooled_blocks(dev):
     t = TensorTransform(mode="typecast", option="float32")
     t.negotiate(caps_for(dim, "uint8"))
     src = upload(t, np.random.default_rng(1).integers(0, 256, n, dtype=np.uint8))
-    for _ in range(20):
+    last = None
+    for _ in range(50):                              # same pattern as below: the pool reaches its depth
         flow, (y,) = t.transform([src])
-        y.release()
+        if last is not None:
+            last.release()
+        last = y
     torch.cuda.synchronize()
     before = torch.cuda.mem_get_info(0)[0]
-    last = None
     for _ in range(3000):
         flow, (y,) = t.transform([src])
         if last is not None:
@@ -200,6 +202,35 @@ def test_converter_frames_per_tensor_changed_mid_batch(dev, port):
     assert dev.download(out.ptr, out.size, np.uint8).tobytes() == np.concatenate([dense[4], dense[7]]).tobytes()
     out.release()
     conv.close()
+
+
+def test_pageable_host_inputs_go_through_the_pinned_staging_ring(dev, port):
+    """An upstream GstMemory is ordinary malloc'd memory.  24.9 MB tensors from pageable numpy
+    arrays: the element-wise path (chunks on two streams, staged by helper threads) and a
+    permutation (whole-tensor upload through the ring), both against the CPU reference; twice, so
+    that recycled staging slots and events are exercised, and with an odd-sized tail."""
+    dim = [3, 1920, 1080, 4]
+    n = int(np.prod(dim))
+    rng = np.random.default_rng(21)
+    t = TensorTransform(mode="arithmetic", option="typecast:float32,per-channel:true@0,add:-1@0,div:3@1,mul:2@2")
+    t.negotiate(caps_for(dim, "uint8"))
+    ops = [("typecast", "float32"), ("add", -1, 0), ("div", 3, 1), ("mul", 2, 2)]
+    for _ in range(2):
+        x = rng.integers(0, 256, n, dtype=np.uint8)          # pageable
+        flow, (y,) = t.transform([x])
+        assert flow == 0
+        assert bits_equal(y.view(np.float32), port.arithmetic(x, dim, ops, True, 0))
+    t.close()
+    dim = [3, 1283, 1009, 2]                                 # 7.7 MB, not a multiple of the 4 MiB pieces
+    n = int(np.prod(dim))
+    t = TensorTransform(mode="transpose", option="1:2:0:3")
+    t.negotiate(caps_for(dim, "uint8"))
+    for _ in range(2):
+        x = rng.integers(0, 256, n, dtype=np.uint8)
+        flow, (y,) = t.transform([x])
+        assert flow == 0
+        assert bits_equal(y, port.transpose(x, dim, (1, 2, 0, 3)))
+    t.close()
 
 
 # ---------------------------------------------------------------------------------------
