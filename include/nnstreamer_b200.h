@@ -429,6 +429,14 @@ NNSB_API int nnsb_transform_download (nnsb_transform * t, void *host_dst, const 
 NNSB_API int nnsb_transform_upload (nnsb_transform * t, const nnsb_memory * dev_dst, const void *host_src);
 /* kernels launched by this element so far */
 NNSB_API int nnsb_transform_kernel_launches (nnsb_transform * t, uint64_t *count);
+/* Where device outputs come from: by default the element's own pool (the reference calls
+ * gst_allocator_alloc (NULL, ...), :1758); a provider lets the DOWNSTREAM element hand out the
+ * memory instead (GstBaseTransform's decide_allocation choosing the peer's pool), so that e.g.
+ * tensor_aggregator receives its frames where it wants them.  The provider returns 0 and an
+ * owned device memory of exactly `size` bytes, or an error (the element's pool is used then).
+ * fn == NULL removes the provider. */
+typedef int (*nnsb_output_provider_fn) (void *user, size_t size, nnsb_memory * out);
+NNSB_API int nnsb_transform_set_output_provider (nnsb_transform * t, nnsb_output_provider_fn fn, void *user);
 
 typedef struct nnsb_converter nnsb_converter;
 
@@ -500,6 +508,15 @@ NNSB_API int nnsb_aggregator_chain (nnsb_aggregator * a, const nnsb_memory * in,
     const nnsb_buffer_time * t_in, nnsb_memory * outs, nnsb_buffer_time * t_outs, uint32_t max_out,
     uint32_t *n_out);
 NNSB_API int nnsb_aggregator_kernel_launches (nnsb_aggregator * a, uint64_t *count);
+/* The memory the next input buffer should be written into: a share of the adapter's ring at its
+ * tail.  A producer that fills it and passes it to nnsb_aggregator_chain has pushed the buffer
+ * without a copy (gst_adapter_push, :873, normally memcpy's into the adapter).  This is the role
+ * of a downstream-proposed buffer pool in GStreamer; the signature is nnsb_output_provider_fn so
+ * that nnsb_transform_set_output_provider (t, nnsb_aggregator_acquire, a) wires an upstream
+ * tensor_transform to it.  Fails with NNSB_ENOTSUP when frames-in == frames-out. */
+NNSB_API int nnsb_aggregator_acquire (void *aggregator, size_t size, nnsb_memory * out);
+/* bytes the element has moved itself so far: into the adapter / out of it (concatenation) */
+NNSB_API int nnsb_aggregator_copy_counters (nnsb_aggregator * a, uint64_t *copied_in, uint64_t *copied_out);
 
 /* ---------------------------------------------------------------------------------------
  * tensor_decoder mode=direct_video mirror: the GstTensorDecoderDef

@@ -211,6 +211,9 @@ _PROTOS = {
                                         C.POINTER(Memory), C.POINTER(BufferTime), C.c_uint32,
                                         C.POINTER(C.c_uint32)]),
     "nnsb_aggregator_kernel_launches": (C.c_int, [_VP, C.POINTER(C.c_uint64)]),
+    "nnsb_aggregator_acquire": (C.c_int, [_VP, C.c_size_t, C.POINTER(Memory)]),
+    "nnsb_aggregator_copy_counters": (C.c_int, [_VP, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "nnsb_transform_set_output_provider": (C.c_int, [_VP, _VP, _VP]),
     "nnsb_pad_launch": (C.c_int, [_VP, _VP, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),
     "nnsb_d2h_2d_async": (C.c_int, [_VP, _VP, C.c_size_t, _VP, C.c_size_t, C.c_size_t, C.c_size_t]),
     "nnsb_direct_video_new": (C.c_int, [C.c_int, C.POINTER(_VP)]),

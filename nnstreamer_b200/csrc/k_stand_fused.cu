@@ -22,16 +22,19 @@
  *           full (during the cross-CTA hand-shake below); L2 is the second buffer.
  *   6 warps (statistics) read every tile once as it lands: fp64 sum (x - K) and sum (x - K)^2
  *           per channel, K = first element of the channel (same shifted one-pass formula as
- *           k_stand.cuh).  After the last tile of tensor f: block reduction, the CTA's partial
- *           goes to global scratch, a release-store of a flag publishes it; every CTA then
- *           acquires all flags, folds the 148 partials in a fixed order (all CTAs compute the
- *           same bits) -> {mean, 1/std} into shared memory -> arrive on `ready[f & 1]`.
+ *           k_stand.cuh).  After the last tile of tensor f each warp leaves its sums in shared
+ *           memory, arrives on `stats_done[f & 1]` and goes on with tensor f + 1.
+ *   warp 1  (control) adds the six warp sums, writes the CTA's partial to global scratch and
+ *           bumps ONE counter per tensor (fence + atomicAdd); lane 0 polls that counter until all
+ *           CTAs have arrived, then the warp reads the 148 partials (coalesced, L2) and folds
+ *           them in a fixed order -- every CTA computes the same bits -- into {mean, 1/std} in
+ *           shared memory, and arrives on `ready[f & 1]`.
  *   12 warps (normalisation) wait for `ready`, read the tiles of tensor f from shared memory
  *           again, fp64 (x - mean) * (1 / std), |.|, convert, 128-bit stores to global, and free
  *           the slot (arrive on `empty`): the producer refills it with tensor f+1.
  *
  * DRAM traffic: one read + one write = the algorithmic 8 B/element.  The statistics warps run
- * one tensor ahead of the normalisation warps, so the only serial gap per tensor is the flag
+ * one tensor ahead of the normalisation warps, so the only serial gap per tensor is the counter
  * hand-shake (~1.5 us), during which the L2 prefetch keeps HBM busy.
  *
  * Restrictions (else the three-launch path is used, nnsb_runtime.cu): float32 in and out,
@@ -39,8 +42,9 @@
  * Summation order differs from k_stand.cuh (tiles instead of a grid-stride), so results agree
  * with it within stand's tolerance, not bit for bit; the normalisation arithmetic is identical.
  */
-#include <cooperative_groups.h>
 #include <cuda_runtime.h>
+
+#include <cstdlib>
 
 #include "nnsb_device.cuh"
 #include "nnsb_kernels.h"
@@ -56,10 +60,10 @@ constexpr int NSLOT = 18;
 constexpr int STATS_WARPS = 6, APPLY_WARPS = 12;
 constexpr int STATS_THREADS = STATS_WARPS * 32;         /* 192: 4 vectors per tile and thread */
 constexpr int APPLY_THREADS = APPLY_WARPS * 32;         /* 384: 2 vectors per tile and thread */
-constexpr int THREADS = 32 + STATS_THREADS + APPLY_THREADS;
+constexpr int THREADS = 64 + STATS_THREADS + APPLY_THREADS;     /* producer + control + ... */
 constexpr int MAX_CTAS = 160;
 constexpr int PUB_SLOTS = 4;                    /* scratch slots cycled by tensor index */
-constexpr int LOOKAHEAD = 16;                   /* tiles the L2 prefetch runs ahead of the ring */
+constexpr int LOOKAHEAD_DEFAULT = 16;           /* tiles the L2 prefetch runs ahead of the ring */
 
 __device__ __forceinline__ uint32_t smem_u32 (const void *p)
 {
@@ -101,21 +105,12 @@ __device__ __forceinline__ void bulk_prefetch_l2 (const void *gmem_src, uint32_t
 {
   asm volatile ("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l" (gmem_src), "r" (bytes) : "memory");
 }
-__device__ __forceinline__ void st_release_u32 (uint32_t *p, uint32_t v)
-{
-  asm volatile ("st.release.gpu.global.u32 [%0], %1;" :: "l" (p), "r" (v) : "memory");
-}
 __device__ __forceinline__ uint32_t ld_acquire_u32 (const uint32_t *p)
 {
   uint32_t v;
   asm volatile ("ld.acquire.gpu.global.u32 %0, [%1];" : "=r" (v) : "l" (p) : "memory");
   return v;
 }
-__device__ __forceinline__ void named_barrier (int id, int threads)
-{
-  asm volatile ("bar.sync %0, %1;" :: "r" (id), "r" (threads) : "memory");
-}
-
 struct FusedArgs
 {
   const float *in;
@@ -124,8 +119,9 @@ struct FusedArgs
   uint32_t batch;
   uint32_t n_tiles;             /* tiles per tensor (the last one may be short) */
   uint32_t tiles_lo, n_hi;      /* CTAs [0, n_hi) own tiles_lo + 1 tiles, the others tiles_lo */
-  uint32_t *flags;              /* [PUB_SLOTS][gridDim.x], zero on entry */
-  double *partial;              /* [PUB_SLOTS][gridDim.x][4][2] */
+  uint32_t *counter;            /* [PUB_SLOTS] (one per 128-byte line), zero on entry */
+  double *partial;              /* [PUB_SLOTS][4][2][gridDim.x] */
+  uint32_t lookahead;
   double *stats;                /* [batch][nch][2] = {mean, std}, for nnsb_plan_stand_stats */
   int default_mode;
 };
@@ -134,9 +130,9 @@ struct __align__ (16) Shared
 {
   uint64_t full[NSLOT], empty[NSLOT];
   uint64_t ready[2];            /* {mean, 1/std} of tensor f is in ms[f & 1] */
+  uint64_t stats_done[2];       /* the six warp sums of tensor f are in red[f & 1] */
   double ms[2][4][2];           /* mean, 1/std per channel */
-  double red[2][4][STATS_WARPS];
-  double fold[2][4][MAX_CTAS];
+  double red[2][2][4][STATS_WARPS];
 };
 
 template <int NCH>
@@ -159,6 +155,8 @@ stand_fused_kernel (FusedArgs a)
     }
     mbar_init (&sh.ready[0], 1);
     mbar_init (&sh.ready[1], 1);
+    mbar_init (&sh.stats_done[0], STATS_WARPS);
+    mbar_init (&sh.stats_done[1], STATS_WARPS);
     asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads ();
@@ -177,7 +175,7 @@ stand_fused_kernel (FusedArgs a)
       uint64_t pf = 0;                                          /* next tile to prefetch into L2 */
       for (uint64_t q = 0; q < total; q++) {
         /* keep the L2 prefetch LOOKAHEAD tiles ahead of the shared-memory loads */
-        const uint64_t pf_end = q + LOOKAHEAD < total ? q + LOOKAHEAD : total;
+        const uint64_t pf_end = q + a.lookahead < total ? q + a.lookahead : total;
         if (pf < q)
           pf = q;
         for (; pf < pf_end; pf++) {
@@ -200,9 +198,88 @@ stand_fused_kernel (FusedArgs a)
     return;
   }
 
-  if (warp <= STATS_WARPS) {
+  if (warp == 1) {
+    /* ------------------------------ control ------------------------------ */
+    for (uint32_t f = 0; f < a.batch; f++) {
+      const uint32_t pub = f % PUB_SLOTS;
+      mbar_wait (&sh.stats_done[f & 1], (f >> 1) & 1);
+      /* lane (c, k): channel c, k = 0 sum / 1 sum of squares */
+      if (lane < NCH * 2) {
+        const uint32_t c = lane >> 1, k = lane & 1;
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < STATS_WARPS; w++)
+          t += sh.red[f & 1][k][c][w];
+        a.partial[(((size_t) pub * 4 + c) * 2 + k) * n_cta + cta] = t;
+      }
+      __syncwarp ();
+      if (lane == 0) {
+        __threadfence ();
+        atomicAdd (a.counter + pub * 32, 1u);
+        /* this slot's (f / PUB_SLOTS)-th use: everybody has arrived at n_cta * (uses so far) */
+        const uint32_t target = n_cta * (f / PUB_SLOTS + 1);
+        while (ld_acquire_u32 (a.counter + pub * 32) < target)
+          __nanosleep (32);
+      }
+      __syncwarp ();
+      /* fold the n_cta partials: lane l takes CTAs l, l + 32, ... in order, then a fixed
+       * shuffle tree: the same bits in every CTA */
+      double tot[NCH][2];
+#pragma unroll
+      for (int c = 0; c < NCH; c++)
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+          const double *p = a.partial + (((size_t) pub * 4 + c) * 2 + k) * n_cta;
+          double v[(MAX_CTAS + 31) / 32];
+#pragma unroll
+          for (int i = 0; i < (MAX_CTAS + 31) / 32; i++)
+            v[i] = (lane + i * 32 < n_cta) ? __ldcg (p + lane + i * 32) : 0.0;
+          double t = 0.0;
+#pragma unroll
+          for (int i = 0; i < (MAX_CTAS + 31) / 32; i++)
+            t += v[i];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1)
+            t += __shfl_xor_sync (0xffffffffu, t, o);
+          tot[c][k] = t;
+        }
+      if (lane < NCH) {
+        double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+        for (int c = 0; c < NCH; c++)
+          if (lane == (uint32_t) c) {
+            s1 = tot[c][0];
+            s2 = tot[c][1];
+          }
+        const float *base = a.in + (uint64_t) f * a.frame_elems;
+        const double n = (double) (a.frame_elems / NCH);
+        const double k0 = (double) __ldg (base + lane);
+        const double mean = k0 + s1 / n;
+        double sd = 0.0;
+        if (a.default_mode) {
+          const double var = (s2 - s1 * (s1 / n)) / n;
+          /* tensor_data.c:438,488: std = (sum != 0) ? sqrt (sum) : 1e-10 */
+          sd = (var > 0.0) ? sqrt (var) : 1e-10;
+        }
+        /* ms[f & 1] was last read by the normalisation of tensor f - 2, which finished before
+         * the slots of tensor f could be filled */
+        sh.ms[f & 1][lane][0] = mean;
+        sh.ms[f & 1][lane][1] = a.default_mode ? __drcp_rn (sd) : 0.0;
+        if (cta == 0) {
+          a.stats[((size_t) f * NCH + lane) * 2 + 0] = mean;
+          a.stats[((size_t) f * NCH + lane) * 2 + 1] = sd;
+        }
+      }
+      __syncwarp ();
+      if (lane == 0)
+        mbar_arrive (&sh.ready[f & 1]);
+    }
+    return;
+  }
+
+  if (warp < 2 + STATS_WARPS) {
     /* ------------------------------ statistics ------------------------------ */
-    const uint32_t tid = threadIdx.x - 32;                      /* 0..191 */
+    const uint32_t tid = threadIdx.x - 64;                      /* 0..191 */
     const uint32_t swarp = tid >> 5;
     /* vector v = tid + i * 192 of a tile: its lane k belongs to channel (c0 + k) % NCH; 192 and
      * TILE are multiples of 3 and 4, so c0 depends on the thread only */
@@ -242,7 +319,8 @@ stand_fused_kernel (FusedArgs a)
           }
         }
       }
-      /* actual-channel order, then a fixed-order block reduction */
+      /* actual-channel order, a fixed shuffle tree per warp; the control warp adds the warps.
+       * red[f & 1] was consumed (tensor f - 2) long before these tiles could even be loaded */
 #pragma unroll
       for (int c = 0; c < NCH; c++) {
         double s1 = 0.0, s2 = 0.0;
@@ -258,75 +336,20 @@ stand_fused_kernel (FusedArgs a)
           s2 += __shfl_xor_sync (0xffffffffu, s2, o);
         }
         if (lane == 0) {
-          sh.red[0][c][swarp] = s1;
-          sh.red[1][c][swarp] = s2;
+          sh.red[f & 1][0][c][swarp] = s1;
+          sh.red[f & 1][1][c][swarp] = s2;
         }
       }
-      named_barrier (1, STATS_THREADS);
-      const uint32_t pub = f % PUB_SLOTS;
-      if (tid < NCH) {
-        double t1 = 0.0, t2 = 0.0;
-#pragma unroll
-        for (int w = 0; w < STATS_WARPS; w++) {
-          t1 += sh.red[0][tid][w];
-          t2 += sh.red[1][tid][w];
-        }
-        double *p = a.partial + (((size_t) pub * n_cta + cta) * 4 + tid) * 2;
-        p[0] = t1;
-        p[1] = t2;
-        __threadfence ();
-      }
-      named_barrier (1, STATS_THREADS);
-      if (tid == 0)
-        st_release_u32 (a.flags + (size_t) pub * n_cta + cta, f + 1);
-      /* gather: thread i waits for CTA i, then pulls its partial into shared memory */
-      for (uint32_t i = tid; i < n_cta; i += STATS_THREADS) {
-        const uint32_t *fl = a.flags + (size_t) pub * n_cta + i;
-        while (ld_acquire_u32 (fl) != f + 1)
-          __nanosleep (20);
-        const double *p = a.partial + (((size_t) pub * n_cta + i) * 4) * 2;
-#pragma unroll
-        for (int c = 0; c < NCH; c++) {
-          sh.fold[0][c][i] = __ldcg (p + c * 2);
-          sh.fold[1][c][i] = __ldcg (p + c * 2 + 1);
-        }
-      }
-      named_barrier (1, STATS_THREADS);
-      if (tid < NCH) {
-        /* every CTA folds the same numbers in the same order: identical statistics everywhere */
-        double s1 = 0.0, s2 = 0.0;
-        for (uint32_t i = 0; i < n_cta; i++) {
-          s1 += sh.fold[0][tid][i];
-          s2 += sh.fold[1][tid][i];
-        }
-        const double n = (double) (a.frame_elems / NCH);
-        const double k0 = (double) __ldg (base + tid);
-        const double mean = k0 + s1 / n;
-        double sd = 0.0;
-        if (a.default_mode) {
-          const double var = (s2 - s1 * (s1 / n)) / n;
-          /* tensor_data.c:438,488: std = (sum != 0) ? sqrt (sum) : 1e-10 */
-          sd = (var > 0.0) ? sqrt (var) : 1e-10;
-        }
-        /* ms[f & 1] was last read by the normalisation of tensor f - 2, which finished before
-         * the slots of tensor f could be filled */
-        sh.ms[f & 1][tid][0] = mean;
-        sh.ms[f & 1][tid][1] = a.default_mode ? __drcp_rn (sd) : 0.0;
-        if (cta == 0) {
-          a.stats[((size_t) f * NCH + tid) * 2 + 0] = mean;
-          a.stats[((size_t) f * NCH + tid) * 2 + 1] = sd;
-        }
-      }
-      named_barrier (1, STATS_THREADS);
-      if (tid == 0)
-        mbar_arrive (&sh.ready[f & 1]);
+      __syncwarp ();
+      if (lane == 0)
+        mbar_arrive (&sh.stats_done[f & 1]);
     }
     return;
   }
 
   /* ------------------------------ normalisation ------------------------------ */
   {
-    const uint32_t tid = threadIdx.x - 32 - STATS_THREADS;      /* 0..383 */
+    const uint32_t tid = threadIdx.x - 64 - STATS_THREADS;      /* 0..383 */
     const uint32_t c0 = (tid * 4) % NCH;                        /* 384 is a multiple of 3 and 4 too */
     for (uint32_t f = 0; f < a.batch; f++) {
       mbar_wait (&sh.ready[f & 1], (f >> 1) & 1);
@@ -442,12 +465,13 @@ stand_fused_supported (int in_type, int out_type, const void *in, const void *ou
   return geometry (frame_elems, cfg, &g);
 }
 
+constexpr size_t COUNTER_BYTES = (size_t) PUB_SLOTS * 128;      /* one 128-byte line per counter */
+
 size_t
 stand_fused_scratch_bytes (const LaunchCfg &cfg)
 {
-  /* flags, then partials (256-byte aligned) */
-  const size_t flags = ((size_t) PUB_SLOTS * cfg.sm_count * sizeof (uint32_t) + 255) / 256 * 256;
-  return flags + (size_t) PUB_SLOTS * cfg.sm_count * 4 * 2 * sizeof (double);
+  /* counters, then partials */
+  return COUNTER_BYTES + (size_t) PUB_SLOTS * cfg.sm_count * 4 * 2 * sizeof (double);
 }
 
 int
@@ -458,8 +482,7 @@ launch_stand_fused (int stand_mode, const void *in, void *out, size_t frame_elem
   Geometry g;
   if (!geometry (frame_elems, cfg, &g))
     return (int) cudaErrorInvalidValue;
-  const size_t flag_bytes = ((size_t) PUB_SLOTS * cfg.sm_count * sizeof (uint32_t) + 255) / 256 * 256;
-  cudaError_t e = cudaMemsetAsync (scratch, 0, flag_bytes, stream);
+  cudaError_t e = cudaMemsetAsync (scratch, 0, COUNTER_BYTES, stream);
   if (e != cudaSuccess)
     return (int) e;
   FusedArgs a;
@@ -470,8 +493,11 @@ launch_stand_fused (int stand_mode, const void *in, void *out, size_t frame_elem
   a.n_tiles = g.n_tiles;
   a.tiles_lo = g.tiles_lo;
   a.n_hi = g.n_hi;
-  a.flags = (uint32_t *) scratch;
-  a.partial = (double *) ((char *) scratch + flag_bytes);
+  a.counter = (uint32_t *) scratch;
+  a.partial = (double *) ((char *) scratch + COUNTER_BYTES);
+  a.lookahead = LOOKAHEAD_DEFAULT;
+  if (const char *env = getenv ("NNSB_STAND_LOOKAHEAD"))
+    a.lookahead = (uint32_t) atoi (env);
   a.stats = stats;
   a.default_mode = stand_mode == NNSB_STAND_DEFAULT;
   int err;

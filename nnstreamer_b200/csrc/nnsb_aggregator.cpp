@@ -5,11 +5,20 @@
  * The reference keeps incoming buffers in a host GstAdapter, takes frames_out frames off its
  * head for every output (gst_adapter_get_buffer, :903), re-orders them with a host memcpy
  * loop when the frames are concatenated along an inner axis (:768-787) and flushes
- * frames_flush frames (:921-938).  Here the adapter is a byte range [head, tail) of one
- * device buffer: pushing is an async copy to the tail (H2D for host buffers, D2D for device
- * ones), flushing is pointer arithmetic, an output is either a D2D copy of the head or -- for
- * the concatenation -- one launch of the permutation kernels (the block interleave is a rank-3
- * strided copy: out[block][frame][byte-in-block] <- in[frame][block][byte-in-block]).
+ * frames_flush frames (:921-938).  Here the adapter is a byte range [head, tail) of one pooled,
+ * reference-counted device block (the ring):
+ *   push    a producer that asked for its output memory with nnsb_aggregator_acquire writes
+ *           straight into the tail (nothing is moved); any other buffer is copied to the tail
+ *           (H2D for host buffers, D2D for device ones);
+ *   output  without concatenation an output is a SHARE of the ring at the head (nothing is
+ *           moved; overlapping windows of frames_flush < frames_out simply overlap); with it,
+ *           one launch of the permutation kernels (the block interleave is a rank-3 strided
+ *           copy: out[block][frame][byte-in-block] <- in[frame][block][byte-in-block]);
+ *   flush   pointer arithmetic.  When the tail reaches the end of the block while outputs still
+ *           reference it, the few live bytes move to the front of a fresh block from the pool
+ *           and the old one lives on until its last share is released.
+ * Everything is stream-ordered (nnsb_memory): chain() does not wait for the GPU unless the
+ * input is host memory (the caller may reuse that on return).
  *
  * Same property names and defaults (:276-281), the same caps arithmetic (:1026-1081), the same
  * timestamp interpolation (:873-900).  Not mirrored: the per-client adapter table keyed by the
@@ -82,9 +91,11 @@ struct nnsb_aggregator
   bool configured = false;
   nnsb_tensors_config in_config, out_config;
 
-  /* the adapter: bytes [head, tail) of d_buf hold the stream positions [base, base + tail - head) */
-  char *d_buf = nullptr;
+  /* the adapter: bytes [head, tail) of the ring hold the stream positions
+   * [stream_pos, stream_pos + tail - head) */
+  nnsb_memory ring;                     /* data == NULL: none yet */
   size_t capacity = 0, head = 0, tail = 0;
+  uint64_t copied_in = 0, copied_out = 0;       /* bytes this element moved itself */
   uint64_t stream_pos = 0;              /* stream position of d_buf[head] */
   uint64_t pushed = 0;                  /* stream position of the next pushed byte */
   std::vector<StampedOffset> stamps;
@@ -113,6 +124,7 @@ nnsb_aggregator_new (int device_id, nnsb_aggregator ** out)
   if (!a)
     return nnsb_set_error (NNSB_ENOMEM, "nnsb_aggregator_new: out of memory");
   a->device_id = device_id;
+  memset (&a->ring, 0, sizeof (a->ring));
   config_init (&a->in_config);
   config_init (&a->out_config);
   *out = a;
@@ -127,6 +139,10 @@ nnsb_aggregator_reset (nnsb_aggregator * a)
     return nnsb_set_error (NNSB_EINVAL, "nnsb_aggregator_reset: null argument");
   if (a->stream)
     nnsb_stream_sync (a->stream);
+  /* outputs handed out earlier keep the old block; start over in a fresh one */
+  nnsb_memory_release (&a->ring);
+  memset (&a->ring, 0, sizeof (a->ring));
+  a->capacity = 0;
   a->head = a->tail = 0;
   a->stream_pos = a->pushed = 0;
   a->stamps.clear ();
@@ -141,8 +157,7 @@ nnsb_aggregator_free (nnsb_aggregator * a)
   drop_plan (a);
   if (a->stream)
     nnsb_stream_sync (a->stream);
-  if (a->d_buf)
-    nnsb_dev_free (a->ctx, a->d_buf);
+  nnsb_memory_release (&a->ring);
   if (a->stream)
     nnsb_stream_destroy (a->stream);
   if (a->ctx)
@@ -349,12 +364,11 @@ ensure_concat_plan (nnsb_aggregator * a, const nnsb_tensor_info & frame, size_t 
   return r;
 }
 
-/* gst_tensor_aggregator_push, :805-830: `d_src` holds frames_out frames back to back; the
- * result (concatenated if needed) becomes *out.  pass: a device buffer of the caller that may be
- * handed on as it is; adopt: a device block of ours (staged host data) that may become the output. */
+/* gst_tensor_aggregator_push, :805-830: `src` (a device memory: the caller's buffer, a staged
+ * copy of it, or the ring) holds frames_out frames back to back at byte `off`; the result
+ * (concatenated if needed) becomes *out. */
 static int
-produce (nnsb_aggregator * a, const char *d_src, size_t frame_size, const nnsb_memory * pass,
-    void *adopt, nnsb_memory * out)
+produce (nnsb_aggregator * a, const nnsb_memory * src, size_t off, size_t frame_size, nnsb_memory * out)
 {
   nnsb_tensor_info frame = a->out_config.info[0];
   frame.dim[a->frames_dim] /= a->frames_out;
@@ -364,75 +378,101 @@ produce (nnsb_aggregator * a, const char *d_src, size_t frame_size, const nnsb_m
     return NNSB_FLOW_ERROR;
   }
   const size_t out_size = frame_size * a->frames_out;
-  const bool do_concat = needs_concat (a, frame);
-  if (!do_concat && pass && pass->on_device) {
-    /* gst_pad_push of the incoming buffer itself: no copy, one more reference */
-    return nnsb_memory_ref (pass, out) == NNSB_OK ? NNSB_FLOW_OK : NNSB_FLOW_ERROR;
+  if (!needs_concat (a, frame)) {
+    /* gst_pad_push of (a sub-buffer of) what is already there: one more reference, no copy */
+    return nnsb_memory_share (src, off, out_size, out) == NNSB_OK ? NNSB_FLOW_OK : NNSB_FLOW_ERROR;
   }
-  if (!do_concat && adopt) {
-    /* a staged copy of a host buffer is already the output */
-    return nnsb_memory_adopt (a->ctx, adopt, out_size, 1, out) == NNSB_OK ? NNSB_FLOW_OK
-        : NNSB_FLOW_ERROR;
-  }
-  void *d_out = nullptr;
-  if (nnsb_dev_alloc (a->ctx, out_size, &d_out) != NNSB_OK)
+  if (nnsb_memory_alloc (a->ctx, out_size, 1, a->stream, out) != NNSB_OK)
     return NNSB_FLOW_ERROR;
-  int r;
-  if (do_concat) {
-    r = ensure_concat_plan (a, frame, frame_size);
-    if (r == NNSB_OK)
-      r = nnsb_plan_launch (a->concat_plan, d_src, d_out, 1, a->stream);
-    if (r == NNSB_OK)
-      a->launches += (uint64_t) nnsb_plan_last_launch_count (a->concat_plan);
-  } else {
-    r = nnsb_d2d_async (a->stream, d_out, d_src, out_size);
+  int r = ensure_concat_plan (a, frame, frame_size);
+  if (r == NNSB_OK)
+    r = nnsb_memory_wait (src, a->stream);
+  if (r == NNSB_OK)
+    r = nnsb_plan_launch (a->concat_plan, (const char *) src->data + off, out->data, 1, a->stream);
+  if (r == NNSB_OK) {
+    a->launches += (uint64_t) nnsb_plan_last_launch_count (a->concat_plan);
+    a->copied_out += out_size;
+    r = nnsb_memory_mark_io (a->stream, out, 1, src, 1);
   }
   if (r != NNSB_OK) {
-    nnsb_dev_free (a->ctx, d_out);
-    return NNSB_FLOW_ERROR;
-  }
-  if (nnsb_memory_adopt (a->ctx, d_out, out_size, 1, out) != NNSB_OK) {
     nnsb_stream_sync (a->stream);
-    nnsb_dev_free (a->ctx, d_out);
+    nnsb_memory_release (out);
     return NNSB_FLOW_ERROR;
   }
   return NNSB_FLOW_OK;
 }
 
-/* room for `need` more bytes behind the tail: rewind when empty, else move the live bytes to
- * the front of a larger (or the same-sized, fresh) buffer */
+/* room for `need` more bytes behind the tail.  An empty adapter rewinds only when nobody else
+ * references the block (outputs are shares of it); otherwise, and when the tail reaches the end,
+ * the live bytes move to the front of a fresh block from the pool. */
 static int
 make_room (nnsb_aggregator * a, size_t need, size_t out_size)
 {
-  if (a->head == a->tail)
+  if (a->ring.data && a->head == a->tail && nnsb_memory_is_unique (&a->ring))
     a->head = a->tail = 0;
-  if (a->d_buf && a->tail + need <= a->capacity)
+  if (a->ring.data && a->tail + need <= a->capacity)
     return NNSB_OK;
   const size_t live = a->tail - a->head;
-  size_t cap = a->capacity ? a->capacity : 0;
+  size_t cap = a->capacity;
   const size_t want = 4 * (live + need + out_size);
   if (cap < want)
     cap = want;
-  void *fresh = nullptr;
-  int r = nnsb_dev_alloc (a->ctx, cap, &fresh);
+  nnsb_memory fresh;
+  int r = nnsb_memory_alloc (a->ctx, cap, 1, a->stream, &fresh);
   if (r != NNSB_OK)
     return r;
   if (live) {
-    r = nnsb_d2d_async (a->stream, fresh, a->d_buf + a->head, live);
+    r = nnsb_memory_wait (&a->ring, a->stream);
+    if (r == NNSB_OK)
+      r = nnsb_d2d_async (a->stream, fresh.data, (char *) a->ring.data + a->head, live);
+    if (r == NNSB_OK)
+      r = nnsb_memory_mark_io (a->stream, &fresh, 1, &a->ring, 1);
     if (r != NNSB_OK) {
-      nnsb_dev_free (a->ctx, fresh);
+      nnsb_stream_sync (a->stream);
+      nnsb_memory_release (&fresh);
       return r;
     }
+    a->copied_in += live;
   }
-  if (a->d_buf) {
-    /* outputs and copies that still read the old buffer are ordered on the stream */
-    nnsb_stream_sync (a->stream);
-    nnsb_dev_free (a->ctx, a->d_buf);
-  }
-  a->d_buf = (char *) fresh;
+  nnsb_memory_release (&a->ring);       /* lives on while outputs share it */
+  a->ring = fresh;
   a->capacity = cap;
   a->head = 0;
   a->tail = live;
+  return NNSB_OK;
+}
+
+/* The memory the NEXT buffer should be written into: a share of the ring at the tail.  A
+ * producer that fills it (and marks it ready on its stream) and passes it to chain() has
+ * pushed its buffer without a copy -- what a downstream-proposed buffer pool does in GStreamer
+ * (gst_base_transform decide_allocation).  Same signature as nnsb_output_provider_fn. */
+extern "C" int
+nnsb_aggregator_acquire (void *aggregator, size_t size, nnsb_memory * out)
+{
+  nnsb_aggregator *a = (nnsb_aggregator *) aggregator;
+  if (!a || !out || size == 0)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_aggregator_acquire: invalid argument");
+  if (!a->configured || a->frames_in == a->frames_out)
+    return nnsb_set_error (NNSB_ENOTSUP, "nnsb_aggregator_acquire: nothing is accumulated in this configuration");
+  int r = ensure_device (a);
+  if (r)
+    return r;
+  const size_t frame_size = size / a->frames_in;
+  r = make_room (a, size, frame_size * a->frames_out);
+  if (r)
+    return r;
+  return nnsb_memory_share (&a->ring, a->tail, size, out);
+}
+
+extern "C" int
+nnsb_aggregator_copy_counters (nnsb_aggregator * a, uint64_t * copied_in, uint64_t * copied_out)
+{
+  if (!a)
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_aggregator_copy_counters: null argument");
+  if (copied_in)
+    *copied_in = a->copied_in;
+  if (copied_out)
+    *copied_out = a->copied_out;
   return NNSB_OK;
 }
 
@@ -493,32 +533,29 @@ nnsb_aggregator_chain (nnsb_aggregator * a, const nnsb_memory * in, const nnsb_b
 
   if (frames_in == frames_out) {
     /* push the incoming buffer (do concat if needed), :856-859 */
-    const char *d_src = (const char *) in->data;
-    void *staged = nullptr;
+    nnsb_memory staged;
+    memset (&staged, 0, sizeof (staged));
+    const nnsb_memory *src = in;
     if (!in->on_device) {
-      if (nnsb_dev_alloc (a->ctx, buf_size, &staged) != NNSB_OK)
+      if (nnsb_memory_alloc (a->ctx, buf_size, 1, a->stream, &staged) != NNSB_OK)
         return NNSB_FLOW_ERROR;
-      if (nnsb_h2d_async (a->stream, staged, in->data, buf_size) != NNSB_OK) {
-        nnsb_dev_free (a->ctx, staged);
+      if (nnsb_h2d_async (a->stream, staged.data, in->data, buf_size) != NNSB_OK) {
+        nnsb_stream_sync (a->stream);
+        nnsb_memory_release (&staged);
         return NNSB_FLOW_ERROR;
       }
-      d_src = (const char *) staged;
+      a->copied_in += buf_size;
+      src = &staged;
     }
-    int r = produce (a, d_src, frame_size, in->on_device ? in : nullptr, staged, &outs[0]);
-    if (r == NNSB_FLOW_OK && staged && outs[0].data != staged) {
-      /* the staged copy was only the source of the concatenation */
-      nnsb_stream_sync (a->stream);
-      nnsb_dev_free (a->ctx, staged);
-      staged = nullptr;
+    int r = produce (a, src, 0, frame_size, &outs[0]);
+    if (staged.data) {
+      nnsb_stream_sync (a->stream);     /* the caller may reuse its host buffer */
+      nnsb_memory_release (&staged);    /* the output holds its own reference if it is a share */
     }
-    if (r != NNSB_FLOW_OK) {
-      if (staged)
-        nnsb_dev_free (a->ctx, staged);
+    if (r != NNSB_FLOW_OK)
       return r;
-    }
     if (t_outs)
       t_outs[0] = tin;
-    nnsb_stream_sync (a->stream);       /* the caller may reuse its buffer */
     *n_out = 1;
     return NNSB_FLOW_OK;
   }
@@ -529,12 +566,22 @@ nnsb_aggregator_chain (nnsb_aggregator * a, const nnsb_memory * in, const nnsb_b
 
   /* gst_adapter_push, :873 */
   const size_t out_size = frame_size * frames_out;
-  if (make_room (a, buf_size, out_size) != NNSB_OK)
-    return NNSB_FLOW_ERROR;
-  int r = in->on_device ? nnsb_d2d_async (a->stream, a->d_buf + a->tail, in->data, buf_size)
-      : nnsb_h2d_async (a->stream, a->d_buf + a->tail, in->data, buf_size);
-  if (r != NNSB_OK)
-    return NNSB_FLOW_ERROR;
+  const bool in_place = a->ring.data && in->on_device && in->block && in->block == a->ring.block
+      && (const char *) in->data == (const char *) a->ring.data + a->tail
+      && a->tail + buf_size <= a->capacity;
+  if (!in_place) {
+    if (make_room (a, buf_size, out_size) != NNSB_OK)
+      return NNSB_FLOW_ERROR;
+    char *dst = (char *) a->ring.data + a->tail;
+    int r = in->on_device ? nnsb_d2d_async (a->stream, dst, in->data, buf_size)
+        : nnsb_h2d_async (a->stream, dst, in->data, buf_size);
+    if (r == NNSB_OK && in->on_device)
+      r = nnsb_memory_mark_io (a->stream, &a->ring, 1, in, 1);
+    if (r != NNSB_OK)
+      return NNSB_FLOW_ERROR;
+    a->copied_in += buf_size;
+  }
+  /* in place: the producer wrote the bytes where they belong and marked the block ready */
   a->tail += buf_size;
   a->stamps.push_back ({ a->pushed, tin.pts, tin.dts });
   a->pushed += buf_size;
@@ -555,7 +602,7 @@ nnsb_aggregator_chain (nnsb_aggregator * a, const nnsb_memory * in, const nnsb_b
           dts += scale_u64 (dts_dist * (uint64_t) fd, 1000000000ull, (uint64_t) fn * frame_size);
       }
     }
-    ret = produce (a, a->d_buf + a->head, frame_size, nullptr, nullptr, &outs[*n_out]);
+    ret = produce (a, &a->ring, a->head, frame_size, &outs[*n_out]);
     if (ret != NNSB_FLOW_OK)
       break;
     if (t_outs) {
@@ -576,8 +623,14 @@ nnsb_aggregator_chain (nnsb_aggregator * a, const nnsb_memory * in, const nnsb_b
   /* timestamps of buffers that lie entirely before the head are no longer reachable */
   while (a->stamps.size () > 1 && a->stamps[1].offset <= a->stream_pos)
     a->stamps.erase (a->stamps.begin ());
-  /* the caller may reuse its buffer, and the outputs are complete, once we return */
-  if (nnsb_stream_sync (a->stream) != NNSB_OK)
+  /* a host buffer, or device memory the caller manages itself (no block to hold on to), may be
+   * reused by the caller once we return; for pooled blocks the device work just stays queued */
+  if ((!in->on_device || !in->block) && !in_place && nnsb_stream_sync (a->stream) != NNSB_OK)
     return NNSB_FLOW_ERROR;
+  if (ret != NNSB_FLOW_OK) {
+    for (uint32_t k = 0; k < *n_out; k++)
+      nnsb_memory_release (&outs[k]);
+    *n_out = 0;
+  }
   return ret;
 }

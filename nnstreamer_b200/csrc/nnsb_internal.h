@@ -47,6 +47,8 @@ nnsb_cell nnsb_cast_operand (const nnsb_arith_op * op, int type);
 /* wraps a raw allocation of `ctx` (nnsb_dev_alloc / nnsb_pinned_alloc) into an owned,
  * reference-counted memory (nnsb_runtime.cu); on failure the allocation stays raw */
 int nnsb_memory_adopt (nnsb_ctx * ctx, void *ptr, size_t size, int on_device, nnsb_memory * out);
+/* 1 when `mem` holds the only reference on its block */
+int nnsb_memory_is_unique (const nnsb_memory * mem);
 /* 1 = page-locked / managed host memory (the copy engine reads it directly), 0 = pageable */
 int nnsb_host_is_pinned (const void *p);
 

@@ -548,7 +548,16 @@ nnsb_event_destroy (nnsb_event * e)
  * 8 x 4 elements queued 300 frames deep ran at 13 k frames/s; bounded to three frames in flight
  * per element the same chain is HBM-bound).  Three blocks let producer, consumer and the next
  * frame overlap. */
-static const int POOL_DEPTH_BEFORE_WAIT = 3;
+static int
+pool_depth ()
+{
+  static int depth = 0;
+  if (depth == 0) {
+    const char *env = getenv ("NNSB_POOL_DEPTH");
+    depth = (env && atoi (env) > 0) ? atoi (env) : 3;
+  }
+  return depth;
+}
 
 /* Takes a device block of `bucket` bytes.  have_stream: the block will first be touched by
  * work on `stream`. */
@@ -576,7 +585,7 @@ dev_take (nnsb_ctx * ctx, size_t b, bool have_stream, cudaStream_t stream, void 
           v.erase (v.begin () + (long) i);
         }
       }
-      if (!p && ctx->dev_count[b] >= POOL_DEPTH_BEFORE_WAIT) {
+      if (!p && ctx->dev_count[b] >= pool_depth ()) {
         /* every cached block is still in use by queued work: take the oldest and wait for it */
         p = v.front ().ptr;
         must_wait.swap (v.front ().pending);
@@ -589,7 +598,7 @@ dev_take (nnsb_ctx * ctx, size_t b, bool have_stream, cudaStream_t stream, void 
   if (p) {
     for (nnsb_evt * ev : must_wait) {
       if (!(have_stream && ev->stream == stream))
-        cudaEventSynchronize (ev->e);           /* back-pressure: see POOL_DEPTH_BEFORE_WAIT */
+        cudaEventSynchronize (ev->e);           /* back-pressure: see pool_depth () */
       evt_unref (ev);
     }
     *out = p;
@@ -867,6 +876,17 @@ nnsb_memory_ref (const nnsb_memory * mem, nnsb_memory * out)
   }
   *out = m;
   return NNSB_OK;
+}
+
+/* 1 when `mem` holds the only reference on its block (nobody else can be reading it) */
+extern "C" int
+nnsb_memory_is_unique (const nnsb_memory * mem)
+{
+  nnsb_block *blk = mem ? (nnsb_block *) mem->block : nullptr;
+  if (!blk)
+    return 0;
+  std::lock_guard<std::mutex> lk (blk->ctx->mu);
+  return blk->refs == 1;
 }
 
 extern "C" int

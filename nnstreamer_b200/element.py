@@ -230,6 +230,15 @@ class TensorTransform:
         L.check(self._lib.nnsb_transform_kernel_launches(self.handle, C.byref(c)))
         return int(c.value)
 
+    def link_to_aggregator(self, aggregator):
+        """Device outputs are written where the downstream tensor_aggregator wants them (its ring):
+        what a downstream-proposed buffer pool does in GStreamer.  None unlinks."""
+        if aggregator is None:
+            L.check(self._lib.nnsb_transform_set_output_provider(self.handle, None, None))
+        else:
+            fn = C.cast(self._lib.nnsb_aggregator_acquire, C.c_void_p)
+            L.check(self._lib.nnsb_transform_set_output_provider(self.handle, fn, aggregator.handle))
+
 
 class TensorConverter:
     """gst_element_factory_make ("tensor_converter"), video/x-raw input only."""
@@ -386,6 +395,19 @@ class TensorAggregator:
         c = C.c_uint64(0)
         L.check(self._lib.nnsb_aggregator_kernel_launches(self.handle, C.byref(c)))
         return int(c.value)
+
+    def acquire(self, nbytes):
+        """The device memory the next input buffer should be written into (a share of the ring)."""
+        m = L.Memory()
+        L.check(self._lib.nnsb_aggregator_acquire(self.handle, int(nbytes), C.byref(m)))
+        return DeviceMemory(m)
+
+    @property
+    def bytes_copied(self):
+        """(bytes copied into the adapter, bytes moved by the concatenation) so far."""
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        L.check(self._lib.nnsb_aggregator_copy_counters(self.handle, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
 
 
 class DirectVideoDecoder:

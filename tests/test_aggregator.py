@@ -266,3 +266,74 @@ def test_device_large_concat_uses_the_permutation_kernels(dev, port):
     assert a.kernel_launches == 1
     a.close()
     assert len(got) == 1 and np.array_equal(got[0], want[0])
+
+
+@pytest.mark.gpu
+def test_zero_copy_append_and_concat_through_the_output_provider(dev, port):
+    """tensor_transform ! tensor_aggregator with the aggregator handing out the memory the
+    transform writes into (its ring): appending along the outermost axis moves no bytes at all --
+    outputs are shares of the ring -- and the width concatenation moves each byte exactly once
+    (the permutation launch).  Sliding window (frames-flush 2 of 4) so that outputs overlap."""
+    import ctypes as C
+
+    from nnstreamer_b200 import DeviceMemory, TensorTransform
+    dim = [3, 320, 240, 1]
+    n = int(np.prod(dim))
+    rng = np.random.default_rng(17)
+    frames = [rng.integers(0, 256, n, dtype=np.uint8) for _ in range(10)]
+    conv = [port.typecast(f, "float32") for f in frames]
+    for frames_dim, concat_bytes in ((3, 0), (1, 1)):
+        t = TensorTransform(mode="typecast", option="float32")
+        out_caps = t.negotiate(caps_for(dim, "uint8", "30/1"))
+        agg = TensorAggregator(frames_out=4, frames_flush=2, frames_dim=frames_dim)
+        agg.set_caps(out_caps)
+        t.link_to_aggregator(agg)
+        model = O.AggregatorModel(port, dim, "float32", 1, 4, 2, frames_dim, True)
+        got, want = [], []
+        for f, c in zip(frames, conv):
+            m = t.alloc(n, on_device=True)
+            assert t._lib.nnsb_transform_upload(t.handle, C.byref(m), f.ctypes.data_as(C.c_void_p)) == 0
+            src = DeviceMemory(m)
+            flow, (y,) = t.transform([src])
+            assert flow == 0
+            src.release()
+            flow, mems, _ = agg.chain(y)
+            assert flow == 0, nb.lib().nnsb_last_error()
+            y.release()
+            got += mems
+            want += model.chain(c)
+        assert len(got) == len(want) == 4
+        copied_in, copied_out = agg.bytes_copied
+        assert copied_in == 0, "the frames were written in place"
+        assert copied_out == concat_bytes * sum(w.nbytes for w in want)
+        for g, w in zip(got, want):
+            assert dev.download(g.ptr, g.size, np.uint8).tobytes() == w.tobytes()
+            g.release()
+        agg.close()
+        t.close()
+
+
+@pytest.mark.gpu
+def test_ring_is_replaced_while_outputs_still_reference_it(dev, port):
+    """Outputs are shares of the adapter's block: keep ALL of them alive over many buffers, so
+    the adapter has to move on to fresh blocks; every output must still hold its own bytes."""
+    dim = [4, 16, 16, 1]
+    n = int(np.prod(dim))
+    rng = np.random.default_rng(3)
+    agg = TensorAggregator(frames_out=2, frames_flush=1, frames_dim=3)
+    agg.set_caps(caps_for(dim, "int32"))
+    model = O.AggregatorModel(port, dim, "int32", 1, 2, 1, 3, True)
+    got, want = [], []
+    for i in range(40):
+        b = rng.integers(-1000, 1000, n, dtype=np.int32)
+        flow, mems, _ = agg.chain(b)
+        assert flow == 0
+        got += mems
+        want += model.chain(b)
+    assert len(got) == len(want) == 39
+    for g, w in zip(got, want):
+        assert dev.download(g.ptr, g.size, np.uint8).tobytes() == w.tobytes()
+    agg.close()                                      # the element goes first, the shares stay valid
+    for g, w in zip(got, want):
+        assert dev.download(g.ptr, g.size, np.uint8).tobytes() == w.tobytes()
+        g.release()
