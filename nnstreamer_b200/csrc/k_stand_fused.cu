@@ -63,7 +63,7 @@ constexpr int APPLY_THREADS = APPLY_WARPS * 32;         /* 384: 2 vectors per ti
 constexpr int THREADS = 64 + STATS_THREADS + APPLY_THREADS;     /* producer + control + ... */
 constexpr int MAX_CTAS = 160;
 constexpr int PUB_SLOTS = 4;                    /* scratch slots cycled by tensor index */
-constexpr int LOOKAHEAD_DEFAULT = 16;           /* tiles the L2 prefetch runs ahead of the ring */
+constexpr int LOOKAHEAD_DEFAULT = 8;            /* tiles the L2 prefetch runs ahead of the ring */
 
 __device__ __forceinline__ uint32_t smem_u32 (const void *p)
 {
@@ -161,38 +161,47 @@ stand_fused_kernel (FusedArgs a)
   }
   __syncthreads ();
 
-  /* elements of tile t of a tensor */
-  auto tile_elems = [&] (uint32_t t) -> uint32_t {
-    const uint64_t start = (uint64_t) t * TILE;
-    const uint64_t left = a.frame_elems - start;
-    return left < (uint64_t) TILE ? (uint32_t) left : (uint32_t) TILE;
-  };
+  /* elements of tile t of a tensor: all tiles are full except possibly the last one.  (No
+   * division anywhere below: slot and phase of the ring advance incrementally -- a 64-bit
+   * modulo per tile and thread costs more than the tile's arithmetic.) */
+  const uint32_t last_tile = a.n_tiles - 1;
+  const uint32_t last_elems = (uint32_t) (a.frame_elems - (uint64_t) last_tile * TILE);
+  auto tile_elems = [&] (uint32_t t) -> uint32_t { return t == last_tile ? last_elems : (uint32_t) TILE; };
 
   if (warp == 0) {
     /* ------------------------------ producer ------------------------------ */
     if (lane == 0 && my_tiles) {
-      const uint64_t total = (uint64_t) a.batch * my_tiles;     /* tiles this CTA moves */
-      uint64_t pf = 0;                                          /* next tile to prefetch into L2 */
-      for (uint64_t q = 0; q < total; q++) {
-        /* keep the L2 prefetch LOOKAHEAD tiles ahead of the shared-memory loads */
-        const uint64_t pf_end = q + a.lookahead < total ? q + a.lookahead : total;
-        if (pf < q)
-          pf = q;
+      const uint32_t total = a.batch * my_tiles;        /* tiles this CTA moves (fits 32 bits) */
+      /* the L2 prefetch cursor (tensor pf_f, tile pf_j) runs `lookahead` tiles ahead of q */
+      uint32_t pf = 0, pf_f = 0, pf_j = 0;
+      uint32_t f = 0, j = 0, s = 0, round = 0;
+      for (uint32_t q = 0; q < total; q++) {
+        const uint32_t pf_end = (total - q > a.lookahead) ? q + a.lookahead : total;
         for (; pf < pf_end; pf++) {
-          const uint32_t f = (uint32_t) (pf / my_tiles), j = (uint32_t) (pf % my_tiles);
-          const uint32_t t = first_tile + j;
-          bulk_prefetch_l2 (a.in + (uint64_t) f * a.frame_elems + (uint64_t) t * TILE, tile_elems (t) * 4);
+          if (pf >= q) {
+            const uint32_t t = first_tile + pf_j;
+            bulk_prefetch_l2 (a.in + (uint64_t) pf_f * a.frame_elems + (uint64_t) t * TILE, tile_elems (t) * 4);
+          }
+          if (++pf_j == my_tiles) {
+            pf_j = 0;
+            pf_f++;
+          }
         }
-        const uint32_t s = (uint32_t) (q % NSLOT);
-        const uint32_t round = (uint32_t) (q / NSLOT);
         if (round)
           mbar_wait (&sh.empty[s], (round - 1) & 1);
-        const uint32_t f = (uint32_t) (q / my_tiles), j = (uint32_t) (q % my_tiles);
         const uint32_t t = first_tile + j;
         const uint32_t bytes = tile_elems (t) * 4;
         mbar_expect_tx (&sh.full[s], bytes);
         bulk_g2s (ring + (size_t) s * TILE, a.in + (uint64_t) f * a.frame_elems + (uint64_t) t * TILE,
             bytes, &sh.full[s]);
+        if (++j == my_tiles) {
+          j = 0;
+          f++;
+        }
+        if (++s == NSLOT) {
+          s = 0;
+          round++;
+        }
       }
     }
     return;
@@ -284,6 +293,7 @@ stand_fused_kernel (FusedArgs a)
     /* vector v = tid + i * 192 of a tile: its lane k belongs to channel (c0 + k) % NCH; 192 and
      * TILE are multiples of 3 and 4, so c0 depends on the thread only */
     const uint32_t c0 = (tid * 4) % NCH;
+    uint32_t s = 0, phase = 0;                  /* ring slot and mbarrier parity of the next tile */
     for (uint32_t f = 0; f < a.batch; f++) {
       const float *base = a.in + (uint64_t) f * a.frame_elems;
       double kk[NCH], a1[NCH], a2[NCH];
@@ -294,11 +304,13 @@ stand_fused_kernel (FusedArgs a)
         a2[r] = 0.0;
       }
       for (uint32_t j = 0; j < my_tiles; j++) {
-        const uint64_t q = (uint64_t) f * my_tiles + j;
-        const uint32_t s = (uint32_t) (q % NSLOT);
-        mbar_wait (&sh.full[s], (uint32_t) (q / NSLOT) & 1);
+        mbar_wait (&sh.full[s], phase);
         const float4 *tile = reinterpret_cast<const float4 *> (ring + (size_t) s * TILE);
         const uint32_t nv = tile_elems (first_tile + j) / 4;
+        if (++s == NSLOT) {
+          s = 0;
+          phase ^= 1;
+        }
         float4 x[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
@@ -351,6 +363,7 @@ stand_fused_kernel (FusedArgs a)
   {
     const uint32_t tid = threadIdx.x - 64 - STATS_THREADS;      /* 0..383 */
     const uint32_t c0 = (tid * 4) % NCH;                        /* 384 is a multiple of 3 and 4 too */
+    uint32_t s = 0;
     for (uint32_t f = 0; f < a.batch; f++) {
       mbar_wait (&sh.ready[f & 1], (f >> 1) & 1);
       double mean[NCH], rsd[NCH];
@@ -361,9 +374,10 @@ stand_fused_kernel (FusedArgs a)
       }
       float *obase = a.out + (uint64_t) f * a.frame_elems;
       for (uint32_t j = 0; j < my_tiles; j++) {
-        const uint64_t q = (uint64_t) f * my_tiles + j;
-        const uint32_t s = (uint32_t) (q % NSLOT);
         const float4 *tile = reinterpret_cast<const float4 *> (ring + (size_t) s * TILE);
+        uint64_t *const empty_bar = &sh.empty[s];
+        if (++s == NSLOT)
+          s = 0;
         const uint32_t t = first_tile + j;
         const uint32_t nv = tile_elems (t) / 4;
         float4 *dst = reinterpret_cast<float4 *> (obase + (uint64_t) t * TILE);
@@ -376,7 +390,7 @@ stand_fused_kernel (FusedArgs a)
         /* the values are in registers: the slot can be refilled while we compute and store */
         __syncwarp ();
         if (lane == 0)
-          mbar_arrive (&sh.empty[s]);
+          mbar_arrive (empty_bar);
 #pragma unroll
         for (int i = 0; i < 2; i++) {
           const uint32_t v = tid + i * APPLY_THREADS;

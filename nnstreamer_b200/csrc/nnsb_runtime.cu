@@ -545,16 +545,19 @@ nnsb_event_destroy (nnsb_event * e)
  * (cudaEventSynchronize on the oldest block's events): it is the back-pressure of the pipeline.
  * Without it a producer thread runs arbitrarily far ahead of the GPU, and deep queues on more
  * streams than the device has hardware connections serialise behind each other (measured:
- * 8 x 4 elements queued 300 frames deep ran at 13 k frames/s; bounded to three frames in flight
- * per element the same chain is HBM-bound).  Three blocks let producer, consumer and the next
- * frame overlap. */
+ * 8 pipelines x 4 elements queued 300 frames deep ran at 13 k frames/s).  The depth also decides
+ * how far apart in time a tensor's producer and consumer run, i.e. whether the consumer still
+ * finds it in the 126 MB L2: 8 x 1080p converter -> typecast -> arithmetic -> transpose chains
+ * gave 48.3 / 43.1 / 34.0 / 36.4 k frames/s at depth 1 / 2 / 3 / 4 (profiles/r2_pool_depth.md),
+ * so the default is 1: an element starts its next buffer when its consumer is done with the
+ * previous one.  NNSB_POOL_DEPTH overrides. */
 static int
 pool_depth ()
 {
   static int depth = 0;
   if (depth == 0) {
     const char *env = getenv ("NNSB_POOL_DEPTH");
-    depth = (env && atoi (env) > 0) ? atoi (env) : 3;
+    depth = (env && atoi (env) > 0) ? atoi (env) : 1;
   }
   return depth;
 }
