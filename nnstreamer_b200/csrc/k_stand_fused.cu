@@ -1,15 +1,20 @@
 /*
  * k_stand_fused.cu -- stand (standardisation) of a BATCH of float32 tensors with ONE read of
- * the input from HBM: a persistent, warp-specialised kernel that keeps each tensor resident in
- * shared memory between its statistics pass and its normalisation pass.
+ * the input from HBM: a persistent, warp-specialised kernel that keeps each tensor on the SMs
+ * between its statistics pass and its normalisation pass -- alternately in shared memory and in
+ * TENSOR MEMORY (TMEM), so that two tensors are resident at any time.
  *
  * Reference semantics: gst_tensor_transform_stand (gsttensor_transform.c:1512-1619) +
  * gst_tensor_data_raw_average / _std [_per_channel] (tensor_data.c:314-493), see k_stand.cuh.
  *
  * Why: the three-launch scheme (k_stand.cuh) reads the input twice -- 12 B of DRAM traffic per
  * element for 8 algorithmic bytes -- and is therefore capped at 2/3 of the HBM roof.  A 1080p
- * RGB float32 frame is 24.9 MB; split over the 148 SMs that is 168 KB per SM, which FITS in the
- * 227 KB of shared memory of one CTA.  So:
+ * RGB float32 frame is 24.9 MB; split over the 148 SMs that is 168 KB per SM, which fits in the
+ * 227 KB of shared memory of one CTA -- but only once, and the statistics of a tensor need a
+ * grid-wide reduction (~3 us of latency) before it can be normalised; with one resident tensor
+ * the SMs sit idle during it (measured: 13.6 us per tensor, 3.6 TB/s).  The 256 KB of tensor
+ * memory next to the tensor cores are idle in this library (nothing here is a contraction), and
+ * tcgen05.st / tcgen05.ld move registers to and from it.  So:
  *
  *   grid    one CTA per SM, launched cooperatively (all CTAs must be co-resident: they wait for
  *           one another); CTA b owns the same slice of every tensor of the batch: tiles
@@ -17,34 +22,38 @@
  *           and of the thread strides below, so a thread's channel phase never changes).
  *   ring    NSLOT = 18 tile slots of shared memory, one `full` and one `empty` mbarrier each.
  *   warp 0  (producer) one elected thread issues cp.async.bulk global -> shared for the tiles of
- *           tensor f, f+1, ... in order as slots become empty, and -- LOOKAHEAD tiles ahead -- a
- *           cp.async.bulk.prefetch.L2 so that HBM keeps streaming into L2 while the ring is
- *           full (during the cross-CTA hand-shake below); L2 is the second buffer.
- *   6 warps (statistics) read every tile once as it lands: fp64 sum (x - K) and sum (x - K)^2
- *           per channel, K = first element of the channel (same shifted one-pass formula as
- *           k_stand.cuh).  After the last tile of tensor f each warp leaves its sums in shared
- *           memory, arrives on `stats_done[f & 1]` and goes on with tensor f + 1.
- *   warp 1  (control) adds the six warp sums, writes the CTA's partial to global scratch and
- *           bumps ONE counter per tensor (fence + atomicAdd); lane 0 polls that counter until all
- *           CTAs have arrived, then the warp reads the 148 partials (coalesced, L2) and folds
- *           them in a fixed order -- every CTA computes the same bits -- into {mean, 1/std} in
- *           shared memory, and arrives on `ready[f & 1]`.
- *   12 warps (normalisation) wait for `ready`, read the tiles of tensor f from shared memory
- *           again, fp64 (x - mean) * (1 / std), |.|, convert, 128-bit stores to global, and free
- *           the slot (arrive on `empty`): the producer refills it with tensor f+1.
+ *           tensor 0, 1, 2, ... in order as slots become empty (+ an L2 prefetch a few tiles ahead).
+ *   8 warps (statistics) read every tile once as it lands: fp64 sum (x - K) and sum (x - K)^2
+ *           per channel, K = first element of the channel (the shifted one-pass formula of
+ *           k_stand.cuh).  EVEN tensors are parked in TMEM: the values just loaded go there with
+ *           tcgen05.st and the shared-memory slot is freed at once (the ring is only a FIFO for
+ *           them).  ODD tensors stay in their 13-14 ring slots.  After the last tile each warp
+ *           leaves its sums in shared memory and arrives on `stats_done[f & 1]`.
+ *   warp 1  (control) adds the warp sums, writes the CTA's partial to global scratch and bumps one
+ *           counter per tensor (fence + atomicAdd); lane 0 polls it until all CTAs have arrived,
+ *           then the warp reads the 148 partials (L2) and folds them in a fixed order -- every CTA
+ *           computes the same bits -- into {mean, 1/std}, and arrives on `ready[f & 1]`.
+ *   8 warps (normalisation) wait for `ready`, fetch the tensor's tiles again -- tcgen05.ld from
+ *           TMEM (even) or ld.shared from the ring (odd, freeing the slot) -- fp64
+ *           (x - mean) * (1 / std), |.|, convert, 128-bit stores to global.
  *
- * DRAM traffic: one read + one write = the algorithmic 8 B/element.  The statistics warps run
- * one tensor ahead of the normalisation warps, so the only serial gap per tensor is the counter
- * hand-shake (~1.5 us), during which the L2 prefetch keeps HBM busy.
+ * While tensor f is normalised out of one memory, tensor f + 1 is loaded, reduced and
+ * hand-shaken in the other: the grid-wide latency is off the critical path, and DRAM sees one
+ * read + one write = the algorithmic 8 B/element.  A thread of a statistics warp and the thread
+ * of a normalisation warp with the same (warp % 4, lane) own the same vectors of every tile
+ * (a warp reaches only its own quarter of the TMEM lanes), which also fixes the TMEM layout:
+ * tile j = columns [24 j, 24 j + 24), 128 lanes x 24 words = 3072 elements.
  *
  * Restrictions (else the three-launch path is used, nnsb_runtime.cu): float32 in and out,
- * 1..4 channels, frame_elems % 4 == 0, 16-byte aligned bases, 4 <= tiles per CTA <= NSLOT - 2.
+ * 1..4 channels, frame_elems % 4 == 0, 16-byte aligned bases, 4 <= tiles per CTA <= 16.
  * Summation order differs from k_stand.cuh (tiles instead of a grid-stride), so results agree
  * with it within stand's tolerance, not bit for bit; the normalisation arithmetic is identical.
  */
 #include <cuda_runtime.h>
 
+#include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 #include "nnsb_device.cuh"
 #include "nnsb_kernels.h"
@@ -55,12 +64,15 @@ namespace {
 
 constexpr int TILE = 3072;                      /* elements per tile */
 constexpr int TILE_BYTES = TILE * 4;
-constexpr int TILE_VECS = TILE / 4;             /* float4 per tile: 768 */
 constexpr int NSLOT = 18;
-constexpr int STATS_WARPS = 6, APPLY_WARPS = 12;
-constexpr int STATS_THREADS = STATS_WARPS * 32;         /* 192: 4 vectors per tile and thread */
-constexpr int APPLY_THREADS = APPLY_WARPS * 32;         /* 384: 2 vectors per tile and thread */
-constexpr int THREADS = 64 + STATS_THREADS + APPLY_THREADS;     /* producer + control + ... */
+constexpr int MAX_TILES = 16;                   /* per CTA and tensor: NSLOT - 2, and 24 * 16 <= 512 TMEM columns */
+constexpr int STATS_WARPS = 8, APPLY_WARPS = 8; /* two of each per TMEM lane quarter */
+constexpr int STATS_THREADS = STATS_WARPS * 32;
+constexpr int APPLY_THREADS = APPLY_WARPS * 32;
+constexpr int THREADS = 64 + STATS_THREADS + APPLY_THREADS;     /* producer + control + ... = 576 */
+constexpr int VPT = 3;                          /* vectors per tile and thread: 768 / 256 */
+constexpr int TILE_COLS = 24;                   /* TMEM columns per tile: 2 halves x VPT x 4 words */
+constexpr int TMEM_COLS = 512;
 constexpr int MAX_CTAS = 160;
 constexpr int PUB_SLOTS = 4;                    /* scratch slots cycled by tensor index */
 constexpr int LOOKAHEAD_DEFAULT = 8;            /* tiles the L2 prefetch runs ahead of the ring */
@@ -111,6 +123,22 @@ __device__ __forceinline__ uint32_t ld_acquire_u32 (const uint32_t *p)
   asm volatile ("ld.acquire.gpu.global.u32 %0, [%1];" : "=r" (v) : "l" (p) : "memory");
   return v;
 }
+/* tensor memory: a warp reaches lanes [32 (warp % 4), +32); thread i of the warp = lane 32 q + i,
+ * four consecutive 32-bit columns per instruction */
+__device__ __forceinline__ void tmem_st4 (uint32_t taddr, const float4 &v)
+{
+  asm volatile ("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
+      :: "r" (taddr), "r" (__float_as_uint (v.x)), "r" (__float_as_uint (v.y)),
+         "r" (__float_as_uint (v.z)), "r" (__float_as_uint (v.w)) : "memory");
+}
+__device__ __forceinline__ float4 tmem_ld4 (uint32_t taddr)
+{
+  uint32_t a, b, c, d;
+  asm volatile ("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+      : "=r" (a), "=r" (b), "=r" (c), "=r" (d) : "r" (taddr) : "memory");
+  return make_float4 (__uint_as_float (a), __uint_as_float (b), __uint_as_float (c), __uint_as_float (d));
+}
+
 struct FusedArgs
 {
   const float *in;
@@ -124,16 +152,38 @@ struct FusedArgs
   uint32_t lookahead;
   double *stats;                /* [batch][nch][2] = {mean, std}, for nnsb_plan_stand_stats */
   int default_mode;
+  unsigned long long *dbg;      /* NNSB_STAND_TRACE: [cta][tensor][TRACE_POINTS] globaltimer ns, else NULL */
 };
+
+constexpr int TRACE_POINTS = 10;
+__device__ __forceinline__ void
+trace (const FusedArgs &a, uint32_t cta, uint32_t f, int point)
+{
+  if (a.dbg) {
+    unsigned long long t;
+    asm volatile ("mov.u64 %0, %%globaltimer;" : "=l" (t));
+    a.dbg[((size_t) cta * a.batch + f) * TRACE_POINTS + point] = t;
+  }
+}
 
 struct __align__ (16) Shared
 {
   uint64_t full[NSLOT], empty[NSLOT];
   uint64_t ready[2];            /* {mean, 1/std} of tensor f is in ms[f & 1] */
-  uint64_t stats_done[2];       /* the six warp sums of tensor f are in red[f & 1] */
+  uint64_t stats_done[2];       /* the warp sums of tensor f are in red[f & 1] */
+  uint64_t tmem_free;           /* the normalisation warps are done with the tensor in TMEM */
   double ms[2][4][2];           /* mean, 1/std per channel */
   double red[2][2][4][STATS_WARPS];
+  uint32_t tmem_base;
 };
+
+/* one element: the arithmetic of stand_one (k_stand.cuh) */
+template <bool DEFAULT_MODE> __device__ __forceinline__ float
+norm_one (float x, double mean, double rsd)
+{
+  const double d = __dsub_rn ((double) x, mean);
+  return DEFAULT_MODE ? (float) fabs (__dmul_rn (d, rsd)) : (float) d;
+}
 
 template <int NCH>
 __global__ void __launch_bounds__ (THREADS, 1)
@@ -151,15 +201,25 @@ stand_fused_kernel (FusedArgs a)
   if (threadIdx.x == 0) {
     for (int s = 0; s < NSLOT; s++) {
       mbar_init (&sh.full[s], 1);
-      mbar_init (&sh.empty[s], APPLY_WARPS);
+      mbar_init (&sh.empty[s], STATS_WARPS);    /* even tensors: freed by the statistics warps,
+                                                 * odd ones by the (as many) normalisation warps */
     }
     mbar_init (&sh.ready[0], 1);
     mbar_init (&sh.ready[1], 1);
     mbar_init (&sh.stats_done[0], STATS_WARPS);
     mbar_init (&sh.stats_done[1], STATS_WARPS);
+    mbar_init (&sh.tmem_free, APPLY_WARPS);
     asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  if (warp == 1) {
+    /* all 512 columns: this CTA has the SM to itself */
+    asm volatile ("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+        :: "r" (smem_u32 (&sh.tmem_base)), "n" (TMEM_COLS) : "memory");
+    asm volatile ("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile ("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads ();
+  asm volatile ("tcgen05.fence::after_thread_sync;" ::: "memory");
 
   /* elements of tile t of a tensor: all tiles are full except possibly the last one.  (No
    * division anywhere below: slot and phase of the ring advance incrementally -- a 64-bit
@@ -167,6 +227,18 @@ stand_fused_kernel (FusedArgs a)
   const uint32_t last_tile = a.n_tiles - 1;
   const uint32_t last_elems = (uint32_t) (a.frame_elems - (uint64_t) last_tile * TILE);
   auto tile_elems = [&] (uint32_t t) -> uint32_t { return t == last_tile ? last_elems : (uint32_t) TILE; };
+
+  /* statistics warp 2 + i and normalisation warp 10 + i: TMEM quarter q = warp % 4, half h = i / 4;
+   * thread (q, h, lane) owns the vectors v = 192 q + 96 h + 32 k + lane, k = 0..2, of every tile,
+   * kept in TMEM columns 24 j + 12 h + 4 k .. + 3 of lanes 32 q + lane */
+  const uint32_t role_idx = warp >= 2 + STATS_WARPS ? warp - 2 - STATS_WARPS : warp - 2;
+  const uint32_t quarter = warp & 3, half = (role_idx >> 2) & 1;
+  const uint32_t v0 = quarter * 192 + half * 96 + lane;
+  const uint32_t tmem_thread = sh.tmem_base + ((quarter * 32) << 16) + half * 12;
+  /* lane k' of vector v0 + 32 k belongs to channel (4 v0 + 128 k + k') % NCH = (c0 + 2 k + k') % NCH
+   * for 3 channels (128 = 2 mod 3) and (c0 + k') % NCH for 1, 2, 4 */
+  const uint32_t c0 = (v0 * 4) % NCH;
+  constexpr int KROT = (NCH == 3) ? 2 : 0;
 
   if (warp == 0) {
     /* ------------------------------ producer ------------------------------ */
@@ -194,7 +266,10 @@ stand_fused_kernel (FusedArgs a)
         mbar_expect_tx (&sh.full[s], bytes);
         bulk_g2s (ring + (size_t) s * TILE, a.in + (uint64_t) f * a.frame_elems + (uint64_t) t * TILE,
             bytes, &sh.full[s]);
+        if (j == 0)
+          trace (a, cta, f, 8);
         if (++j == my_tiles) {
+          trace (a, cta, f, 9);
           j = 0;
           f++;
         }
@@ -204,14 +279,15 @@ stand_fused_kernel (FusedArgs a)
         }
       }
     }
-    return;
-  }
-
-  if (warp == 1) {
+  } else if (warp == 1) {
     /* ------------------------------ control ------------------------------ */
     for (uint32_t f = 0; f < a.batch; f++) {
       const uint32_t pub = f % PUB_SLOTS;
+      const float *base = a.in + (uint64_t) f * a.frame_elems;
+      const double k0 = lane < NCH ? (double) __ldg (base + lane) : 0.0;       /* issued early */
       mbar_wait (&sh.stats_done[f & 1], (f >> 1) & 1);
+      if (lane == 0)
+        trace (a, cta, f, 4);
       /* lane (c, k): channel c, k = 0 sum / 1 sum of squares */
       if (lane < NCH * 2) {
         const uint32_t c = lane >> 1, k = lane & 1;
@@ -225,10 +301,12 @@ stand_fused_kernel (FusedArgs a)
       if (lane == 0) {
         __threadfence ();
         atomicAdd (a.counter + pub * 32, 1u);
+        trace (a, cta, f, 5);
         /* this slot's (f / PUB_SLOTS)-th use: everybody has arrived at n_cta * (uses so far) */
         const uint32_t target = n_cta * (f / PUB_SLOTS + 1);
         while (ld_acquire_u32 (a.counter + pub * 32) < target)
           __nanosleep (32);
+        trace (a, cta, f, 6);
       }
       __syncwarp ();
       /* fold the n_cta partials: lane l takes CTAs l, l + 32, ... in order, then a fixed
@@ -260,9 +338,7 @@ stand_fused_kernel (FusedArgs a)
             s1 = tot[c][0];
             s2 = tot[c][1];
           }
-        const float *base = a.in + (uint64_t) f * a.frame_elems;
         const double n = (double) (a.frame_elems / NCH);
-        const double k0 = (double) __ldg (base + lane);
         const double mean = k0 + s1 / n;
         double sd = 0.0;
         if (a.default_mode) {
@@ -270,8 +346,8 @@ stand_fused_kernel (FusedArgs a)
           /* tensor_data.c:438,488: std = (sum != 0) ? sqrt (sum) : 1e-10 */
           sd = (var > 0.0) ? sqrt (var) : 1e-10;
         }
-        /* ms[f & 1] was last read by the normalisation of tensor f - 2, which finished before
-         * the slots of tensor f could be filled */
+        /* ms[f & 1] was last read by the normalisation of tensor f - 2: tensor f can only be
+         * loaded into the memory tensor f - 2 lived in once that has finished */
         sh.ms[f & 1][lane][0] = mean;
         sh.ms[f & 1][lane][1] = a.default_mode ? __drcp_rn (sd) : 0.0;
         if (cta == 0) {
@@ -280,22 +356,17 @@ stand_fused_kernel (FusedArgs a)
         }
       }
       __syncwarp ();
-      if (lane == 0)
+      if (lane == 0) {
+        trace (a, cta, f, 7);
         mbar_arrive (&sh.ready[f & 1]);
+      }
     }
-    return;
-  }
-
-  if (warp < 2 + STATS_WARPS) {
+  } else if (warp < 2 + STATS_WARPS) {
     /* ------------------------------ statistics ------------------------------ */
-    const uint32_t tid = threadIdx.x - 64;                      /* 0..191 */
-    const uint32_t swarp = tid >> 5;
-    /* vector v = tid + i * 192 of a tile: its lane k belongs to channel (c0 + k) % NCH; 192 and
-     * TILE are multiples of 3 and 4, so c0 depends on the thread only */
-    const uint32_t c0 = (tid * 4) % NCH;
     uint32_t s = 0, phase = 0;                  /* ring slot and mbarrier parity of the next tile */
     for (uint32_t f = 0; f < a.batch; f++) {
       const float *base = a.in + (uint64_t) f * a.frame_elems;
+      const bool to_tmem = (f & 1) == 0;
       double kk[NCH], a1[NCH], a2[NCH];
 #pragma unroll
       for (int r = 0; r < NCH; r++) {
@@ -303,32 +374,55 @@ stand_fused_kernel (FusedArgs a)
         a1[r] = 0.0;
         a2[r] = 0.0;
       }
+      if (to_tmem && f >= 2) {
+        /* the tensor parked in TMEM two tensors ago must have been normalised */
+        mbar_wait (&sh.tmem_free, ((f >> 1) - 1) & 1);
+        asm volatile ("tcgen05.fence::after_thread_sync;" ::: "memory");
+      }
       for (uint32_t j = 0; j < my_tiles; j++) {
         mbar_wait (&sh.full[s], phase);
+        if (role_idx == 0 && lane == 0 && j + 1 == my_tiles)
+          trace (a, cta, f, 2);
         const float4 *tile = reinterpret_cast<const float4 *> (ring + (size_t) s * TILE);
         const uint32_t nv = tile_elems (first_tile + j) / 4;
+        uint64_t *const empty_bar = &sh.empty[s];
         if (++s == NSLOT) {
           s = 0;
           phase ^= 1;
         }
-        float4 x[4];
+        float4 x[VPT];
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-          const uint32_t v = tid + i * STATS_THREADS;
-          x[i] = v < nv ? tile[v] : make_float4 (0.f, 0.f, 0.f, 0.f);
+        for (int k = 0; k < VPT; k++) {
+          const uint32_t v = v0 + 32 * k;
+          x[k] = v < nv ? tile[v] : make_float4 (0.f, 0.f, 0.f, 0.f);
+        }
+        if (to_tmem) {
+          __syncwarp ();                        /* the spin loop above may have split the warp */
+#pragma unroll
+          for (int k = 0; k < VPT; k++)
+            tmem_st4 (tmem_thread + j * TILE_COLS + 4 * k, x[k]);
         }
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-          const uint32_t v = tid + i * STATS_THREADS;
+        for (int k = 0; k < VPT; k++) {
+          const uint32_t v = v0 + 32 * k;
           if (v < nv) {
-            const float e[4] = { x[i].x, x[i].y, x[i].z, x[i].w };
+            const float e[4] = { x[k].x, x[k].y, x[k].z, x[k].w };
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-              const double d = __dsub_rn ((double) e[k], kk[k % NCH]);
-              a1[k % NCH] += d;
-              a2[k % NCH] = fma (d, d, a2[k % NCH]);
+            for (int i = 0; i < 4; i++) {
+              const int r = (KROT * k + i) % NCH;
+              const double d = __dsub_rn ((double) e[i], kk[r]);
+              a1[r] += d;
+              a2[r] = fma (d, d, a2[r]);
             }
           }
+        }
+        if (to_tmem) {
+          /* the ring slot is only a FIFO for this tensor: free it as soon as the copy is out */
+          __syncwarp ();
+          asm volatile ("tcgen05.wait::st.sync.aligned;" ::: "memory");
+          __syncwarp ();
+          if (lane == 0)
+            mbar_arrive (empty_bar);
         }
       }
       /* actual-channel order, a fixed shuffle tree per warp; the control warp adds the warps.
@@ -348,24 +442,29 @@ stand_fused_kernel (FusedArgs a)
           s2 += __shfl_xor_sync (0xffffffffu, s2, o);
         }
         if (lane == 0) {
-          sh.red[f & 1][0][c][swarp] = s1;
-          sh.red[f & 1][1][c][swarp] = s2;
+          sh.red[f & 1][0][c][role_idx] = s1;
+          sh.red[f & 1][1][c][role_idx] = s2;
         }
       }
+      if (to_tmem)
+        asm volatile ("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp ();
+      if (role_idx == 0 && lane == 0)
+        trace (a, cta, f, 3);
       if (lane == 0)
         mbar_arrive (&sh.stats_done[f & 1]);
     }
-    return;
-  }
-
-  /* ------------------------------ normalisation ------------------------------ */
-  {
-    const uint32_t tid = threadIdx.x - 64 - STATS_THREADS;      /* 0..383 */
-    const uint32_t c0 = (tid * 4) % NCH;                        /* 384 is a multiple of 3 and 4 too */
+  } else {
+    /* ------------------------------ normalisation ------------------------------ */
+    /* ring slot of the next ODD tensor's first tile: advances over the even tensors too */
     uint32_t s = 0;
     for (uint32_t f = 0; f < a.batch; f++) {
+      const bool from_tmem = (f & 1) == 0;
       mbar_wait (&sh.ready[f & 1], (f >> 1) & 1);
+      if (role_idx == 0 && lane == 0)
+        trace (a, cta, f, 0);
+      if (from_tmem)
+        asm volatile ("tcgen05.fence::after_thread_sync;" ::: "memory");
       double mean[NCH], rsd[NCH];
 #pragma unroll
       for (int r = 0; r < NCH; r++) {
@@ -381,35 +480,62 @@ stand_fused_kernel (FusedArgs a)
         const uint32_t t = first_tile + j;
         const uint32_t nv = tile_elems (t) / 4;
         float4 *dst = reinterpret_cast<float4 *> (obase + (uint64_t) t * TILE);
-        float4 x[2];
+        float4 x[VPT];
+        if (from_tmem) {
+          __syncwarp ();
 #pragma unroll
-        for (int i = 0; i < 2; i++) {
-          const uint32_t v = tid + i * APPLY_THREADS;
-          x[i] = v < nv ? tile[v] : make_float4 (0.f, 0.f, 0.f, 0.f);
+          for (int k = 0; k < VPT; k++)
+            x[k] = tmem_ld4 (tmem_thread + j * TILE_COLS + 4 * k);
+          asm volatile ("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        } else {
+#pragma unroll
+          for (int k = 0; k < VPT; k++) {
+            const uint32_t v = v0 + 32 * k;
+            x[k] = v < nv ? tile[v] : make_float4 (0.f, 0.f, 0.f, 0.f);
+          }
+          /* the values are in registers: the slot can be refilled while we compute and store */
+          __syncwarp ();
+          if (lane == 0)
+            mbar_arrive (empty_bar);
         }
-        /* the values are in registers: the slot can be refilled while we compute and store */
-        __syncwarp ();
-        if (lane == 0)
-          mbar_arrive (empty_bar);
 #pragma unroll
-        for (int i = 0; i < 2; i++) {
-          const uint32_t v = tid + i * APPLY_THREADS;
+        for (int k = 0; k < VPT; k++) {
+          const uint32_t v = v0 + 32 * k;
           if (v < nv) {
-            const float e[4] = { x[i].x, x[i].y, x[i].z, x[i].w };
+            const float e[4] = { x[k].x, x[k].y, x[k].z, x[k].w };
             float y[4];
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-              const double d = __dsub_rn ((double) e[k], mean[k % NCH]);
-              y[k] = a.default_mode ? (float) fabs (__dmul_rn (d, rsd[k % NCH])) : (float) d;
+            for (int i = 0; i < 4; i++) {
+              const int r = (KROT * k + i) % NCH;
+              y[i] = a.default_mode ? norm_one<true> (e[i], mean[r], rsd[r])
+                  : norm_one<false> (e[i], mean[r], rsd[r]);
             }
-            uint32_t w[4] = { __float_as_uint (y[0]), __float_as_uint (y[1]), __float_as_uint (y[2]),
-              __float_as_uint (y[3]) };
             asm volatile ("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
-                :: "l" (dst + v), "r" (w[0]), "r" (w[1]), "r" (w[2]), "r" (w[3]) : "memory");
+                :: "l" (dst + v), "r" (__float_as_uint (y[0])), "r" (__float_as_uint (y[1])),
+                   "r" (__float_as_uint (y[2])), "r" (__float_as_uint (y[3])) : "memory");
           }
         }
       }
+      if (from_tmem) {
+        /* TMEM may be overwritten by the tensor after next */
+        asm volatile ("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp ();
+        if (lane == 0)
+          mbar_arrive (&sh.tmem_free);
+      }
+      if (role_idx == 0 && lane == 0)
+        trace (a, cta, f, 1);
     }
+  }
+
+  /* everybody is done with TMEM: give it back */
+  __syncwarp ();
+  asm volatile ("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads ();
+  if (warp == 1) {
+    asm volatile ("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile ("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;"
+        :: "r" (sh.tmem_base), "n" (TMEM_COLS) : "memory");
   }
 }
 
@@ -434,8 +560,8 @@ geometry (size_t frame_elems, const LaunchCfg &cfg, Geometry *g)
   if (n_tiles < grid * 4)
     return false;               /* too little work per CTA: the hand-shake would dominate */
   const uint64_t lo = n_tiles / grid, hi = n_tiles % grid;
-  if (lo + (hi ? 1 : 0) > (uint64_t) NSLOT - 2)
-    return false;               /* the slice must fit in the ring with two slots to spare */
+  if (lo + (hi ? 1 : 0) > (uint64_t) MAX_TILES)
+    return false;               /* the slice must fit in the ring (with two slots to spare) and in TMEM */
   g->n_tiles = (uint32_t) n_tiles;
   g->grid = (uint32_t) grid;
   g->tiles_lo = (uint32_t) lo;
@@ -514,6 +640,11 @@ launch_stand_fused (int stand_mode, const void *in, void *out, size_t frame_elem
     a.lookahead = (uint32_t) atoi (env);
   a.stats = stats;
   a.default_mode = stand_mode == NNSB_STAND_DEFAULT;
+  a.dbg = nullptr;
+  const char *trace_path = getenv ("NNSB_STAND_TRACE");
+  const size_t trace_n = (size_t) g.grid * batch * TRACE_POINTS;
+  if (trace_path && cudaMalloc ((void **) &a.dbg, trace_n * 8) == cudaSuccess)
+    cudaMemsetAsync (a.dbg, 0, trace_n * 8, stream);
   int err;
   switch (nch) {
     case 1: err = launch_n<1> (a, g.grid, stream); break;
@@ -521,6 +652,19 @@ launch_stand_fused (int stand_mode, const void *in, void *out, size_t frame_elem
     case 3: err = launch_n<3> (a, g.grid, stream); break;
     case 4: err = launch_n<4> (a, g.grid, stream); break;
     default: err = (int) cudaErrorInvalidValue; break;
+  }
+  if (a.dbg) {
+    /* developer aid (profiles/): per CTA and tensor, when each role reached each point */
+    std::vector<unsigned long long> h (trace_n);
+    cudaStreamSynchronize (stream);
+    cudaMemcpy (h.data (), a.dbg, trace_n * 8, cudaMemcpyDeviceToHost);
+    cudaFree (a.dbg);
+    if (FILE *fp = fopen (trace_path, "wb")) {
+      const unsigned long long hdr[3] = { g.grid, batch, (unsigned long long) TRACE_POINTS };
+      fwrite (hdr, 8, 3, fp);
+      fwrite (h.data (), 8, trace_n, fp);
+      fclose (fp);
+    }
   }
   if (n_launches)
     *n_launches = 1;
