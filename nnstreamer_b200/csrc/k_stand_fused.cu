@@ -1,8 +1,8 @@
 /*
  * k_stand_fused.cu -- stand (standardisation) of a BATCH of float32 tensors with ONE read of
  * the input from HBM: a persistent, warp-specialised kernel that keeps each tensor on the SMs
- * between its statistics pass and its normalisation pass -- alternately in shared memory and in
- * TENSOR MEMORY (TMEM), so that two tensors are resident at any time.
+ * between its statistics pass and its normalisation pass -- in shared memory AND in TENSOR
+ * MEMORY (TMEM), so that two and a half tensors are resident at any time.
  *
  * Reference semantics: gst_tensor_transform_stand (gsttensor_transform.c:1512-1619) +
  * gst_tensor_data_raw_average / _std [_per_channel] (tensor_data.c:314-493), see k_stand.cuh.
@@ -20,29 +20,34 @@
  *           one another); CTA b owns the same slice of every tensor of the batch: tiles
  *           [first_b, first_b + n_b) of TILE = 3072 elements (12 KB; a multiple of 1..4 channels
  *           and of the thread strides below, so a thread's channel phase never changes).
- *   ring    NSLOT = 18 tile slots of shared memory, one `full` and one `empty` mbarrier each.
+ *   places  a tile of a tensor is PARKED, from the moment it is loaded until it has been
+ *           normalised, in one of 35 places that are used round robin: 21 in TMEM (24 columns x
+ *           128 lanes each) and 14 in shared memory.  35 places = 2.5 tensors of 13-14 tiles: the
+ *           loads run up to 2.5 tensors ahead of the normalisation, which takes the grid-wide
+ *           reduction off the critical path.  Four more shared-memory slots are the landing
+ *           FIFO of the tiles bound for TMEM.  Every place / slot has its mbarrier(s).
  *   warp 0  (producer) one elected thread issues cp.async.bulk global -> shared for the tiles of
- *           tensor 0, 1, 2, ... in order as slots become empty (+ an L2 prefetch a few tiles ahead).
+ *           tensor 0, 1, 2, ... in order as their place (or a landing slot) becomes free (+ an L2
+ *           prefetch a few tiles ahead).
  *   8 warps (statistics) read every tile once as it lands: fp64 sum (x - K) and sum (x - K)^2
  *           per channel, K = first element of the channel (the shifted one-pass formula of
- *           k_stand.cuh).  EVEN tensors are parked in TMEM: the values just loaded go there with
- *           tcgen05.st and the shared-memory slot is freed at once (the ring is only a FIFO for
- *           them).  ODD tensors stay in their 13-14 ring slots.  After the last tile each warp
- *           leaves its sums in shared memory and arrives on `stats_done[f & 1]`.
+ *           k_stand.cuh).  Tiles bound for TMEM go there with tcgen05.st straight from the
+ *           registers they were just loaded into, and the landing slot is freed.  After the last
+ *           tile of a tensor each warp leaves its sums in shared memory and arrives on
+ *           `stats_done[f & 1]`.
  *   warp 1  (control) adds the warp sums, writes the CTA's partial to global scratch and bumps one
- *           counter per tensor (fence + atomicAdd); lane 0 polls it until all CTAs have arrived,
- *           then the warp reads the 148 partials (L2) and folds them in a fixed order -- every CTA
- *           computes the same bits -- into {mean, 1/std}, and arrives on `ready[f & 1]`.
+ *           counter per tensor (fence + atomicAdd).  The CTA that arrives LAST reads the 148
+ *           partials, folds them in a fixed order, computes {mean, 1/std} and publishes them
+ *           behind a flag; everybody polls that flag and copies the one result line (148 CTAs
+ *           each reading all partials made the reduction a 4-10 us hot spot in L2).
  *   8 warps (normalisation) wait for `ready`, fetch the tensor's tiles again -- tcgen05.ld from
- *           TMEM (even) or ld.shared from the ring (odd, freeing the slot) -- fp64
+ *           TMEM or ld.shared from a parking slot, freeing the place -- fp64
  *           (x - mean) * (1 / std), |.|, convert, 128-bit stores to global.
  *
- * While tensor f is normalised out of one memory, tensor f + 1 is loaded, reduced and
- * hand-shaken in the other: the grid-wide latency is off the critical path, and DRAM sees one
- * read + one write = the algorithmic 8 B/element.  A thread of a statistics warp and the thread
- * of a normalisation warp with the same (warp % 4, lane) own the same vectors of every tile
- * (a warp reaches only its own quarter of the TMEM lanes), which also fixes the TMEM layout:
- * tile j = columns [24 j, 24 j + 24), 128 lanes x 24 words = 3072 elements.
+ * DRAM sees one read + one write = the algorithmic 8 B/element.  A thread of a statistics warp
+ * and the thread of a normalisation warp with the same (warp % 4, lane) own the same vectors of
+ * every tile (a warp reaches only its own quarter of the TMEM lanes), which also fixes the TMEM
+ * layout: place p = columns [24 p, 24 p + 24), 128 lanes x 24 words = 3072 elements.
  *
  * Restrictions (else the three-launch path is used, nnsb_runtime.cu): float32 in and out,
  * 1..4 channels, frame_elems % 4 == 0, 16-byte aligned bases, 4 <= tiles per CTA <= 16.
@@ -64,8 +69,12 @@ namespace {
 
 constexpr int TILE = 3072;                      /* elements per tile */
 constexpr int TILE_BYTES = TILE * 4;
-constexpr int NSLOT = 18;
-constexpr int MAX_TILES = 16;                   /* per CTA and tensor: NSLOT - 2, and 24 * 16 <= 512 TMEM columns */
+constexpr int LAND = 4;                         /* landing FIFO slots (shared memory) */
+constexpr int PARK = 14;                        /* parking slots in shared memory */
+constexpr int NSLOT = LAND + PARK;              /* 18 x 12 KB */
+constexpr int TPLACES = 21;                     /* parking places in TMEM: 21 x 24 of the 512 columns */
+constexpr int PLACES = TPLACES + PARK;          /* 35 */
+constexpr int MAX_TILES = 16;                   /* per CTA and tensor; must stay well below PLACES */
 constexpr int STATS_WARPS = 8, APPLY_WARPS = 8; /* two of each per TMEM lane quarter */
 constexpr int STATS_THREADS = STATS_WARPS * 32;
 constexpr int APPLY_THREADS = APPLY_WARPS * 32;
@@ -147,8 +156,9 @@ struct FusedArgs
   uint32_t batch;
   uint32_t n_tiles;             /* tiles per tensor (the last one may be short) */
   uint32_t tiles_lo, n_hi;      /* CTAs [0, n_hi) own tiles_lo + 1 tiles, the others tiles_lo */
-  uint32_t *counter;            /* [PUB_SLOTS] (one per 128-byte line), zero on entry */
+  uint32_t *counter;            /* [PUB_SLOTS] arrivals, then [PUB_SLOTS] flags (one per 128-byte line), zero on entry */
   double *partial;              /* [PUB_SLOTS][4][2][gridDim.x] */
+  double *final_ms;             /* [PUB_SLOTS][4][4]: mean, 1/std, std, - */
   uint32_t lookahead;
   double *stats;                /* [batch][nch][2] = {mean, std}, for nnsb_plan_stand_stats */
   int default_mode;
@@ -168,10 +178,11 @@ trace (const FusedArgs &a, uint32_t cta, uint32_t f, int point)
 
 struct __align__ (16) Shared
 {
-  uint64_t full[NSLOT], empty[NSLOT];
+  uint64_t land_full[LAND], land_empty[LAND];
+  uint64_t park_full[PARK], park_empty[PARK];
+  uint64_t tmem_empty[TPLACES]; /* the normalisation warps have read the tile out of that place */
   uint64_t ready[2];            /* {mean, 1/std} of tensor f is in ms[f & 1] */
   uint64_t stats_done[2];       /* the warp sums of tensor f are in red[f & 1] */
-  uint64_t tmem_free;           /* the normalisation warps are done with the tensor in TMEM */
   double ms[2][4][2];           /* mean, 1/std per channel */
   double red[2][2][4][STATS_WARPS];
   uint32_t tmem_base;
@@ -199,16 +210,20 @@ stand_fused_kernel (FusedArgs a)
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < NSLOT; s++) {
-      mbar_init (&sh.full[s], 1);
-      mbar_init (&sh.empty[s], STATS_WARPS);    /* even tensors: freed by the statistics warps,
-                                                 * odd ones by the (as many) normalisation warps */
+    for (int i = 0; i < LAND; i++) {
+      mbar_init (&sh.land_full[i], 1);
+      mbar_init (&sh.land_empty[i], STATS_WARPS);
     }
+    for (int i = 0; i < PARK; i++) {
+      mbar_init (&sh.park_full[i], 1);
+      mbar_init (&sh.park_empty[i], APPLY_WARPS);
+    }
+    for (int i = 0; i < TPLACES; i++)
+      mbar_init (&sh.tmem_empty[i], APPLY_WARPS);
     mbar_init (&sh.ready[0], 1);
     mbar_init (&sh.ready[1], 1);
     mbar_init (&sh.stats_done[0], STATS_WARPS);
     mbar_init (&sh.stats_done[1], STATS_WARPS);
-    mbar_init (&sh.tmem_free, APPLY_WARPS);
     asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -228,6 +243,13 @@ stand_fused_kernel (FusedArgs a)
   const uint32_t last_elems = (uint32_t) (a.frame_elems - (uint64_t) last_tile * TILE);
   auto tile_elems = [&] (uint32_t t) -> uint32_t { return t == last_tile ? last_elems : (uint32_t) TILE; };
 
+  /* Places in use: two and a half tensors' worth of tiles, TMEM first.  Not more: the control
+   * warp reuses ms[f & 1] / ready[f & 1] for tensor f + 2, which is safe because tensor f + 2
+   * cannot be loaded completely before every normalisation warp has freed the first tiles of
+   * tensor f -- i.e. has long read ms[f & 1]. */
+  const uint32_t n_places = (5 * my_tiles / 2 < (uint32_t) PLACES) ? 5 * my_tiles / 2 : (uint32_t) PLACES;
+  const uint32_t n_tplaces = n_places < (uint32_t) TPLACES ? n_places : (uint32_t) TPLACES;
+
   /* statistics warp 2 + i and normalisation warp 10 + i: TMEM quarter q = warp % 4, half h = i / 4;
    * thread (q, h, lane) owns the vectors v = 192 q + 96 h + 32 k + lane, k = 0..2, of every tile,
    * kept in TMEM columns 24 j + 12 h + 4 k .. + 3 of lanes 32 q + lane */
@@ -246,7 +268,9 @@ stand_fused_kernel (FusedArgs a)
       const uint32_t total = a.batch * my_tiles;        /* tiles this CTA moves (fits 32 bits) */
       /* the L2 prefetch cursor (tensor pf_f, tile pf_j) runs `lookahead` tiles ahead of q */
       uint32_t pf = 0, pf_f = 0, pf_j = 0;
-      uint32_t f = 0, j = 0, s = 0, round = 0;
+      /* the tile sequence walks the 35 places round robin: pl = place, cyc = how often it has
+       * been used; ls / lround the same for the landing slots of the TMEM-bound tiles */
+      uint32_t f = 0, j = 0, pl = 0, cyc = 0, ls = 0, lround = 0;
       for (uint32_t q = 0; q < total; q++) {
         const uint32_t pf_end = (total - q > a.lookahead) ? q + a.lookahead : total;
         for (; pf < pf_end; pf++) {
@@ -259,23 +283,39 @@ stand_fused_kernel (FusedArgs a)
             pf_f++;
           }
         }
-        if (round)
-          mbar_wait (&sh.empty[s], (round - 1) & 1);
+        uint64_t *full;
+        uint32_t slot;
+        if (pl < n_tplaces) {
+          if (lround)
+            mbar_wait (&sh.land_empty[ls], (lround - 1) & 1);
+          full = &sh.land_full[ls];
+          slot = ls;
+          if (++ls == LAND) {
+            ls = 0;
+            lround++;
+          }
+        } else {
+          const uint32_t ps = pl - n_tplaces;
+          if (cyc)
+            mbar_wait (&sh.park_empty[ps], (cyc - 1) & 1);
+          full = &sh.park_full[ps];
+          slot = LAND + ps;
+        }
+        if (++pl == n_places) {
+          pl = 0;
+          cyc++;
+        }
         const uint32_t t = first_tile + j;
         const uint32_t bytes = tile_elems (t) * 4;
-        mbar_expect_tx (&sh.full[s], bytes);
-        bulk_g2s (ring + (size_t) s * TILE, a.in + (uint64_t) f * a.frame_elems + (uint64_t) t * TILE,
-            bytes, &sh.full[s]);
+        mbar_expect_tx (full, bytes);
+        bulk_g2s (ring + (size_t) slot * TILE, a.in + (uint64_t) f * a.frame_elems + (uint64_t) t * TILE,
+            bytes, full);
         if (j == 0)
           trace (a, cta, f, 8);
         if (++j == my_tiles) {
           trace (a, cta, f, 9);
           j = 0;
           f++;
-        }
-        if (++s == NSLOT) {
-          s = 0;
-          round++;
         }
       }
     }
@@ -298,62 +338,80 @@ stand_fused_kernel (FusedArgs a)
         a.partial[(((size_t) pub * 4 + c) * 2 + k) * n_cta + cta] = t;
       }
       __syncwarp ();
+      uint32_t last = 0;
       if (lane == 0) {
         __threadfence ();
-        atomicAdd (a.counter + pub * 32, 1u);
-        trace (a, cta, f, 5);
         /* this slot's (f / PUB_SLOTS)-th use: everybody has arrived at n_cta * (uses so far) */
         const uint32_t target = n_cta * (f / PUB_SLOTS + 1);
-        while (ld_acquire_u32 (a.counter + pub * 32) < target)
+        last = atomicAdd (a.counter + pub * 32, 1u) == target - 1;
+        trace (a, cta, f, 5);
+      }
+      last = __shfl_sync (0xffffffffu, last, 0);
+      if (last) {
+        /* the last CTA to arrive folds the n_cta partials: lane l takes CTAs l, l + 32, ... in
+         * order, then a fixed shuffle tree -- the result does not depend on who is last */
+        __threadfence ();
+        double tot[NCH][2];
+#pragma unroll
+        for (int c = 0; c < NCH; c++)
+#pragma unroll
+          for (int k = 0; k < 2; k++) {
+            const double *p = a.partial + (((size_t) pub * 4 + c) * 2 + k) * n_cta;
+            double v[(MAX_CTAS + 31) / 32];
+#pragma unroll
+            for (int i = 0; i < (MAX_CTAS + 31) / 32; i++)
+              v[i] = (lane + i * 32 < n_cta) ? __ldcg (p + lane + i * 32) : 0.0;
+            double t = 0.0;
+#pragma unroll
+            for (int i = 0; i < (MAX_CTAS + 31) / 32; i++)
+              t += v[i];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+              t += __shfl_xor_sync (0xffffffffu, t, o);
+            tot[c][k] = t;
+          }
+        if (lane < NCH) {
+          double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+          for (int c = 0; c < NCH; c++)
+            if (lane == (uint32_t) c) {
+              s1 = tot[c][0];
+              s2 = tot[c][1];
+            }
+          const double n = (double) (a.frame_elems / NCH);
+          const double mean = k0 + s1 / n;
+          double sd = 0.0;
+          if (a.default_mode) {
+            const double var = (s2 - s1 * (s1 / n)) / n;
+            /* tensor_data.c:438,488: std = (sum != 0) ? sqrt (sum) : 1e-10 */
+            sd = (var > 0.0) ? sqrt (var) : 1e-10;
+          }
+          double *fm = a.final_ms + ((size_t) pub * 4 + lane) * 4;
+          fm[0] = mean;
+          fm[1] = a.default_mode ? __drcp_rn (sd) : 0.0;
+          fm[2] = sd;
+          a.stats[((size_t) f * NCH + lane) * 2 + 0] = mean;
+          a.stats[((size_t) f * NCH + lane) * 2 + 1] = sd;
+        }
+        __syncwarp ();
+        if (lane == 0) {
+          __threadfence ();
+          asm volatile ("st.release.gpu.global.u32 [%0], %1;"
+              :: "l" (a.counter + (PUB_SLOTS + pub) * 32), "r" (f + 1) : "memory");
+        }
+      }
+      if (lane == 0) {
+        while (ld_acquire_u32 (a.counter + (PUB_SLOTS + pub) * 32) != f + 1)
           __nanosleep (32);
         trace (a, cta, f, 6);
       }
       __syncwarp ();
-      /* fold the n_cta partials: lane l takes CTAs l, l + 32, ... in order, then a fixed
-       * shuffle tree: the same bits in every CTA */
-      double tot[NCH][2];
-#pragma unroll
-      for (int c = 0; c < NCH; c++)
-#pragma unroll
-        for (int k = 0; k < 2; k++) {
-          const double *p = a.partial + (((size_t) pub * 4 + c) * 2 + k) * n_cta;
-          double v[(MAX_CTAS + 31) / 32];
-#pragma unroll
-          for (int i = 0; i < (MAX_CTAS + 31) / 32; i++)
-            v[i] = (lane + i * 32 < n_cta) ? __ldcg (p + lane + i * 32) : 0.0;
-          double t = 0.0;
-#pragma unroll
-          for (int i = 0; i < (MAX_CTAS + 31) / 32; i++)
-            t += v[i];
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1)
-            t += __shfl_xor_sync (0xffffffffu, t, o);
-          tot[c][k] = t;
-        }
       if (lane < NCH) {
-        double s1 = 0.0, s2 = 0.0;
-#pragma unroll
-        for (int c = 0; c < NCH; c++)
-          if (lane == (uint32_t) c) {
-            s1 = tot[c][0];
-            s2 = tot[c][1];
-          }
-        const double n = (double) (a.frame_elems / NCH);
-        const double mean = k0 + s1 / n;
-        double sd = 0.0;
-        if (a.default_mode) {
-          const double var = (s2 - s1 * (s1 / n)) / n;
-          /* tensor_data.c:438,488: std = (sum != 0) ? sqrt (sum) : 1e-10 */
-          sd = (var > 0.0) ? sqrt (var) : 1e-10;
-        }
-        /* ms[f & 1] was last read by the normalisation of tensor f - 2: tensor f can only be
-         * loaded into the memory tensor f - 2 lived in once that has finished */
-        sh.ms[f & 1][lane][0] = mean;
-        sh.ms[f & 1][lane][1] = a.default_mode ? __drcp_rn (sd) : 0.0;
-        if (cta == 0) {
-          a.stats[((size_t) f * NCH + lane) * 2 + 0] = mean;
-          a.stats[((size_t) f * NCH + lane) * 2 + 1] = sd;
-        }
+        /* ms[f & 1] was last read by the normalisation of tensor f - 2, which is over: the
+         * places its tiles lived in had to be free before tensor f could be loaded completely */
+        const double *fm = a.final_ms + ((size_t) pub * 4 + lane) * 4;
+        sh.ms[f & 1][lane][0] = __ldcg (fm);
+        sh.ms[f & 1][lane][1] = __ldcg (fm + 1);
       }
       __syncwarp ();
       if (lane == 0) {
@@ -363,10 +421,9 @@ stand_fused_kernel (FusedArgs a)
     }
   } else if (warp < 2 + STATS_WARPS) {
     /* ------------------------------ statistics ------------------------------ */
-    uint32_t s = 0, phase = 0;                  /* ring slot and mbarrier parity of the next tile */
+    uint32_t pl = 0, cyc = 0, ls = 0, lround = 0;       /* as in the producer */
     for (uint32_t f = 0; f < a.batch; f++) {
       const float *base = a.in + (uint64_t) f * a.frame_elems;
-      const bool to_tmem = (f & 1) == 0;
       double kk[NCH], a1[NCH], a2[NCH];
 #pragma unroll
       for (int r = 0; r < NCH; r++) {
@@ -374,22 +431,34 @@ stand_fused_kernel (FusedArgs a)
         a1[r] = 0.0;
         a2[r] = 0.0;
       }
-      if (to_tmem && f >= 2) {
-        /* the tensor parked in TMEM two tensors ago must have been normalised */
-        mbar_wait (&sh.tmem_free, ((f >> 1) - 1) & 1);
-        asm volatile ("tcgen05.fence::after_thread_sync;" ::: "memory");
-      }
       for (uint32_t j = 0; j < my_tiles; j++) {
-        mbar_wait (&sh.full[s], phase);
+        const bool to_tmem = pl < n_tplaces;
+        const uint32_t place = pl, use = cyc;
+        uint64_t *full, *land_empty = nullptr;
+        uint32_t slot, parity;
+        if (to_tmem) {
+          full = &sh.land_full[ls];
+          land_empty = &sh.land_empty[ls];
+          slot = ls;
+          parity = lround & 1;
+          if (++ls == LAND) {
+            ls = 0;
+            lround++;
+          }
+        } else {
+          full = &sh.park_full[pl - n_tplaces];
+          slot = LAND + pl - n_tplaces;
+          parity = cyc & 1;
+        }
+        if (++pl == n_places) {
+          pl = 0;
+          cyc++;
+        }
+        mbar_wait (full, parity);
         if (role_idx == 0 && lane == 0 && j + 1 == my_tiles)
           trace (a, cta, f, 2);
-        const float4 *tile = reinterpret_cast<const float4 *> (ring + (size_t) s * TILE);
+        const float4 *tile = reinterpret_cast<const float4 *> (ring + (size_t) slot * TILE);
         const uint32_t nv = tile_elems (first_tile + j) / 4;
-        uint64_t *const empty_bar = &sh.empty[s];
-        if (++s == NSLOT) {
-          s = 0;
-          phase ^= 1;
-        }
         float4 x[VPT];
 #pragma unroll
         for (int k = 0; k < VPT; k++) {
@@ -397,10 +466,14 @@ stand_fused_kernel (FusedArgs a)
           x[k] = v < nv ? tile[v] : make_float4 (0.f, 0.f, 0.f, 0.f);
         }
         if (to_tmem) {
-          __syncwarp ();                        /* the spin loop above may have split the warp */
+          /* the tile that was parked in this place 35 tiles ago must have been normalised */
+          if (use)
+            mbar_wait (&sh.tmem_empty[place], (use - 1) & 1);
+          asm volatile ("tcgen05.fence::after_thread_sync;" ::: "memory");
+          __syncwarp ();                        /* the spin loops above may have split the warp */
 #pragma unroll
           for (int k = 0; k < VPT; k++)
-            tmem_st4 (tmem_thread + j * TILE_COLS + 4 * k, x[k]);
+            tmem_st4 (tmem_thread + place * TILE_COLS + 4 * k, x[k]);
         }
 #pragma unroll
         for (int k = 0; k < VPT; k++) {
@@ -417,12 +490,12 @@ stand_fused_kernel (FusedArgs a)
           }
         }
         if (to_tmem) {
-          /* the ring slot is only a FIFO for this tensor: free it as soon as the copy is out */
+          /* the landing slot is only a FIFO: free it as soon as the copy is out */
           __syncwarp ();
           asm volatile ("tcgen05.wait::st.sync.aligned;" ::: "memory");
           __syncwarp ();
           if (lane == 0)
-            mbar_arrive (empty_bar);
+            mbar_arrive (land_empty);
         }
       }
       /* actual-channel order, a fixed shuffle tree per warp; the control warp adds the warps.
@@ -446,8 +519,7 @@ stand_fused_kernel (FusedArgs a)
           sh.red[f & 1][1][c][role_idx] = s2;
         }
       }
-      if (to_tmem)
-        asm volatile ("tcgen05.fence::before_thread_sync;" ::: "memory");
+      asm volatile ("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp ();
       if (role_idx == 0 && lane == 0)
         trace (a, cta, f, 3);
@@ -456,15 +528,12 @@ stand_fused_kernel (FusedArgs a)
     }
   } else {
     /* ------------------------------ normalisation ------------------------------ */
-    /* ring slot of the next ODD tensor's first tile: advances over the even tensors too */
-    uint32_t s = 0;
+    uint32_t pl = 0;
     for (uint32_t f = 0; f < a.batch; f++) {
-      const bool from_tmem = (f & 1) == 0;
       mbar_wait (&sh.ready[f & 1], (f >> 1) & 1);
       if (role_idx == 0 && lane == 0)
         trace (a, cta, f, 0);
-      if (from_tmem)
-        asm volatile ("tcgen05.fence::after_thread_sync;" ::: "memory");
+      asm volatile ("tcgen05.fence::after_thread_sync;" ::: "memory");
       double mean[NCH], rsd[NCH];
 #pragma unroll
       for (int r = 0; r < NCH; r++) {
@@ -473,10 +542,10 @@ stand_fused_kernel (FusedArgs a)
       }
       float *obase = a.out + (uint64_t) f * a.frame_elems;
       for (uint32_t j = 0; j < my_tiles; j++) {
-        const float4 *tile = reinterpret_cast<const float4 *> (ring + (size_t) s * TILE);
-        uint64_t *const empty_bar = &sh.empty[s];
-        if (++s == NSLOT)
-          s = 0;
+        const bool from_tmem = pl < n_tplaces;
+        const uint32_t place = pl;
+        if (++pl == n_places)
+          pl = 0;
         const uint32_t t = first_tile + j;
         const uint32_t nv = tile_elems (t) / 4;
         float4 *dst = reinterpret_cast<float4 *> (obase + (uint64_t) t * TILE);
@@ -485,18 +554,23 @@ stand_fused_kernel (FusedArgs a)
           __syncwarp ();
 #pragma unroll
           for (int k = 0; k < VPT; k++)
-            x[k] = tmem_ld4 (tmem_thread + j * TILE_COLS + 4 * k);
+            x[k] = tmem_ld4 (tmem_thread + place * TILE_COLS + 4 * k);
           asm volatile ("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          /* the values are in registers: the place can take another tile */
+          asm volatile ("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp ();
+          if (lane == 0)
+            mbar_arrive (&sh.tmem_empty[place]);
         } else {
+          const float4 *tile = reinterpret_cast<const float4 *> (ring + (size_t) (LAND + place - n_tplaces) * TILE);
 #pragma unroll
           for (int k = 0; k < VPT; k++) {
             const uint32_t v = v0 + 32 * k;
             x[k] = v < nv ? tile[v] : make_float4 (0.f, 0.f, 0.f, 0.f);
           }
-          /* the values are in registers: the slot can be refilled while we compute and store */
           __syncwarp ();
           if (lane == 0)
-            mbar_arrive (empty_bar);
+            mbar_arrive (&sh.park_empty[place - n_tplaces]);
         }
 #pragma unroll
         for (int k = 0; k < VPT; k++) {
@@ -515,13 +589,6 @@ stand_fused_kernel (FusedArgs a)
                    "r" (__float_as_uint (y[2])), "r" (__float_as_uint (y[3])) : "memory");
           }
         }
-      }
-      if (from_tmem) {
-        /* TMEM may be overwritten by the tensor after next */
-        asm volatile ("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncwarp ();
-        if (lane == 0)
-          mbar_arrive (&sh.tmem_free);
       }
       if (role_idx == 0 && lane == 0)
         trace (a, cta, f, 1);
@@ -605,13 +672,14 @@ stand_fused_supported (int in_type, int out_type, const void *in, const void *ou
   return geometry (frame_elems, cfg, &g);
 }
 
-constexpr size_t COUNTER_BYTES = (size_t) PUB_SLOTS * 128;      /* one 128-byte line per counter */
+constexpr size_t COUNTER_BYTES = (size_t) 2 * PUB_SLOTS * 128;  /* arrival counters + flags, one 128-byte line each */
+constexpr size_t FINAL_BYTES = (size_t) PUB_SLOTS * 4 * 4 * sizeof (double);
 
 size_t
 stand_fused_scratch_bytes (const LaunchCfg &cfg)
 {
-  /* counters, then partials */
-  return COUNTER_BYTES + (size_t) PUB_SLOTS * cfg.sm_count * 4 * 2 * sizeof (double);
+  /* counters and flags, the published statistics, then the partials */
+  return COUNTER_BYTES + FINAL_BYTES + (size_t) PUB_SLOTS * cfg.sm_count * 4 * 2 * sizeof (double);
 }
 
 int
@@ -634,7 +702,8 @@ launch_stand_fused (int stand_mode, const void *in, void *out, size_t frame_elem
   a.tiles_lo = g.tiles_lo;
   a.n_hi = g.n_hi;
   a.counter = (uint32_t *) scratch;
-  a.partial = (double *) ((char *) scratch + COUNTER_BYTES);
+  a.final_ms = (double *) ((char *) scratch + COUNTER_BYTES);
+  a.partial = (double *) ((char *) scratch + COUNTER_BYTES + FINAL_BYTES);
   a.lookahead = LOOKAHEAD_DEFAULT;
   if (const char *env = getenv ("NNSB_STAND_LOOKAHEAD"))
     a.lookahead = (uint32_t) atoi (env);

@@ -23,7 +23,7 @@ CASES = [
     ([3, 1920, 1080, 1], 4, "dc-average,per-channel:true", "dc-average", True),
     ([3, 1920, 1080, 1], 3, "default,per-channel:true", "default", True),
     ([4, 1001, 500, 1], 7, "default,per-channel:true", "default", True),     # short last tile, 4 channels
-    ([2, 1283, 731, 1], 6, "dc-average,per-channel:true", "dc-average", True),
+    ([2, 1284, 731, 1], 6, "dc-average,per-channel:true", "dc-average", True),
     ([1, 2500, 1001, 1], 2, "default", "default", False),
     ([3, 1280, 720, 1], 9, "default", "default", False),
 ]
