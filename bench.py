@@ -473,13 +473,16 @@ def aggregator_extras(dev, peak, with_cpu):
     return out
 
 
-def python_stream_chain(device_id, n_streams=8, frames_per_stream=100):
-    """BASELINE configs[4] on ONE GPU driven from Python threads through the element mirrors
-    (nnstreamer_b200.TensorConverter / TensorTransform): what the stream-ordered memories buy a
+def python_stream_chain(device_id, n_streams=8, frames_per_stream=300):
+    """BASELINE configs[4] on ONE GPU driven from Python threads: the same C-ABI calls as
+    tools/stream_bench (nnsb_converter_chain, nnsb_transform_transform x3, nnsb_memory_release),
+    made through ctypes with pre-built argument arrays -- what the stream-ordered memories buy a
     caller that is NOT native code.  Device-resident frames, one thread and one set of elements
     per pipeline; each thread waits once, for its last output."""
     from nnstreamer_b200 import DeviceMemory, TensorConverter, TensorTransform
+    from nnstreamer_b200 import _lib as L
     import ctypes as C
+    lib = L.lib()
     caps = ("video/x-raw, format=(string)RGB, width=(int)%d, height=(int)%d, framerate=(fraction)30/1" % (W, H))
     pipes = []
     for sidx in range(n_streams):
@@ -491,24 +494,32 @@ def python_stream_chain(device_id, n_streams=8, frames_per_stream=100):
         t3.negotiate(t2.negotiate(t1.negotiate(c1)))
         x = np.random.default_rng(sidx).integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
         m = t1.alloc(FRAME_ELEMS, on_device=True)
-        assert t1._lib.nnsb_transform_upload(t1.handle, C.byref(m), x.ctypes.data_as(C.c_void_p)) == 0
+        assert lib.nnsb_transform_upload(t1.handle, C.byref(m), x.ctypes.data_as(C.c_void_p)) == 0
         pipes.append((conv, t1, t2, t3, DeviceMemory(m)))
 
     def run(pipe, n):
         conv, t1, t2, t3, frame = pipe
-        last = None
+        chain, transform, release = lib.nnsb_converter_chain, lib.nnsb_transform_transform, lib.nnsb_memory_release
+        m = [(L.Memory * L.SIZE_LIMIT)() for _ in range(4)]
+        produced, n_out = C.c_int(0), C.c_uint32(0)
+        fr = C.byref(frame.mem)
+        p_produced, p_n = C.byref(produced), C.byref(n_out)
+        last = L.Memory()
+        p_last = C.byref(last)
+        handles = (t1.handle, t2.handle, t3.handle)
         for _ in range(n):
-            flow, m0 = conv.chain(frame)
-            flow, (m1,) = t1.transform([m0])
-            flow, (m2,) = t2.transform([m1])
-            flow, (m3,) = t3.transform([m2])
-            for m in (m0, m1, m2):
-                m.release()
-            if last is not None:
-                last.release()
-            last = m3
-        last.sync()
-        last.release()
+            if chain(conv.handle, fr, m[0], p_produced) != 0:
+                raise RuntimeError("converter failed")
+            for k in range(3):
+                if transform(handles[k], m[k], 1, m[k + 1], p_n) != 0:
+                    raise RuntimeError("transform failed: %s" % lib.nnsb_last_error())
+            release(m[0])
+            release(m[1])
+            release(m[2])
+            release(p_last)
+            C.memmove(p_last, m[3], C.sizeof(L.Memory))
+        L.check(lib.nnsb_memory_sync(p_last))
+        release(p_last)
 
     for p in pipes:
         run(p, 3)
@@ -526,7 +537,7 @@ def python_stream_chain(device_id, n_streams=8, frames_per_stream=100):
             e.close()
     return {"frames/s": fps, "GB/s": fps * FRAME_ELEMS * 21 / 1e9, "streams": n_streams,
             "frames_per_stream": frames_per_stream,
-            "driver": "Python threads through the element mirrors, device-resident frames"}
+            "driver": "Python threads, raw ctypes calls of the C-ABI element mirrors, device-resident frames"}
 
 
 STREAMS_PER_GPU = 8

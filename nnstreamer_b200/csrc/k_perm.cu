@@ -341,6 +341,30 @@ launch_permute_t (const PermDev &p, const void *in, void *out, const LaunchCfg &
   return (int) cudaGetLastError ();
 }
 
+/* which kernel a permutation of `batch` tensors at 256-byte aligned addresses would take */
+const char *
+permute_path_name (const PermDesc &d0, size_t frame_elems, uint32_t batch, const PermVecPlan *vec)
+{
+  CDim dims[PERM_DIMS];
+  int es = d0.es;
+  uint64_t alignment = 256;
+  if (batch > 1)
+    alignment |= (uint64_t) frame_elems * d0.es;
+  const int n = canonicalise_perm (d0.size, d0.in_stride, d0.rank, frame_elems, batch, 8, alignment, dims, &es);
+  if (n == 0 || (n == 1 && dims[0].in == 1))
+    return "copy";
+  const char *env = getenv ("NNSB_PERM_SLAB");
+  const int mode = env ? atoi (env) : 1;
+  LaunchCfg cfg;
+  cfg.sm_count = 148;
+  cfg.blocks_per_sm = 0;
+  if (mode && n <= 8 && (mode == 2 || !vec || !vec->valid || (vec->vb < 16 && es <= 2))
+      && launch_permute_slab (dims, n, es, (const void *) 256, (void *) 256,
+          (uint64_t) frame_elems * batch * d0.es / es, cfg, nullptr, true) == 0)
+    return "slab";
+  return (vec && vec->valid) ? "vector" : "scalar";
+}
+
 int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_elems,
     uint32_t batch, const LaunchCfg &cfg, cudaStream_t stream, const PermVecPlan *vec,
     const void *d_table)
@@ -389,6 +413,20 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
       else if (dims[ix].size >= 2 && dims[ix].size <= 4 && dims[iy].out == dims[ix].size)
         r = launch_plane (false, (int) dims[ix].size, es, dims[iy].size, dims[ix].in, no, o_size,
             o_out, o_in, in, out, cfg, stream);
+      if (r != -1)
+        return r;
+    }
+  }
+
+  /* 3b. rows that are not multiples of 16 bytes (the vector plan is 8 / 4 bytes wide or missing)
+   *     but long output runs: contiguous input slabs through shared memory (k_perm_slab.cu) */
+  {
+    const char *env = getenv ("NNSB_PERM_SLAB");
+    const int mode = env ? atoi (env) : 1;      /* 0 = never, 1 = when the vector path is narrow, 2 = whenever it fits */
+    /* measured: a win for 1- and 2-byte elements (u16 225x113x3: 1.4 -> 2.1 TB/s), not for floats
+     * with 4-byte vectors (227x227x3: 1.85 -> 1.3) */
+    if (mode && n <= 8 && (mode == 2 || !vec || !vec->valid || (vec->vb < 16 && es <= 2))) {
+      const int r = launch_permute_slab (dims, n, es, in, out, total * d0.es / es, cfg, stream);
       if (r != -1)
         return r;
     }
@@ -734,6 +772,175 @@ merge_kernel (unsigned char *__restrict__ dst, const __grid_constant__ MergeDev 
   }
 }
 
+/* Small blocks (RGB + alpha -> RGBA: 3 + 1 bytes per row): every 16-byte output chunk mixes
+ * bytes of several inputs, and the generic byte path above spends its time searching for them.
+ * But the pattern repeats with period P = lcm (row bytes, 16): the host lists, for each of the P
+ * output bytes of a period, the input it comes from and its offset inside that input's share
+ * of the period.  The grid stride is a multiple of P / 16 chunks, so a thread always produces
+ * the same phase of the period: its 16 source addresses are set up once and then only advance
+ * by a constant -- per byte one load, one add, one insert. */
+constexpr int MERGE_PERIOD_MAX = 256;
+struct MergePhaseDev
+{
+  int n;
+  uint32_t chunks_per_period;
+  const unsigned char *in[NNSB_MERGE_MAX];
+  uint64_t in_bytes[NNSB_MERGE_MAX];
+  uint32_t run[NNSB_MERGE_MAX];         /* bytes of input k consumed per period */
+  uint16_t delta[MERGE_PERIOD_MAX];     /* per output byte of a period: offset inside that run */
+  uint8_t src[MERGE_PERIOD_MAX];        /* ... and the input it comes from */
+};
+
+constexpr int MERGE_PHASE_J = 4;                /* chunks per thread and batch */
+constexpr int MERGE_PHASE_SMEM = 2 * 16 * STRIP_THREADS * MERGE_PHASE_J / 2 + 32 * NNSB_MERGE_MAX;
+
+/* The inputs' shares of a batch of periods are contiguous byte ranges: they are copied to shared
+ * memory with 16-byte loads (aligned supersets, any alignment), and the byte gather runs on
+ * ld.shared (byte loads from global memory were bound by L1 tag look-ups: 2.4 TB/s). */
+__global__ void __launch_bounds__ (STRIP_THREADS)
+merge_phase_kernel (unsigned char *__restrict__ dst, const __grid_constant__ MergePhaseDev m,
+    uint64_t total, uint32_t threads_used, uint64_t n_batches)
+{
+  extern __shared__ __align__ (16) unsigned char stage[];
+  __shared__ uint32_t region[NNSB_MERGE_MAX + 1];       /* where input k's bytes start in `stage` */
+  const uint32_t cpp = m.chunks_per_period;
+  const uint32_t tid = threadIdx.x;
+  const bool worker = tid < threads_used;
+  const uint32_t period0 = tid / cpp, phase = tid - period0 * cpp;
+  const uint32_t periods_per_step = threads_used / cpp;         /* threads_used is a multiple of cpp */
+  const uint32_t periods_per_batch = periods_per_step * MERGE_PHASE_J;
+  const uint64_t batch_bytes = (uint64_t) periods_per_batch * cpp * 16;
+  /* per thread: input and in-run offset of its 16 bytes (the phase never changes) */
+  uint32_t off[16], adv[16];
+  uint8_t src[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    const uint32_t e = phase * 16 + i;
+    src[i] = m.src[e];
+    off[i] = period0 * m.run[src[i]] + m.delta[e];
+    adv[i] = periods_per_step * m.run[src[i]];
+  }
+  for (uint64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
+    const uint64_t first_period = b * periods_per_batch;
+    /* ---- stage the inputs' shares of this batch ---- */
+    if (tid == 0) {
+      uint32_t pos = 0;
+      for (int k = 0; k < m.n; k++) {
+        const uintptr_t a0 = (uintptr_t) m.in[k] + first_period * m.run[k];
+        region[k] = pos + (uint32_t) (a0 & 15);
+        pos += (((uint32_t) (a0 & 15) + periods_per_batch * m.run[k] + 15) / 16) * 16;
+      }
+    }
+    __syncthreads ();
+    for (int k = 0; k < m.n; k++) {
+      const uintptr_t lo = (uintptr_t) m.in[k], hi = lo + m.in_bytes[k];
+      const uintptr_t a0 = lo + first_period * m.run[k];
+      const uintptr_t ga = a0 & ~(uintptr_t) 15;
+      const uint32_t n16 = ((uint32_t) (a0 - ga) + periods_per_batch * m.run[k] + 15) / 16;
+      unsigned char *dstk = stage + (region[k] - (uint32_t) (a0 - ga));
+      for (uint32_t c = tid; c < n16; c += STRIP_THREADS) {
+        const uintptr_t g = ga + (uintptr_t) c * 16;
+        if (g >= lo && g + 16 <= hi) {
+          asm volatile ("cp.async.cg.shared.global [%0], [%1], 16;"
+              :: "r" ((uint32_t) __cvta_generic_to_shared (dstk + c * 16)), "l" (g) : "memory");
+        } else {
+          for (int x = 0; x < 16; x++)
+            if (g + x >= lo && g + x < hi)
+              dstk[c * 16 + x] = *reinterpret_cast<const unsigned char *> (g + x);
+        }
+      }
+    }
+    asm volatile ("cp.async.commit_group;" ::: "memory");
+    asm volatile ("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads ();
+    /* ---- gather ---- */
+    if (worker) {
+      const unsigned char *base[16];
+#pragma unroll
+      for (int i = 0; i < 16; i++)
+        base[i] = stage + region[src[i]] + off[i];
+      uint64_t o = b * batch_bytes + (uint64_t) tid * 16;
+#pragma unroll
+      for (int j = 0; j < MERGE_PHASE_J; j++) {
+        if (o + 16 <= total) {
+          uint32_t w[4] = { 0, 0, 0, 0 };
+#pragma unroll
+          for (int i = 0; i < 16; i++)
+            w[i >> 2] |= (uint32_t) base[i][j * adv[i]] << (8 * (i & 3));
+          st_stream<16> (dst + o, w);
+        } else if (o < total) {
+#pragma unroll
+          for (int i = 0; i < 16; i++)
+            if (o + i < total)
+              dst[o + i] = base[i][j * adv[i]];
+        }
+        o += (uint64_t) threads_used * 16;
+      }
+    }
+    __syncthreads ();
+  }
+}
+
+static bool
+launch_merge_phase (int n, const void *const *in, const uint64_t *block_bytes, void *out,
+    uint64_t rows, const LaunchCfg &cfg, cudaStream_t stream, int *err)
+{
+  uint64_t S = 0, smallest = ~0ull;
+  for (int k = 0; k < n; k++) {
+    S += block_bytes[k];
+    if (block_bytes[k] < smallest)
+      smallest = block_bytes[k];
+  }
+  if (smallest >= 16 || (uintptr_t) out % 16 || getenv ("NNSB_MERGE_NO_PHASE"))
+    return false;
+  uint64_t a = S, b = 16;
+  while (b) { const uint64_t t = a % b; a = b; b = t; }
+  const uint64_t P = S / a * 16;
+  if (P > MERGE_PERIOD_MAX)
+    return false;
+  MergePhaseDev m;
+  memset (&m, 0, sizeof (m));
+  m.n = n;
+  m.chunks_per_period = (uint32_t) (P / 16);
+  const uint64_t rows_per_period = P / S;
+  for (int k = 0; k < n; k++) {
+    m.in[k] = (const unsigned char *) in[k];
+    m.in_bytes[k] = block_bytes[k] * rows;
+    m.run[k] = (uint32_t) (rows_per_period * block_bytes[k]);
+  }
+  for (uint64_t e = 0; e < P; e++) {
+    const uint64_t r = e / S;
+    uint64_t c = e % S;
+    int k = 0;
+    while (c >= block_bytes[k]) {
+      c -= block_bytes[k];
+      k++;
+    }
+    m.src[e] = (uint8_t) k;
+    m.delta[e] = (uint16_t) (r * block_bytes[k] + c);
+  }
+  const uint64_t total = S * rows;
+  const uint32_t cpp = m.chunks_per_period;
+  const uint32_t threads_used = STRIP_THREADS / cpp * cpp;
+  const uint64_t batch_bytes = (uint64_t) threads_used * MERGE_PHASE_J * 16;
+  const uint64_t n_batches = (total + batch_bytes - 1) / batch_bytes;
+  static int configured[64];
+  int dev = 0;
+  cudaGetDevice (&dev);
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
+    cudaFuncSetAttribute (merge_phase_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MERGE_PHASE_SMEM);
+    configured[dev] = 1;
+  }
+  uint64_t blocks = n_batches;
+  const uint64_t cap = (uint64_t) cfg.sm_count * (cfg.blocks_per_sm > 0 ? cfg.blocks_per_sm : 8);
+  if (blocks > cap)
+    blocks = cap;
+  merge_phase_kernel<<<(unsigned int) blocks, STRIP_THREADS, MERGE_PHASE_SMEM, stream>>> (
+      (unsigned char *) out, m, total, threads_used, n_batches);
+  *err = (int) cudaGetLastError ();
+  return true;
+}
+
 int launch_merge (int n, const void *const *in, const uint64_t *block_bytes, void *out,
     uint64_t rows, const LaunchCfg &cfg, cudaStream_t stream)
 {
@@ -761,6 +968,11 @@ int launch_merge (int n, const void *const *in, const uint64_t *block_bytes, voi
   m.off[n] = (uint32_t) S;
   if (n == 1)
     return launch_copy (in[0], out, S * rows, cfg, stream);
+  {
+    int err = 0;
+    if (launch_merge_phase (n, in, block_bytes, out, rows, cfg, stream, &err))
+      return err;
+  }
   const uint64_t total = S * rows;
   const uint64_t work = words ? (total + 15) / 16 : total;
   uint64_t blocks = (work + STRIP_THREADS - 1) / STRIP_THREADS;

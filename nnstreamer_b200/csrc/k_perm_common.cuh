@@ -6,6 +6,8 @@
 
 #include <cstdint>
 
+#include <cuda_runtime.h>
+
 namespace nnsb {
 
 /* exact q / d for q < 2^31 with one 64-bit multiply: m = ceil (2^(31+s) / d), s = ceil (log2 d) */
@@ -98,6 +100,12 @@ canonicalise_perm (const uint32_t *size, const uint64_t *in_stride, int rank, ui
   }
   return n;
 }
+
+/* k_perm_slab.cu: -1 = not suited (short runs, sparse input, ...), else the launch result;
+ * dry_run only answers the question */
+struct LaunchCfg;
+int launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
+    uint64_t total_elems, const LaunchCfg &cfg, cudaStream_t stream, bool dry_run = false);
 
 }  // namespace nnsb
 #endif

@@ -1,0 +1,400 @@
+/*
+ * k_perm_slab.cu -- K3/K4 slab path: permutations whose rows are NOT multiples of 16 bytes
+ * (u16 225x113x3 frames, 227x227x3 floats, frames of 152 550 bytes back to back ...), where
+ * the table-driven vector kernel (k_perm_vec.cu) falls back to 8- / 4-byte vectors or to the
+ * scalar kernel because a 16-byte access would straddle a row.
+ *
+ * Same job as the other permute kernels: gst_tensor_transform_transpose
+ * (gsttensor_transform.c:1417-1500) / _dimchg (:1120-1191).  Idea: bytes do not care about
+ * rows.
+ *   load    a SLAB = k consecutive slices of the dimension that is outermost on the input side
+ *           (that fits: <= ~100 KB) is one contiguous byte range of the input, whatever its
+ *           alignment: the 16-byte aligned superset of it is copied to shared memory with
+ *           cp.async.cg 16 (the element at slab byte b sits at smem[mis + b], mis = start & 15).
+ *   store   the slab's elements form contiguous RUNS in the output (the dims below the slab
+ *           dimension in output order, full, times k).  A thread owns 16-byte aligned output
+ *           chunks of a run: it gathers the chunk's 16 / es elements from shared memory
+ *           (coordinates advance incrementally, one divide per chunk) and writes one
+ *           st.global.v4; the at most two chunks per run that are cut by the run's ends are
+ *           written element by element.
+ * Two CTAs per SM alternate load and store phases.  Algorithmic bytes: 2 * es per element.
+ * Used when the vector plan is not 16 bytes wide and the runs are >= 128 bytes long.
+ */
+#include <cstdlib>
+#include <cstring>
+
+#include "nnsb_device.cuh"
+#include "nnsb_kernels.h"
+#include "k_perm_common.cuh"
+
+namespace nnsb {
+
+namespace {
+
+constexpr int SLAB_THREADS = 256;
+constexpr uint32_t SLAB_MAX_BYTES = 72 * 1024;        /* three CTAs per SM overlap their load and store phases */
+constexpr int SLAB_DIMS = 4;
+
+struct SlabDev
+{
+  int es;
+  /* dims inside a run, output order; the last one may be the slab dimension (extent k) */
+  int n_run;
+  uint32_t run_size[SLAB_DIMS];         /* extents (k for the slab dimension) */
+  FastDiv run_div[SLAB_DIMS];           /* the same as divisors: only full-size dims are ever divided by */
+  uint32_t run_in[SLAB_DIMS];           /* input strides, elements, slab relative */
+  int run_slab;                         /* index of the slab dimension among the run dims, -1 if none */
+  /* dims that enumerate the runs of a slab (the slab dimension is one of them unless it is in the run) */
+  int n_idx;
+  FastDiv idx_div[SLAB_DIMS];
+  uint32_t idx_in[SLAB_DIMS];           /* elements, slab relative */
+  uint64_t idx_out[SLAB_DIMS];          /* elements */
+  int idx_slab;                         /* index of the slab dimension among them, -1 if none */
+  /* dims outside (fixed per slab) */
+  int n_outer;
+  FastDiv outer_div[SLAB_DIMS];
+  uint64_t outer_in[SLAB_DIMS], outer_out[SLAB_DIMS];
+  /* the slab dimension */
+  uint32_t s_size, k;
+  FastDiv slabs_per_outer;
+  uint64_t s_in, s_out;                 /* elements */
+  uint32_t n_slabs;
+  uint64_t total_bytes;
+  /* divisors that depend on the slab height, for full slabs [0] and for the last, shorter one [1] */
+  FastDiv cpr_div[2], keff_div[2];
+};
+
+__device__ __forceinline__ uint32_t
+lds_elem (const unsigned char *p, int es, uint32_t *hi)
+{
+  *hi = 0;
+  if (es == 1)
+    return *p;
+  if (es == 2)
+    return *reinterpret_cast<const uint16_t *> (p);
+  if (es == 4)
+    return *reinterpret_cast<const uint32_t *> (p);
+  const uint2 v = *reinterpret_cast<const uint2 *> (p);
+  *hi = v.y;
+  return v.x;
+}
+
+template <int ES>
+__global__ void __launch_bounds__ (SLAB_THREADS)
+permute_slab_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
+    const __grid_constant__ SlabDev p)
+{
+  extern __shared__ __align__ (16) unsigned char buf[];
+  const uintptr_t in_lo = (uintptr_t) in, in_hi = in_lo + p.total_bytes;
+
+  for (uint32_t slab = blockIdx.x; slab < p.n_slabs; slab += gridDim.x) {
+    /* which slab: (outer coordinates, position along the slab dimension) */
+    uint32_t oi, si;
+    divmod (slab, p.slabs_per_outer, oi, si);
+    uint64_t in_base = 0, out_base = 0;         /* elements */
+#pragma unroll
+    for (int d = 0; d < SLAB_DIMS; d++)
+      if (d < p.n_outer) {
+        uint32_t q, c;
+        divmod (oi, p.outer_div[d], q, c);
+        oi = q;
+        in_base += (uint64_t) c * p.outer_in[d];
+        out_base += (uint64_t) c * p.outer_out[d];
+      }
+    const uint32_t o0 = si * p.k;
+    const uint32_t k_eff = (p.s_size - o0 < p.k) ? p.s_size - o0 : p.k;
+    in_base += (uint64_t) o0 * p.s_in;
+    out_base += (uint64_t) o0 * p.s_out;
+    const uint32_t slab_bytes = (uint32_t) (k_eff * p.s_in) * ES;
+
+    /* ---- load: the aligned superset of [abs0, abs0 + slab_bytes) ---- */
+    const uintptr_t abs0 = in_lo + in_base * ES;
+    const uintptr_t ga = abs0 & ~(uintptr_t) 15;
+    const uint32_t mis = (uint32_t) (abs0 - ga);
+    const uint32_t n_chunks = (mis + slab_bytes + 15) / 16;
+    for (uint32_t c = threadIdx.x; c < n_chunks; c += SLAB_THREADS) {
+      const uintptr_t g = ga + (uintptr_t) c * 16;
+      if (g >= in_lo && g + 16 <= in_hi) {
+        asm volatile ("cp.async.cg.shared.global [%0], [%1], 16;"
+            :: "r" ((uint32_t) __cvta_generic_to_shared (buf + c * 16)), "l" (g) : "memory");
+      } else {
+        /* first / last bytes of the whole tensor: never touch what is not ours */
+        for (int b = 0; b < 16; b++)
+          if (g + b >= in_lo && g + b < in_hi)
+            buf[c * 16 + b] = *reinterpret_cast<const unsigned char *> (g + b);
+      }
+    }
+    asm volatile ("cp.async.commit_group;" ::: "memory");
+    asm volatile ("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads ();
+
+    /* ---- store: runs of L elements, 16-byte chunks ---- */
+    uint32_t L = 1;
+#pragma unroll
+    for (int d = 0; d < SLAB_DIMS; d++)
+      if (d < p.n_run)
+        L *= (d == p.run_slab) ? k_eff : p.run_size[d];
+    uint32_t n_runs = 1;
+#pragma unroll
+    for (int d = 0; d < SLAB_DIMS; d++)
+      if (d < p.n_idx)
+        n_runs *= (d == p.idx_slab) ? k_eff : p.idx_div[d].d;
+    const uint32_t run_bytes = L * ES;
+    const int short_slab = k_eff != p.k;
+    const FastDiv cpr_div = p.cpr_div[short_slab], keff_div = p.keff_div[short_slab];
+    const uint32_t cpr = cpr_div.d;                     /* chunks a run can touch, any alignment */
+    const uint32_t items = n_runs * cpr;
+    const unsigned char *src0 = buf + mis;
+    for (uint32_t w = threadIdx.x; w < items; w += SLAB_THREADS) {
+      uint32_t r, ci;
+      divmod (w, cpr_div, r, ci);
+      uint64_t out_off = out_base;
+      uint32_t in_off = 0;
+#pragma unroll
+      for (int d = 0; d < SLAB_DIMS; d++)
+        if (d < p.n_idx) {
+          uint32_t q, c;
+          if (d == p.idx_slab)
+            divmod (r, keff_div, q, c);
+          else
+            divmod (r, p.idx_div[d], q, c);
+          r = q;
+          out_off += (uint64_t) c * p.idx_out[d];
+          in_off += c * p.idx_in[d];
+        }
+      const uintptr_t A = (uintptr_t) out + out_off * ES;       /* first byte of the run */
+      const uintptr_t g = (A & ~(uintptr_t) 15) + (uintptr_t) ci * 16;
+      if (g >= A + run_bytes)
+        continue;
+      const uint32_t e_lo = g > A ? (uint32_t) (g - A) / ES : 0;
+      uint32_t e_hi = (uint32_t) (g + 16 - A) / ES;
+      if (e_hi > L)
+        e_hi = L;
+      /* coordinates of element e_lo inside the run (<= 3 dims), then incremental */
+      uint32_t c0 = e_lo, c1 = 0, c2 = 0;
+      const uint32_t x0 = p.run_slab == 0 ? k_eff : p.run_size[0];
+      const uint32_t x1 = p.n_run > 1 ? (p.run_slab == 1 ? k_eff : p.run_size[1]) : 1;
+      if (p.n_run > 1) {
+        /* x0 (and x1) are full-size dims here: a run continues past a dim only if it is complete */
+        divmod (e_lo, p.run_div[0], c1, c0);
+        if (p.n_run > 2) {
+          const uint32_t t = c1;
+          divmod (t, p.run_div[1], c2, c1);
+        }
+      }
+      uint32_t s = in_off + c0 * p.run_in[0] + c1 * p.run_in[1] + c2 * p.run_in[2];
+      const bool full = g >= A && g + 16 <= A + run_bytes;
+      /* advance (c0, c1, s) to the next element of the run */
+#define NNSB_SLAB_NEXT() \
+      do { \
+        s += p.run_in[0]; \
+        if (++c0 == x0) { \
+          c0 = 0; \
+          s += p.run_in[1] - x0 * p.run_in[0]; \
+          if (++c1 == x1) { \
+            c1 = 0; \
+            s += p.run_in[2] - x1 * p.run_in[1]; \
+          } \
+        } \
+      } while (0)
+      if (full) {
+        /* exactly 16 / ES elements: unrolled, the four words stay in registers */
+        constexpr int NE = 16 / ES;
+        uint32_t wv[4] = { 0, 0, 0, 0 };
+#pragma unroll
+        for (int i = 0; i < NE; i++) {
+          uint32_t hi;
+          const uint32_t v = lds_elem (src0 + (size_t) s * ES, ES, &hi);
+          if (ES == 1)
+            wv[i >> 2] |= v << (8 * (i & 3));
+          else if (ES == 2)
+            wv[i >> 1] |= v << (16 * (i & 1));
+          else if (ES == 4)
+            wv[i] = v;
+          else {
+            wv[2 * i] = v;
+            wv[2 * i + 1] = hi;
+          }
+          NNSB_SLAB_NEXT ();
+        }
+        asm volatile ("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+            :: "l" (g), "r" (wv[0]), "r" (wv[1]), "r" (wv[2]), "r" (wv[3]) : "memory");
+      } else {
+        /* a chunk cut by one end of the run: element by element */
+        for (uint32_t e = e_lo; e < e_hi; e++) {
+          uint32_t hi;
+          const uint32_t v = lds_elem (src0 + (size_t) s * ES, ES, &hi);
+          unsigned char *d = reinterpret_cast<unsigned char *> (A) + (size_t) e * ES;
+          if (ES == 1)
+            *d = (unsigned char) v;
+          else if (ES == 2)
+            *reinterpret_cast<uint16_t *> (d) = (uint16_t) v;
+          else if (ES == 4)
+            *reinterpret_cast<uint32_t *> (d) = v;
+          else
+            *reinterpret_cast<uint2 *> (d) = make_uint2 (v, hi);
+          NNSB_SLAB_NEXT ();
+        }
+      }
+#undef NNSB_SLAB_NEXT
+    }
+    __syncthreads ();           /* the buffer is about to be overwritten */
+  }
+}
+
+template <int ES> int
+launch_t (const SlabDev &p, const void *in, void *out, size_t smem, const LaunchCfg &cfg,
+    cudaStream_t stream)
+{
+  static int configured[64];
+  int dev = 0;
+  cudaGetDevice (&dev);
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute (permute_slab_kernel<ES>,
+        cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SLAB_MAX_BYTES + 64));
+    if (e != cudaSuccess)
+      return (int) e;
+    configured[dev] = 1;
+  }
+  uint64_t grid = (uint64_t) cfg.sm_count * 2;
+  if (grid > p.n_slabs)
+    grid = p.n_slabs;
+  permute_slab_kernel<ES><<<(unsigned int) grid, SLAB_THREADS, smem, stream>>> (
+      (const unsigned char *) in, (unsigned char *) out, p);
+  return (int) cudaGetLastError ();
+}
+
+}  // namespace
+
+/* -1: this permutation does not suit the slab kernel; else the launch result */
+int
+launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out, uint64_t total_elems,
+    const LaunchCfg &cfg, cudaStream_t stream, bool dry_run)
+{
+  if (n < 2 || n > 2 * SLAB_DIMS || (es != 1 && es != 2 && es != 4 && es != 8))
+    return -1;
+  if (((uintptr_t) in | (uintptr_t) out) % (uintptr_t) es)
+    return -1;
+  /* dims by input stride; the input must be dense */
+  int by_in[2 * SLAB_DIMS];
+  for (int i = 0; i < n; i++)
+    by_in[i] = i;
+  for (int i = 1; i < n; i++)
+    for (int j = i; j > 0 && dims[by_in[j]].in < dims[by_in[j - 1]].in; j--) {
+      const int t = by_in[j];
+      by_in[j] = by_in[j - 1];
+      by_in[j - 1] = t;
+    }
+  uint64_t expect = 1;
+  for (int i = 0; i < n; i++) {
+    if (dims[by_in[i]].in != expect || dims[by_in[i]].size >= (1ull << 31))
+      return -1;
+    expect *= dims[by_in[i]].size;
+  }
+  /* the slab dimension: the outermost (on the input side) whose single slice fits */
+  int si = -1;
+  for (int i = n - 1; i >= 0; i--)
+    if (dims[by_in[i]].in * (uint64_t) es <= SLAB_MAX_BYTES) {
+      si = i;
+      break;
+    }
+  if (si < 1)
+    return -1;                  /* nothing fits, or the slab dimension would be the innermost */
+  const int S = by_in[si];
+  uint64_t k = SLAB_MAX_BYTES / (dims[S].in * es);
+  if (k > dims[S].size)
+    k = dims[S].size;
+  const uint64_t nsl = (dims[S].size + k - 1) / k;
+  k = (dims[S].size + nsl - 1) / nsl;
+  if (k * dims[S].in * es >= (1ull << 31))
+    return -1;
+
+  SlabDev p;
+  memset (&p, 0, sizeof (p));
+  p.es = es;
+  p.idx_slab = -1;
+  p.run_slab = -1;
+  bool outer[2 * SLAB_DIMS];
+  for (int i = 0; i < n; i++)
+    outer[i] = false;
+  for (int i = si + 1; i < n; i++) {
+    if (p.n_outer >= SLAB_DIMS)
+      return -1;
+    const int d = by_in[i];
+    outer[d] = true;
+    p.outer_div[p.n_outer] = make_fastdiv ((uint32_t) dims[d].size);
+    p.outer_in[p.n_outer] = dims[d].in;
+    p.outer_out[p.n_outer] = dims[d].out;
+    p.n_outer++;
+  }
+  /* local dims in output order (dims[] is in output order already): the run is the prefix that
+   * is contiguous in the output */
+  bool in_run = true;
+  uint64_t next_out = 1, run_elems = 1;
+  for (int d = 0; d < n; d++) {
+    if (outer[d]) {
+      in_run = false;           /* a fixed dim below: whatever follows starts new runs */
+      continue;
+    }
+    if (in_run && dims[d].out == next_out && p.n_run < 3) {
+      p.run_size[p.n_run] = (uint32_t) (d == S ? k : dims[d].size);
+      p.run_div[p.n_run] = make_fastdiv (p.run_size[p.n_run]);
+      p.run_in[p.n_run] = (uint32_t) dims[d].in;
+      p.n_run++;
+      run_elems *= (d == S ? k : dims[d].size);
+      next_out = dims[d].out * dims[d].size;
+      if (d == S) {
+        p.run_slab = p.n_run - 1;
+        if (k < dims[S].size)
+          in_run = false;
+      }
+      continue;
+    }
+    in_run = false;
+    if (p.n_idx >= SLAB_DIMS)
+      return -1;
+    if (d == S)
+      p.idx_slab = p.n_idx;
+    p.idx_div[p.n_idx] = make_fastdiv ((uint32_t) (d == S ? k : dims[d].size));
+    p.idx_in[p.n_idx] = (uint32_t) dims[d].in;
+    p.idx_out[p.n_idx] = dims[d].out;
+    p.n_idx++;
+  }
+  if (p.n_run == 0 || run_elems * es < 128 || run_elems >= (1ull << 28))
+    return -1;                  /* short runs: the tiled kernels do better */
+  /* slab-relative input strides: dims inside the slab have in < in[S] * k already */
+  p.s_size = (uint32_t) dims[S].size;
+  p.k = (uint32_t) k;
+  p.s_in = dims[S].in;
+  p.s_out = dims[S].out;
+  p.slabs_per_outer = make_fastdiv ((uint32_t) nsl);
+  uint64_t n_slabs = nsl;
+  for (int i = 0; i < p.n_outer; i++)
+    n_slabs *= p.outer_div[i].d;
+  if (n_slabs >= (1ull << 31))
+    return -1;
+  p.n_slabs = (uint32_t) n_slabs;
+  p.total_bytes = total_elems * (uint64_t) es;
+  {
+    const uint64_t k_last = dims[S].size - (nsl - 1) * k;       /* height of the last slab */
+    const uint64_t ks[2] = { k, k_last };
+    for (int v = 0; v < 2; v++) {
+      uint64_t run_v = run_elems;
+      if (p.run_slab >= 0)
+        run_v = run_elems / k * ks[v];
+      p.cpr_div[v] = make_fastdiv ((uint32_t) ((run_v * es + 15 + 15) / 16));
+      p.keff_div[v] = make_fastdiv ((uint32_t) ks[v]);
+    }
+  }
+  const size_t smem = (size_t) (k * dims[S].in * es) + 48;
+  if (dry_run)
+    return 0;
+  switch (es) {
+    case 1: return launch_t<1> (p, in, out, smem, cfg, stream);
+    case 2: return launch_t<2> (p, in, out, smem, cfg, stream);
+    case 4: return launch_t<4> (p, in, out, smem, cfg, stream);
+    default: return launch_t<8> (p, in, out, smem, cfg, stream);
+  }
+}
+
+}  // namespace nnsb

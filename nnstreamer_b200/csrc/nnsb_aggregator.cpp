@@ -414,7 +414,12 @@ make_room (nnsb_aggregator * a, size_t need, size_t out_size)
     return NNSB_OK;
   const size_t live = a->tail - a->head;
   size_t cap = a->capacity;
-  const size_t want = 4 * (live + need + out_size);
+  /* Room for a few outputs, a whole number of them: when the inputs tile the outputs (frames-in
+   * divides frames-out, no overlap) the block then runs full exactly at an output boundary and
+   * nothing has to move.  Blocks of one size cycle through the pool as their outputs are released. */
+  size_t want = (live + need + 2 * out_size + out_size - 1) / out_size * out_size;
+  if (want < 3 * out_size)
+    want = 3 * out_size;
   if (cap < want)
     cap = want;
   nnsb_memory fresh;

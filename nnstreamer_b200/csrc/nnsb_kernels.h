@@ -117,6 +117,11 @@ int launch_permute (const PermDesc & d, const void *in, void *out, size_t frame_
     uint32_t batch, const LaunchCfg & cfg, cudaStream_t stream,
     const PermVecPlan * vec = nullptr, const void *d_table = nullptr);
 
+/* "slab" / "vector" / "scalar" / "copy": the kernel a batch of such tensors takes when the
+ * interleaved <-> planar fast path does not apply (for nnsb_plan_describe) */
+const char *permute_path_name (const PermDesc & d, size_t frame_elems, uint32_t batch,
+    const PermVecPlan * vec);
+
 /* K3 fast path (k_plane.cu): interleaved <-> planar through TMA bulk copies.
  * Returns -1 when the problem does not qualify, else the launch status. */
 int launch_plane (bool to_planar, int channels, int es, uint64_t pixels, uint64_t plane_stride,

@@ -1495,6 +1495,12 @@ nnsb_plan_describe (const nnsb_plan * plan, char *buf, size_t buflen)
       } else {
         len = snprintf (buf, buflen, "permute: scalar box kernel");
       }
+      if (len > 0 && (size_t) len < buflen) {
+        /* what a batch of these tensors takes when the planar fast path does not apply */
+        const char *path = permute_path_name (plan->perm, plan->frame_elems, 2, &plan->perm_vec);
+        if (strcmp (path, "slab") == 0)
+          len += snprintf (buf + len, buflen - len, "; batches: contiguous slabs through shared memory");
+      }
       break;
     case NNSB_MODE_TYPECAST:
     case NNSB_MODE_ARITHMETIC:
