@@ -353,6 +353,8 @@ permute_path_name (const PermDesc &d0, size_t frame_elems, uint32_t batch, const
   const int n = canonicalise_perm (d0.size, d0.in_stride, d0.rank, frame_elems, batch, 8, alignment, dims, &es);
   if (n == 0 || (n == 1 && dims[0].in == 1))
     return "copy";
+  if (launch_pixel_transpose (dims, n, es, (const void *) 256, (void *) 256, nullptr, true) == 0)
+    return "pixel";
   const char *env = getenv ("NNSB_PERM_SLAB");
   const int mode = env ? atoi (env) : 1;
   LaunchCfg cfg;
@@ -416,6 +418,13 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
       if (r != -1)
         return r;
     }
+  }
+
+  /* 3a. the image transpose of packed RGB bytes (k_perm_pix.cu) */
+  {
+    const int r = launch_pixel_transpose (dims, n, es, in, out, stream);
+    if (r != -1)
+      return r;
   }
 
   /* 3b. rows that are not multiples of 16 bytes (the vector plan is 8 / 4 bytes wide or missing)

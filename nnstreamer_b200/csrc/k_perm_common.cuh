@@ -107,5 +107,9 @@ struct LaunchCfg;
 int launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
     uint64_t total_elems, const LaunchCfg &cfg, cudaStream_t stream, bool dry_run = false);
 
+/* k_perm_pix.cu: transpose 0:2:1:3 of packed 3-byte pixels; -1 = not that shape */
+int launch_pixel_transpose (const CDim *dims, int n, int es, const void *in, void *out,
+    cudaStream_t stream, bool dry_run = false);
+
 }  // namespace nnsb
 #endif

@@ -1500,6 +1500,8 @@ nnsb_plan_describe (const nnsb_plan * plan, char *buf, size_t buflen)
         const char *path = permute_path_name (plan->perm, plan->frame_elems, 2, &plan->perm_vec);
         if (strcmp (path, "slab") == 0)
           len += snprintf (buf + len, buflen - len, "; batches: contiguous slabs through shared memory");
+        else if (strcmp (path, "pixel") == 0)
+          len += snprintf (buf + len, buflen - len, "; aligned frames: RGB pixel transpose kernel");
       }
       break;
     case NNSB_MODE_TYPECAST:

@@ -72,3 +72,17 @@ def test_slab_leaves_guard_bytes_alone(dev, monkeypatch):
     assert back[guard + 6:guard + 6 + x.nbytes].tobytes() == np_transpose(x, dim, (1, 2, 0), batch).tobytes()
     dev.free(d_in)
     dev.free(d_out)
+
+
+@pytest.mark.parametrize("w,h,batch", [(1920, 1080, 3), (64, 64, 1), (80, 8, 5), (16, 200, 2), (1936, 1096, 1)])
+def test_rgb_pixel_transpose(dev, w, h, batch):
+    """transpose 0:2:1:3 of packed RGB bytes (k_perm_pix.cu): whole tiles, edge tiles in both
+    directions, batches; and widths the kernel must refuse (W % 16 != 0) still come out right."""
+    for ww, hh in ((w, h), (w + 2, h)):
+        dim = [3, ww, hh, 1]
+        n = 3 * ww * hh
+        x = np.random.default_rng(ww * hh).integers(0, 256, n * batch, dtype=np.uint8)
+        plan = dev.plan("transpose", "0:2:1:3", "uint8", dim)
+        got = plan.run_host(x, batch=batch)
+        plan.close()
+        assert bits_equal(got, np_transpose(x, dim, (0, 2, 1), batch)), (ww, hh, batch)
