@@ -10,14 +10,21 @@ Workload (BASELINE.json configs[1], the configuration the metric is quoted on):
 
   value  : device-resident frames/s (inputs already in HBM), CUDA events, max over ranks.
   e2e    : same metric through the host-buffer path: pinned host input -> H2D -> kernel ->
-           D2H into pinned host output, every step, copies inside the timed region.
+           D2H into pinned host output, every step, copies inside the timed region; with
+           `host_link` = bare cudaMemcpyAsync of the same bytes by all ranks at once (the ceiling
+           the host side sets) and the per-rank times.
+  e2e_consumer_on_device : the same batch when the consumer is CUDA-aware (converter uploads the
+           32 host frames, transform, tensor_filter hand-off on the device): H2D only.
   roofline: algorithmic bytes per launch (5 B/element) / measured launch time vs the measured
-           HBM copy bandwidth of this pool (MEASURED_PEAKS.json).
+           HBM copy bandwidth of this pool (MEASURED_PEAKS.json); traffic from the committed ncu CSV.
   cpu_baseline: the reference's own C code (oracle/_ref) or the C port timed on the host cores.
+  kernels: configs[4] (`chain_64_streams_*`: 8 streams per GPU through converter -> typecast ->
+           arithmetic -> transpose, resident / H2D / H2D+D2H, 1920 and 1918 wide) on EVERY N;
+           at N=1 also the other modes at their BASELINE configs.
 
 Multi-GPU (--gpus N under torchrun): streams are independent, so each rank runs its own
-32-frame batch on its own GPU ("weak" scaling); NCCL is used only for the barrier and the
-max-over-ranks of the timings -- the data path has no collective.
+32-frame batch (and its own 8 streams) on its own GPU ("weak" scaling); NCCL is used only for the
+barrier and the reductions of the timings -- the data path has no collective.
 
 `--impl reference` times the reference CPU implementation of the same step on the host cores.
 """
@@ -548,7 +555,7 @@ def sharded_stream_chain(local_rank, rank, world, dist, reduce_device, frames_pe
     """BASELINE configs[4]: 64 concurrent 1080p streams through converter -> typecast -> arithmetic
     -> transpose, 8 per GPU (nnstreamer_b200.sharding: stream s -> GPU s mod G), so N GPUs carry
     8 N of them.  Every rank runs tools/stream_bench (native threads through the C-ABI, one per
-    stream) on ITS GPU; all ranks start their timed region at the same wall-clock instant, the
+    stream) on ITS GPU; all ranks start their timed region together (a file barrier after warm-up), the
     frames are summed over the ranks and divided by the slowest rank's time.  Three modes
     (device-resident / H2D per frame / H2D + D2H per frame) x two widths (1920, and 1918 whose
     padded rows the converter strips).  `check` (rank 0, inside the cpu_baseline leg) compares the
@@ -570,13 +577,19 @@ def sharded_stream_chain(local_rank, rank, world, dist, reduce_device, frames_pe
         for mode in ("resident", "h2d", "h2d_d2h"):
             dump = os.path.join(tmp, "w%d" % width) if (mode == "resident" and rank == 0
                                                         and check is not None) else "-"
-            # same start instant on every rank: late enough for the slowest process to finish
-            # creating its CUDA context and warming up
-            start_at = sharding.max_over_ranks(time.time(), dist, reduce_device) + (3.0 if world == 1 else 8.0)
+            # same start instant on every rank: a file barrier after each process's own warm-up
+            # (the ranks of one node share /tmp)
+            bdir = "/tmp/nnsb_chain_barrier_%s_%d_%s" % (os.environ.get("MASTER_PORT", "0"), width, mode)
+            os.makedirs(bdir, exist_ok=True)
+            try:
+                os.remove(os.path.join(bdir, "ready.%d" % rank))
+            except OSError:
+                pass
+            sharding.max_over_ranks(0.0, dist, reduce_device)       # nobody starts before all cleaned up
             res = None
             try:
                 r = subprocess.run([exe, str(local_rank), str(n_local), str(frames_per_stream), mode,
-                                    str(width), dump, "%.6f" % start_at],
+                                    str(width), dump, "barrier:%s:%d:%d" % (bdir, rank, world)],
                                    capture_output=True, text=True, timeout=600)
                 if r.returncode == 0:
                     res = json.loads(r.stdout.strip().splitlines()[-1])
@@ -585,12 +598,17 @@ def sharded_stream_chain(local_rank, rank, world, dist, reduce_device, frames_pe
             except Exception as exc:                # noqa: BLE001
                 entry[mode] = {"error": str(exc)}
             ok = sharding.sum_over_ranks(1.0 if res else 0.0, dist, reduce_device)
+            try:
+                os.remove(os.path.join(bdir, "ready.%d" % rank))
+                os.rmdir(bdir)
+            except OSError:
+                pass
             if ok < world:
                 entry.setdefault(mode, {"error": "a rank failed"})
                 continue
             frames = sharding.sum_over_ranks(n_local * frames_per_stream, dist, reduce_device)
             slowest = sharding.max_over_ranks(res["seconds"], dist, reduce_device)
-            late = sharding.max_over_ranks(res["started_late_s"], dist, reduce_device)
+            skew = sharding.max_over_ranks(res["start_skew_s"], dist, reduce_device)
             h = int(res["stream0_last_output_fnv1a"], 16)
             hashes = sharding.gather_over_ranks([float(h >> 32), float(h & 0xffffffff)], dist, reduce_device)
             fps = frames / slowest
@@ -600,7 +618,7 @@ def sharded_stream_chain(local_rank, rank, world, dist, reduce_device, frames_pe
                            "slowest_rank_seconds": slowest, "this_rank_frames/s": res["frames/s"],
                            "h2d_bytes_per_frame": res["h2d_bytes_per_frame"],
                            "d2h_bytes_per_frame": res["d2h_bytes_per_frame"],
-                           "started_late_s_max": late,
+                           "start_barrier_wait_s_max": skew,
                            "all_ranks_same_output_as_rank0": all(x == hashes[0] for x in hashes)}
             if dump != "-":
                 entry["parity_vs_oracle_stream0_last_frame"] = check(dump, width)

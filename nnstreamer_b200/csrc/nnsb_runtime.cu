@@ -14,6 +14,7 @@
  */
 #include <cstdio>
 #include <cuda_runtime.h>
+#include <sched.h>
 
 #include <cstdlib>
 #include <cstring>
@@ -551,6 +552,24 @@ nnsb_event_destroy (nnsb_event * e)
  * gave 48.3 / 43.1 / 34.0 / 36.4 k frames/s at depth 1 / 2 / 3 / 4 (profiles/r2_pool_depth.md),
  * so the default is 1: an element starts its next buffer when its consumer is done with the
  * previous one.  NNSB_POOL_DEPTH overrides. */
+/* Waits for an event without monopolising the core: cudaEventSynchronize spins, and a node
+ * that runs 8 ranks x 8 streaming threads on 32 cores (BASELINE configs[4]) then loses a fifth of
+ * its throughput to threads spinning against each other.  Query + yield costs nothing when the
+ * cores are free. */
+static void
+host_wait (cudaEvent_t e)
+{
+  for (;;) {
+    const cudaError_t r = cudaEventQuery (e);
+    if (r != cudaErrorNotReady) {
+      if (r != cudaSuccess)
+        cudaGetLastError ();
+      return;
+    }
+    sched_yield ();
+  }
+}
+
 static int
 pool_depth ()
 {
@@ -601,7 +620,7 @@ dev_take (nnsb_ctx * ctx, size_t b, bool have_stream, cudaStream_t stream, void 
   if (p) {
     for (nnsb_evt * ev : must_wait) {
       if (!(have_stream && ev->stream == stream))
-        cudaEventSynchronize (ev->e);           /* back-pressure: see pool_depth () */
+        host_wait (ev->e);                      /* back-pressure: see pool_depth () */
       evt_unref (ev);
     }
     *out = p;

@@ -17,8 +17,10 @@
  *   DUMP  path prefix ("-" = none): DUMP.in receives the video frame of stream 0 and DUMP.out its
  *         last output tensor (float32 CHW), for the parity check bench.py makes against the CPU
  *         reference
- *   START_AT  wall-clock time (seconds since the epoch, fractional): the timed region starts then,
- *         so that the processes of all ranks load the shared host links at the same time
+ *   START_AT  when the timed region starts, so that the processes of all ranks load the shared
+ *         host links at the same time: a wall-clock time (seconds since the epoch, fractional),
+ *         or "barrier:DIR:RANK:WORLD" -- after its warm-up the process creates DIR/ready.RANK and
+ *         starts once all WORLD such files exist (ranks of one node share /tmp)
  * Nothing in the loop waits for the GPU in the resident mode: memories are stream-ordered
  * (include/nnstreamer_b200.h, nnsb_memory); each thread waits once, for its last output.
  * Prints one JSON object.  Built by __graft_entry__.build().
@@ -31,6 +33,8 @@
 #include <string>
 #include <thread>
 #include <vector>
+
+#include <unistd.h>
 
 #include "nnstreamer_b200.h"
 
@@ -107,6 +111,41 @@ fnv1a (const unsigned char *p, size_t n)
   return h;
 }
 
+/* "DIR:RANK:WORLD": announce this rank, wait for the others (at most two minutes).  Returns the
+ * seconds this rank waited. */
+static double
+file_barrier (const char *spec)
+{
+  std::string s (spec);
+  const size_t c2 = s.rfind (':'), c1 = s.rfind (':', c2 - 1);
+  if (c2 == std::string::npos || c1 == std::string::npos) {
+    fprintf (stderr, "bad barrier spec %s\n", spec);
+    exit (2);
+  }
+  const std::string dir = s.substr (0, c1);
+  const int rank = atoi (s.substr (c1 + 1, c2 - c1 - 1).c_str ()), world = atoi (s.substr (c2 + 1).c_str ());
+  FILE *f = fopen ((dir + "/ready." + std::to_string (rank)).c_str (), "w");
+  if (!f) {
+    fprintf (stderr, "cannot write into %s\n", dir.c_str ());
+    exit (1);
+  }
+  fclose (f);
+  const auto t0 = std::chrono::steady_clock::now ();
+  for (int r = 0; r < world; r++) {
+    const std::string name = dir + "/ready." + std::to_string (r);
+    for (;;) {
+      if (access (name.c_str (), F_OK) == 0)
+        break;
+      if (std::chrono::duration<double> (std::chrono::steady_clock::now () - t0).count () > 120.0) {
+        fprintf (stderr, "rank %d never arrived at the start barrier\n", r);
+        exit (1);
+      }
+      std::this_thread::sleep_for (std::chrono::microseconds (200));
+    }
+  }
+  return std::chrono::duration<double> (std::chrono::steady_clock::now () - t0).count ();
+}
+
 int
 main (int argc, char **argv)
 {
@@ -129,7 +168,8 @@ main (int argc, char **argv)
   if (argc > 5)
     W = atoi (argv[5]);
   const char *dump = (argc > 6 && strcmp (argv[6], "-") != 0) ? argv[6] : nullptr;
-  const double start_at = argc > 7 ? atof (argv[7]) : 0.0;
+  const bool use_barrier = argc > 7 && strncmp (argv[7], "barrier:", 8) == 0;
+  const double start_at = (argc > 7 && !use_barrier) ? atof (argv[7]) : 0.0;
   const size_t row = (size_t) W * C, pitch = (row + 3) / 4 * 4;
   const size_t frame_bytes = pitch * H;         /* GST_VIDEO_INFO_SIZE */
   const size_t elems = row * H;
@@ -179,7 +219,9 @@ main (int argc, char **argv)
   for (auto & p : pipes)
     run (&p, 3, mode);          /* warm-up: contexts, plans, pools */
   double late = 0.0;
-  if (start_at > 0.0) {
+  if (use_barrier)
+    late = file_barrier (argv[7] + 8);
+  else if (start_at > 0.0) {
     const double now = std::chrono::duration<double> (
         std::chrono::system_clock::now ().time_since_epoch ()).count ();
     if (now < start_at)
@@ -232,7 +274,7 @@ main (int argc, char **argv)
   printf ("{\"frames/s\": %.1f, \"GB/s\": %.1f, \"streams\": %d, \"frames_per_stream\": %d, "
       "\"mode\": \"%s\", \"width\": %d, \"seconds\": %.4f, \"h2d_bytes_per_frame\": %zu, "
       "\"d2h_bytes_per_frame\": %zu, \"stream0_last_output_fnv1a\": \"%016llx\", "
-      "\"stream0_kernel_launches\": %llu, \"started_late_s\": %.3f, "
+      "\"stream0_kernel_launches\": %llu, \"start_skew_s\": %.3f, "
       "\"driver\": \"native threads through the C-ABI (tools/stream_bench.cpp)\"}\n",
       fps, fps * (double) elems * bpe / 1e9, streams, frames, argv[4], W, dt,
       mode == RESIDENT ? (size_t) 0 : frame_bytes, mode == H2D_D2H ? pipes[0].out_bytes : (size_t) 0,
