@@ -8,9 +8,9 @@ run() { # name, kernel regex, run_kernel.py args...
 }
 mkdir -p gpurun_out
 # stand: fused single-read kernel (1 and 3 channels) and the three-launch kernels (one 400 MB tensor)
-run stand_fused stand_fused --batch 64 --iters 3 -- stand default float32 3:1920:1080:1
-run stand_fused_perch stand_fused --batch 64 --iters 3 -- stand default,per-channel:true float32 3:1920:1080:1
-NNSB_STAND_NO_FUSED=1 timeout 300 ncu --set full --clock-control none --import-source on -k regex:stand_ -c 3 -f -o gpurun_out/prof_stand_three_launch python profiles/run_kernel.py stand default float32 3:1920:1080:64 --iters 1 > gpurun_out/ncu_stand3.log 2>&1
+[ -n "$SKIP_STAND" ] || run stand_fused stand_fused --batch 64 --iters 3 -- stand default float32 3:1920:1080:1
+[ -n "$SKIP_STAND" ] || run stand_fused_perch stand_fused --batch 64 --iters 3 -- stand default,per-channel:true float32 3:1920:1080:1
+[ -n "$SKIP_STAND" ] || NNSB_STAND_NO_FUSED=1 timeout 300 ncu --set full --clock-control none --import-source on -k regex:stand_ -c 3 -f -o gpurun_out/prof_stand_three_launch python profiles/run_kernel.py stand default float32 3:1920:1080:64 --iters 1 > gpurun_out/ncu_stand3.log 2>&1
 # headline kernel (bench workload), planar f32, strip, merge, permutes
 run lut_chain_u8_f32 lut_chain --batch 32 --iters 3 -- arithmetic "typecast:float32,per-channel:true@0,add:-123.675@0,add:-116.28@1,add:-103.53@2,div:58.395@0,div:57.12@1,div:57.375@2" uint8 3:1920:1080:1
 run plane_f32 plane_kernel --batch 8 --iters 3 -- transpose 1:2:0:3 float32 3:3840:2160:1
