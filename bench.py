@@ -468,6 +468,19 @@ def aggregator_extras(dev, peak, with_cpu):
             out[name]["GB/s"] = 2 * nbytes * n_frames / dt / 1e9
             out[name]["frac_of_measured_peak"] = out[name]["GB/s"] / peak
         agg.close()
+    # the same calls from one native streaming thread (tools/agg_bench.cpp)
+    exe = os.path.join(ROOT, "tools", "agg_bench")
+    for name, fdim in (("aggregator_1080p_u8_out32_append", 3), ("aggregator_1080p_u8_out32_concat_w", 1)):
+        try:
+            r = subprocess.run([exe, str(dev.device_id), "32", str(fdim), "12"], capture_output=True,
+                               text=True, timeout=300)
+            res = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else \
+                {"error": r.stderr.strip()[-200:]}
+        except Exception as exc:                    # noqa: BLE001
+            res = {"error": str(exc)[:200]}
+        if fdim == 1 and "GB/s" in res:
+            res["frac_of_measured_peak"] = res["GB/s"] / peak
+        out[name + "_native_thread"] = res
     if with_cpu:
         port = cpu_checker_port()
         frame = np.random.default_rng(11).integers(0, 256, FRAME_ELEMS, dtype=np.uint8)
@@ -480,13 +493,15 @@ def aggregator_extras(dev, peak, with_cpu):
     return out
 
 
-def python_stream_chain(device_id, n_streams=8, frames_per_stream=300):
+def python_stream_chain(device_id, n_streams=8, frames_per_stream=300, linked=False):
     """BASELINE configs[4] on ONE GPU driven from Python threads: the same C-ABI calls as
     tools/stream_bench (nnsb_converter_chain, nnsb_transform_transform x3, nnsb_memory_release),
     made through ctypes with pre-built argument arrays -- what the stream-ordered memories buy a
     caller that is NOT native code.  Device-resident frames, one thread and one set of elements
-    per pipeline; each thread waits once, for its last output."""
-    from nnstreamer_b200 import DeviceMemory, TensorConverter, TensorTransform
+    per pipeline; each thread waits once, for its last output.  linked=True: the four elements
+    are linked into an nnsb_branch and a frame is ONE call (GStreamer's push model), so the
+    interpreter lock is taken once per frame instead of eight times."""
+    from nnstreamer_b200 import Branch, DeviceMemory, TensorConverter, TensorTransform
     from nnstreamer_b200 import _lib as L
     import ctypes as C
     lib = L.lib()
@@ -503,8 +518,27 @@ def python_stream_chain(device_id, n_streams=8, frames_per_stream=300):
         m = t1.alloc(FRAME_ELEMS, on_device=True)
         assert lib.nnsb_transform_upload(t1.handle, C.byref(m), x.ctypes.data_as(C.c_void_p)) == 0
         pipes.append((conv, t1, t2, t3, DeviceMemory(m)))
+    branches = [Branch(p[0], list(p[1:4])) for p in pipes] if linked else []
+
+    def run_linked(branch, frame, n):
+        push, release = lib.nnsb_branch_push, lib.nnsb_memory_release
+        outs = (L.Memory * L.SIZE_LIMIT)()
+        n_out = C.c_uint32(0)
+        fr, p_n, handle = C.byref(frame.mem), C.byref(n_out), branch.handle
+        last = L.Memory()
+        p_last = C.byref(last)
+        size = C.sizeof(L.Memory)
+        for _ in range(n):
+            if push(handle, fr, 1, outs, p_n) != 0:
+                raise RuntimeError("branch failed: %s" % lib.nnsb_last_error())
+            release(p_last)
+            C.memmove(p_last, outs, size)
+        L.check(lib.nnsb_memory_sync(p_last))
+        release(p_last)
 
     def run(pipe, n):
+        if linked:
+            return run_linked(branches[pipes.index(pipe)], pipe[4], n)
         conv, t1, t2, t3, frame = pipe
         chain, transform, release = lib.nnsb_converter_chain, lib.nnsb_transform_transform, lib.nnsb_memory_release
         m = [(L.Memory * L.SIZE_LIMIT)() for _ in range(4)]
@@ -538,13 +572,17 @@ def python_stream_chain(device_id, n_streams=8, frames_per_stream=300):
         t.join()
     dt = time.perf_counter() - t0
     fps = n_streams * frames_per_stream / dt
+    for b in branches:
+        b.close()
     for conv, t1, t2, t3, frame in pipes:
         frame.release()
         for e in (conv, t1, t2, t3):
             e.close()
     return {"frames/s": fps, "GB/s": fps * FRAME_ELEMS * 21 / 1e9, "streams": n_streams,
             "frames_per_stream": frames_per_stream,
-            "driver": "Python threads, raw ctypes calls of the C-ABI element mirrors, device-resident frames"}
+            "driver": ("Python threads, one nnsb_branch_push per frame (elements linked), "
+                       "device-resident frames") if linked else
+                      "Python threads, raw ctypes calls of the C-ABI element mirrors, device-resident frames"}
 
 
 STREAMS_PER_GPU = 8
@@ -976,6 +1014,7 @@ def run_b200(args):
             if world == 1:
                 extras.update(extra_kernels(dev, peak, with_cpu=with_cpu))
                 extras["chain_8_streams_1080p_python_threads"] = python_stream_chain(local_rank)
+                extras["chain_8_streams_1080p_python_threads_linked"] = python_stream_chain(local_rank, linked=True)
                 extras["mobilenet_224_per_frame_element_e2e"] = per_frame_mobilenet(dev, local_rank, with_cpu)
                 extras["e2e_pageable_source"] = pageable
 

@@ -641,6 +641,24 @@ NNSB_API int nnsb_demux_get_out_caps (nnsb_demux * d, uint32_t idx, char *out, s
 NNSB_API int nnsb_demux_chain (nnsb_demux * d, const nnsb_memory * in, uint32_t n_in, nnsb_memory * outs,
     uint32_t max_out, uint32_t *counts, uint32_t max_src, uint32_t *n_src);
 
+/* A linked run of elements pushed by ONE call: tensor_converter (optional) followed by n_t
+ * tensor_transform instances.  This is GStreamer's push model -- the converter's chain function
+ * pushes its buffer into the next element's chain function in the same streaming thread
+ * (gst_pad_push; gsttensor_converter.c:1250, GstBaseTransform's default chain around
+ * gsttensor_transform.c:1667) -- so a caller that pays for every call into the library (Python,
+ * a JNI binding) pays once per frame, not once per element.  The elements stay owned by the
+ * caller and must outlive the branch; they must be negotiated already. */
+typedef struct nnsb_branch nnsb_branch;
+NNSB_API int nnsb_branch_new (nnsb_converter * conv, nnsb_transform * const *t, uint32_t n_t,
+    nnsb_branch ** out);
+NNSB_API int nnsb_branch_free (nnsb_branch * b);
+/* in: one video frame (conv != NULL) or the n_in memories of one tensor buffer.  outs receives the
+ * *n_out memories the last element produced (0 while the converter is still collecting
+ * frames-per-tensor frames).  Intermediate memories are released before the call returns;
+ * nothing waits for the GPU.  Returns NNSB_FLOW_OK or NNSB_FLOW_ERROR. */
+NNSB_API int nnsb_branch_push (nnsb_branch * b, const nnsb_memory * in, uint32_t n_in,
+    nnsb_memory * outs, uint32_t *n_out);
+
 /* No counterpart in the reference (its CPU element simply mallocs).  The same stand kernels
  * as nnsb_plan_launch(), for callers that must not allocate while frames are flowing: a
  * pipeline whose GPU memory is already fully reserved by an inference runtime's pool, a

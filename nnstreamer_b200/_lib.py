@@ -258,6 +258,10 @@ _PROTOS = {
     "nnsb_mux_get_config": (C.c_int, [_VP, C.POINTER(TensorsConfig)]),
     "nnsb_mux_chain": (C.c_int, [_VP, C.POINTER(Memory), C.c_uint32, C.POINTER(Memory),
                                  C.POINTER(C.c_uint32)]),
+    "nnsb_branch_new": (C.c_int, [_VP, C.POINTER(_VP), C.c_uint32, C.POINTER(_VP)]),
+    "nnsb_branch_free": (C.c_int, [_VP]),
+    "nnsb_branch_push": (C.c_int, [_VP, C.POINTER(Memory), C.c_uint32, C.POINTER(Memory),
+                                   C.POINTER(C.c_uint32)]),
     "nnsb_demux_new": (C.c_int, [C.POINTER(_VP)]),
     "nnsb_demux_free": (C.c_int, [_VP]),
     "nnsb_demux_set_property": (C.c_int, [_VP, C.c_char_p, C.c_char_p]),

@@ -665,3 +665,89 @@ nnsb_demux_chain (nnsb_demux * d, const nnsb_memory * in, uint32_t n_in, nnsb_me
   }
   return res;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * nnsb_branch: converter -> transform ... -> transform pushed by one call (gst_pad_push chain)
+ * ------------------------------------------------------------------------------------------ */
+struct nnsb_branch
+{
+  nnsb_converter *conv = nullptr;
+  std::vector<nnsb_transform *> t;
+};
+
+extern "C" int
+nnsb_branch_new (nnsb_converter * conv, nnsb_transform * const *t, uint32_t n_t, nnsb_branch ** out)
+{
+  if (!out || (n_t && !t) || (!conv && !n_t))
+    return nnsb_set_error (NNSB_EINVAL, "nnsb_branch_new: no elements");
+  for (uint32_t i = 0; i < n_t; i++)
+    if (!t[i])
+      return nnsb_set_error (NNSB_EINVAL, "nnsb_branch_new: element %u is NULL", i);
+  nnsb_branch *b = new (std::nothrow) nnsb_branch ();
+  if (!b)
+    return nnsb_set_error (NNSB_ENOMEM, "nnsb_branch_new: out of memory");
+  b->conv = conv;
+  b->t.assign (t, t + n_t);
+  *out = b;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_branch_free (nnsb_branch * b)
+{
+  delete b;
+  return NNSB_OK;
+}
+
+extern "C" int
+nnsb_branch_push (nnsb_branch * b, const nnsb_memory * in, uint32_t n_in, nnsb_memory * outs,
+    uint32_t *n_out)
+{
+  if (!b || !in || !outs || !n_out || n_in == 0 || n_in > NNSB_SIZE_LIMIT) {
+    nnsb_set_error (NNSB_EINVAL, "nnsb_branch_push: bad arguments");
+    return NNSB_FLOW_ERROR;
+  }
+  *n_out = 0;
+  nnsb_memory a[NNSB_SIZE_LIMIT], c[NNSB_SIZE_LIMIT];
+  nnsb_memory *cur = a, *next = c;
+  const nnsb_memory *src = in;
+  uint32_t n = n_in;
+  bool own = false;             /* cur[] holds references of ours */
+  if (b->conv) {
+    int produced = 0;
+    if (n_in != 1) {
+      nnsb_set_error (NNSB_EINVAL, "nnsb_branch_push: the converter takes one frame per push");
+      return NNSB_FLOW_ERROR;
+    }
+    if (nnsb_converter_chain (b->conv, in, cur, &produced) != NNSB_FLOW_OK)
+      return NNSB_FLOW_ERROR;
+    if (!produced)
+      return NNSB_FLOW_OK;
+    src = cur;
+    n = 1;
+    own = true;
+  }
+  for (size_t k = 0; k < b->t.size (); k++) {
+    uint32_t m = 0;
+    nnsb_memory *dst = (k + 1 == b->t.size ()) ? outs : next;
+    const int r = nnsb_transform_transform (b->t[k], src, n, dst, &m);
+    if (own)
+      for (uint32_t i = 0; i < n; i++)
+        nnsb_memory_release (const_cast<nnsb_memory *> (&src[i]));
+    if (r != NNSB_FLOW_OK)
+      return NNSB_FLOW_ERROR;
+    if (dst == outs) {
+      *n_out = m;
+      return NNSB_FLOW_OK;
+    }
+    src = dst;
+    n = m;
+    own = true;
+    std::swap (cur, next);
+  }
+  /* converter only */
+  for (uint32_t i = 0; i < n; i++)
+    outs[i] = src[i];
+  *n_out = n;
+  return NNSB_FLOW_OK;
+}

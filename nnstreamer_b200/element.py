@@ -696,6 +696,67 @@ def _wrap_out(m):
     return DeviceMemory(o) if o.on_device else o
 
 
+class Branch:
+    """A linked run of elements pushed by one call (GStreamer's push model: the converter's chain
+    pushes into the transform's chain in the same streaming thread): `TensorConverter` (optional)
+    followed by `TensorTransform` instances, all negotiated already.  One C-ABI call per frame
+    instead of one per element -- what a Python streaming thread needs to keep up with the GPU."""
+
+    def __init__(self, converter, transforms):
+        self._lib = L.lib()
+        self._elements = (converter, list(transforms))      # kept alive with the branch
+        arr = (C.c_void_p * max(1, len(transforms)))(*[t.handle for t in transforms])
+        self.handle = C.c_void_p()
+        L.check(self._lib.nnsb_branch_new(converter.handle if converter is not None else None,
+                                          arr, len(transforms), C.byref(self.handle)))
+        self._outs = (L.Memory * L.SIZE_LIMIT)()
+        self._n_out = C.c_uint32(0)
+
+    def close(self):
+        if self.handle:
+            self._lib.nnsb_branch_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def push(self, memories):
+        """One frame (a DeviceMemory or numpy array) or the memories of one tensor buffer in ->
+        (flow_return, list of DeviceMemory / numpy outputs; empty while the converter collects)."""
+        if not isinstance(memories, (list, tuple)):
+            memories = [memories]
+        n = len(memories)
+        ins = (L.Memory * max(1, n))()
+        keep = []
+        for i, m in enumerate(memories):
+            if isinstance(m, DeviceMemory):
+                ins[i] = m.mem
+            else:
+                a = np.ascontiguousarray(m)
+                keep.append(a)
+                ins[i] = _host_memory(a)
+        flow = self._lib.nnsb_branch_push(self.handle, ins, n, self._outs, C.byref(self._n_out))
+        results = []
+        for i in range(self._n_out.value):
+            m = L.Memory()
+            C.memmove(C.byref(m), C.byref(self._outs[i]), C.sizeof(L.Memory))
+            if m.on_device:
+                results.append(DeviceMemory(m))
+            else:
+                buf = (C.c_uint8 * m.size).from_address(m.data)
+                results.append(np.frombuffer(buf, dtype=np.uint8).copy())
+                if m.owned:
+                    self._lib.nnsb_memory_release(C.byref(m))
+        return flow, results
+
+    def push_raw(self, ins, n, outs, n_out):
+        """No-copy variant: ctypes Memory arrays in and out, the caller releases the outputs."""
+        return self._lib.nnsb_branch_push(self.handle, ins, n, outs, n_out)
+
+
 class TensorMux:
     """tensor_mux: the memories of all sink pads, in pad order, become one other/tensors buffer
     (references, nothing is copied)."""

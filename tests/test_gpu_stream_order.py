@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 from helpers import bits_equal
-from nnstreamer_b200 import (DeviceMemory, TensorConverter, TensorFilter, TensorTransform,
+from nnstreamer_b200 import (Branch, DeviceMemory, TensorConverter, TensorFilter, TensorTransform,
                              device_memory)
 from nnstreamer_b200 import _lib as L
 
@@ -71,6 +71,66 @@ def test_chained_elements_do_not_need_a_host_sync(dev, port):
         e.close()
     conv.close()
     src.close()
+
+
+def test_branch_pushes_a_frame_through_all_elements_in_one_call(dev, port):
+    """nnsb_branch: converter (frames-per-tensor 2, padded 642-wide rows) -> typecast -> arithmetic
+    -> transpose with ONE call per frame; the result equals the element-by-element chain's, the
+    converter's "not yet" comes back as zero outputs, nothing waits for the GPU in between."""
+    w, h = 642, 480
+    conv = TensorConverter(frames_per_tensor=2)
+    c1 = conv.set_caps(VIDEO % (w, h))
+    t1 = TensorTransform(mode="typecast", option="float32")
+    t2 = TensorTransform(mode="arithmetic", option="add:-127.5,div:127.5")
+    t3 = TensorTransform(mode="transpose", option="1:2:0:3")
+    t3.negotiate(t2.negotiate(t1.negotiate(c1)))
+    br = Branch(conv, [t1, t2, t3])
+    rng = np.random.default_rng(11)
+    pitch = (3 * w + 3) // 4 * 4
+    src = TensorTransform(mode="typecast", option="uint8")
+    frames, outs = [], []
+    for i in range(6):
+        f = rng.integers(0, 256, pitch * h, dtype=np.uint8)
+        frames.append(f)
+        m = upload(src, f)
+        flow, res = br.push(m)
+        m.release()
+        assert flow == 0
+        assert len(res) == (1 if i % 2 else 0)
+        outs.extend(res)
+    ops = [("typecast", "float32"), ("add", -127.5), ("div", 127.5)]
+    for k, m3 in enumerate(outs):
+        dense = np.concatenate([port.stride_strip(frames[2 * k + j], 3, w, h) for j in range(2)])
+        want = port.transpose(port.arithmetic(dense, [3, w, h, 2], ops), [3, w, h, 2], (1, 2, 0, 3))
+        got = dev.download(m3.ptr, 3 * w * h * 2, np.float32)
+        assert bits_equal(got, want), "tensor %d" % k
+        m3.release()
+    # host frames go the same way (the converter uploads them)
+    flow, res = br.push(frames[0])
+    assert flow == 0 and res == []
+    flow, res = br.push(frames[1])
+    assert flow == 0 and len(res) == 1
+    dense = np.concatenate([port.stride_strip(frames[j], 3, w, h) for j in range(2)])
+    want = port.transpose(port.arithmetic(dense, [3, w, h, 2], ops), [3, w, h, 2], (1, 2, 0, 3))
+    assert bits_equal(dev.download(res[0].ptr, 3 * w * h * 2, np.float32), want)
+    res[0].release()
+    # transforms only: a tensor buffer in, a tensor buffer out
+    b2 = Branch(None, [t1, t2])
+    x = rng.integers(0, 256, 3 * w * h * 2, dtype=np.uint8)
+    mx = upload(src, x)
+    flow, res = b2.push([mx])
+    assert flow == 0 and len(res) == 1
+    assert bits_equal(dev.download(res[0].ptr, x.size, np.float32), port.arithmetic(x, [3, w, h, 2], ops))
+    res[0].release()
+    mx.release()
+    # a size mismatch is a flow error, like the element's
+    flow, res = br.push(np.zeros(10, np.uint8))
+    assert flow != 0 and res == []
+    for b in (br, b2):
+        b.close()
+    for e in (t1, t2, t3, src):
+        e.close()
+    conv.close()
 
 
 def test_pool_never_recycles_a_block_that_is_still_being_read(dev, port):

@@ -190,3 +190,19 @@ def test_demux_shares_outlive_the_parent_reference(dev):
             mem.release()
     for p in junk:
         dev.free(p)
+
+
+def test_branch_rejects_bad_arguments():
+    """nnsb_branch_new / _push argument checks (no GPU work)."""
+    import ctypes as C
+    from nnstreamer_b200 import _lib as L
+    lib = L.lib()
+    h = C.c_void_p()
+    assert lib.nnsb_branch_new(None, None, 0, C.byref(h)) < 0           # no elements at all
+    arr = (C.c_void_p * 1)(None)
+    assert lib.nnsb_branch_new(None, arr, 1, C.byref(h)) < 0            # a NULL element
+    assert lib.nnsb_branch_free(None) == 0
+    n = C.c_uint32(7)
+    outs = (L.Memory * L.SIZE_LIMIT)()
+    ins = (L.Memory * 1)()
+    assert lib.nnsb_branch_push(None, ins, 1, outs, C.byref(n)) != 0
