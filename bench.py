@@ -53,7 +53,7 @@ ORACLE_OPS = [("typecast", "float32"), ("add", -123.675, 0), ("add", -116.28, 1)
 WORKLOAD = "3:1920:1080:32 uint8 -> float32, arithmetic " + OPTION
 ALGO_BYTES_PER_ELEM = 5           # sizeof(u8) + sizeof(f32), SURVEY.md 8d
 # ncu --set full capture of the headline kernel (one launch of this very workload), committed
-NCU_RAW_CSV = os.path.join(ROOT, "profiles", "r1_lut_chain_u8_f32_raw.csv")
+NCU_RAW_CSV = os.path.join(ROOT, "profiles", "r2_lut_chain_u8_f32_raw.csv")
 METRIC = "tensor_transform_1080p_frames_per_sec"
 UNIT = "frames/s"
 # the same dict in both arms (`same_config`): what the step is and how L2 is kept out of it

@@ -360,7 +360,7 @@ permute_path_name (const PermDesc &d0, size_t frame_elems, uint32_t batch, const
   LaunchCfg cfg;
   cfg.sm_count = 148;
   cfg.blocks_per_sm = 0;
-  if (mode && n <= 8 && (mode == 2 || !vec || !vec->valid || (vec->vb < 16 && es <= 2))
+  if (mode && n <= 8 && (mode == 2 || !vec || !vec->valid || vec->vb < 16)
       && launch_permute_slab (dims, n, es, (const void *) 256, (void *) 256,
           (uint64_t) frame_elems * batch * d0.es / es, cfg, nullptr, true) == 0)
     return "slab";
@@ -432,9 +432,9 @@ int launch_permute (const PermDesc &d0, const void *in, void *out, size_t frame_
   {
     const char *env = getenv ("NNSB_PERM_SLAB");
     const int mode = env ? atoi (env) : 1;      /* 0 = never, 1 = when the vector path is narrow, 2 = whenever it fits */
-    /* measured: a win for 1- and 2-byte elements (u16 225x113x3: 1.4 -> 2.1 TB/s), not for floats
-     * with 4-byte vectors (227x227x3: 1.85 -> 1.3) */
-    if (mode && n <= 8 && (mode == 2 || !vec || !vec->valid || (vec->vb < 16 && es <= 2))) {
+    /* whenever the vector plan is narrower than 16 bytes: its per-vector overhead is that of a
+     * 16-byte vector, the slab kernel's store phase works per element */
+    if (mode && n <= 8 && (mode == 2 || !vec || !vec->valid || vec->vb < 16)) {
       const int r = launch_permute_slab (dims, n, es, in, out, total * d0.es / es, cfg, stream);
       if (r != -1)
         return r;

@@ -10,7 +10,8 @@
  * word:
  *   load    a tile of 64 x 64 pixels; a thread reads 16 pixels of one input row with three
  *           16-byte loads, widens them to RGBx words (PRMT) and scatters them TRANSPOSED into
- *           shared memory (tile_t[w][h], pitch 65 words);
+ *           shared memory (tile_t[w][h], pitch 65 words, columns swizzled so that neither the
+ *           scatter nor the gather below has bank conflicts within a row);
  *   store   an output row of the tile is 64 pixels = 192 bytes = 24 pieces of 8 bytes; a thread
  *           builds a piece from the 4 pixels it touches (4 ld.shared.b32, 3 PRMT to re-pack to 12
  *           bytes, two funnel shifts to cut the 8 it wants) and consecutive threads store
@@ -51,6 +52,12 @@ pixel_transpose_kernel (const unsigned char *__restrict__ in, unsigned char *__r
     const uint32_t gw = w0 + 16 * q, gh = h0 + h;
     if (gh < H && gw < W) {             /* W % 16 == 0: a quarter is inside or outside as a whole */
       const uint4 *src = reinterpret_cast<const uint4 *> (fin + ((uint64_t) gh * W + gw) * 3);
+      /* column of pixel (row 16q + p, h): h with bit 3 flipped in the upper half of the rows, and
+       * the upper half of the columns shifted by one word.  The four quarters of a warp's store
+       * then fall into four different groups of 8 banks, and the 24 pieces of a row that a warp
+       * reads below hit 24 different banks (columns c and c + 32 no longer share one). */
+      const uint32_t hx = h ^ ((q & 2) << 2);
+      const uint32_t hcol = hx + (hx >> 5);
       uint32_t v[12];
 #pragma unroll
       for (int i = 0; i < 3; i++) {
@@ -67,7 +74,7 @@ pixel_transpose_kernel (const unsigned char *__restrict__ in, unsigned char *__r
         const int b = 3 * p, wi = b >> 2, sh = b & 3;
         const uint32_t lo = v[wi], hi = wi + 1 < 12 ? v[wi + 1] : 0u;
         const uint32_t px = __funnelshift_r (lo, hi, 8 * sh) & 0x00ffffffu;
-        tile_t[(16 * q + p) * PIX_PITCH + h] = px;
+        tile_t[(16 * q + p) * PIX_PITCH + hcol] = px;
       }
     }
   }
@@ -84,9 +91,11 @@ pixel_transpose_kernel (const unsigned char *__restrict__ in, unsigned char *__r
     if (w < rows_here && p < pieces_per_row) {
       /* bytes [8p, 8p + 8) of the row: pixels px0 .. px0 + 3, starting r bytes into px0 */
       const uint32_t px0 = (8 * p) / 3, r = 8 * p - 3 * px0;
-      const uint32_t *row = tile_t + w * PIX_PITCH + px0;
-      const uint32_t a = row[0], b = row[1], c = row[2];
-      const uint32_t d = px0 + 3 < (uint32_t) PIX_T ? row[3] : 0u;
+      const uint32_t *row = tile_t + w * PIX_PITCH;
+      const uint32_t x = (w & 32) >> 2;          /* the swizzle of the load phase: q & 2 == (w >> 4) & 2 */
+      const uint32_t h0x = px0 ^ x, h1x = (px0 + 1) ^ x, h2x = (px0 + 2) ^ x, h3x = (px0 + 3) ^ x;
+      const uint32_t a = row[h0x + (h0x >> 5)], b = row[h1x + (h1x >> 5)], c = row[h2x + (h2x >> 5)];
+      const uint32_t d = px0 + 3 < (uint32_t) PIX_T ? row[h3x + (h3x >> 5)] : 0u;
       /* re-pack 4 x RGBx to 12 bytes */
       const uint32_t x0 = a | (b << 24);
       const uint32_t x1 = (b >> 8) | (c << 16);

@@ -62,6 +62,15 @@ struct SlabDev
   uint64_t total_bytes;
   /* divisors that depend on the slab height, for full slabs [0] and for the last, shorter one [1] */
   FastDiv cpr_div[2], keff_div[2];
+  /* lane-per-element store (store_lanes): a run is cut into segments of `seg` elements (a multiple
+   * of 32), a warp owns a segment, lane l its elements l, l + 32, ...  The step of 32 elements in
+   * the mixed radix of the run dims, and what it adds to the source offset: */
+  int lanes;                            /* use store_lanes */
+  uint32_t seg;
+  FastDiv nseg_div[2];                  /* segments per run: full slab, last slab */
+  uint32_t step_c0, step_c1;            /* 32 = (.. * x1 + step_c1) * x0 + step_c0 */
+  uint32_t step_s;                      /* source elements a step adds when nothing wraps */
+  uint32_t wrap0_s, wrap1_s;            /* added (mod 2^32) when c0 / c1 wraps */
 };
 
 __device__ __forceinline__ uint32_t
@@ -79,8 +88,109 @@ lds_elem (const unsigned char *p, int es, uint32_t *hi)
   return v.x;
 }
 
-template <int ES>
-__global__ void __launch_bounds__ (SLAB_THREADS)
+template <int ES> __device__ __forceinline__ void
+copy_elem (unsigned char *dst, const unsigned char *src)
+{
+  if constexpr (ES == 1) {
+    const unsigned char v = *src;
+    asm volatile ("st.global.L1::no_allocate.u8 [%0], %1;" :: "l" (dst), "r" ((uint32_t) v) : "memory");
+  } else if constexpr (ES == 2) {
+    const uint16_t v = *reinterpret_cast<const uint16_t *> (src);
+    asm volatile ("st.global.L1::no_allocate.u16 [%0], %1;" :: "l" (dst), "h" (v) : "memory");
+  } else if constexpr (ES == 4) {
+    const uint32_t v = *reinterpret_cast<const uint32_t *> (src);
+    asm volatile ("st.global.L1::no_allocate.u32 [%0], %1;" :: "l" (dst), "r" (v) : "memory");
+  } else {
+    const uint2 v = *reinterpret_cast<const uint2 *> (src);
+    asm volatile ("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" :: "l" (dst), "r" (v.x), "r" (v.y) : "memory");
+  }
+}
+
+/* Store phase, one element per lane: consecutive lanes write consecutive elements of a run (a
+ * warp store is 32 * ES contiguous bytes, whatever the alignment of the run), and read their
+ * sources from shared memory at the stride the permutation gives them.  Nothing here depends on
+ * alignment, and a lane spends a handful of instructions per element: its coordinates inside the
+ * run advance by 32 with at most one carry per dim.  NRUN = dims inside a run. */
+template <int ES, int NRUN> __device__ __forceinline__ void
+store_lanes (const SlabDev &p, const unsigned char *src0, unsigned char *out, uint64_t out_base,
+    uint32_t k_eff, int short_slab, uint32_t L, uint32_t n_runs)
+{
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const FastDiv nseg_div = p.nseg_div[short_slab], keff_div = p.keff_div[short_slab];
+  const uint32_t x0 = p.run_slab == 0 ? k_eff : p.run_size[0];
+  const uint32_t x1 = p.run_slab == 1 ? k_eff : p.run_size[1];
+  const uint32_t n0 = p.n_idx > 0 ? (p.idx_slab == 0 ? k_eff : p.idx_div[0].d) : 1;
+  const uint32_t n_outer_runs = p.n_idx > 0 ? n_runs / n0 : 1;
+  const uint32_t items = n0 * nseg_div.d;
+  for (uint32_t o = 0; o < n_outer_runs; o++) {
+    /* the run-index dims above the first: the same for every warp */
+    uint64_t out_o = out_base;
+    uint32_t in_o = 0, r = o;
+#pragma unroll
+    for (int d = 1; d < SLAB_DIMS; d++)
+      if (d < p.n_idx) {
+        uint32_t q, c;
+        if (d == p.idx_slab)
+          divmod (r, keff_div, q, c);
+        else
+          divmod (r, p.idx_div[d], q, c);
+        r = q;
+        out_o += (uint64_t) c * p.idx_out[d];
+        in_o += c * p.idx_in[d];
+      }
+    for (uint32_t m = warp; m < items; m += SLAB_THREADS / 32) {
+      uint32_t i0, sg;
+      divmod (m, nseg_div, i0, sg);
+      uint32_t j = sg * p.seg + lane;
+      uint32_t j_end = (sg + 1) * p.seg;
+      if (j_end > L)
+        j_end = L;
+      uint32_t c0 = j, c1 = 0, c2 = 0;
+      if (NRUN > 1) {
+        divmod (j, p.run_div[0], c1, c0);
+        if (NRUN > 2) {
+          const uint32_t t = c1;
+          divmod (t, p.run_div[1], c2, c1);
+        }
+      }
+      uint32_t sidx = in_o + c0 * p.run_in[0];
+      uint64_t out_r = out_o + j;
+      if (p.n_idx > 0) {
+        sidx += i0 * p.idx_in[0];
+        out_r += (uint64_t) i0 * p.idx_out[0];
+      }
+      if (NRUN > 1)
+        sidx += c1 * p.run_in[1];
+      if (NRUN > 2)
+        sidx += c2 * p.run_in[2];
+      unsigned char *dst = out + out_r * ES;
+      for (; j < j_end; j += 32) {
+        copy_elem<ES> (dst, src0 + (size_t) sidx * ES);
+        dst += 32 * ES;
+        sidx += p.step_s;
+        if (NRUN > 1) {
+          c0 += p.step_c0;
+          if (c0 >= x0) {
+            c0 -= x0;
+            sidx += p.wrap0_s;
+            if (NRUN > 2)
+              c1 += 1;
+          }
+          if (NRUN > 2) {
+            c1 += p.step_c1;
+            if (c1 >= x1) {
+              c1 -= x1;
+              sidx += p.wrap1_s;
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+template <int ES, bool LANES>
+__global__ void __launch_bounds__ (SLAB_THREADS, LANES ? 6 : 5)
 permute_slab_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
     const __grid_constant__ SlabDev p)
 {
@@ -141,6 +251,16 @@ permute_slab_kernel (const unsigned char *__restrict__ in, unsigned char *__rest
         n_runs *= (d == p.idx_slab) ? k_eff : p.idx_div[d].d;
     const uint32_t run_bytes = L * ES;
     const int short_slab = k_eff != p.k;
+    if constexpr (LANES) {
+      if (p.n_run == 1)
+        store_lanes<ES, 1> (p, buf + mis, out, out_base, k_eff, short_slab, L, n_runs);
+      else if (p.n_run == 2)
+        store_lanes<ES, 2> (p, buf + mis, out, out_base, k_eff, short_slab, L, n_runs);
+      else
+        store_lanes<ES, 3> (p, buf + mis, out, out_base, k_eff, short_slab, L, n_runs);
+      __syncthreads ();         /* the buffer is about to be overwritten */
+      continue;
+    } else {
     const FastDiv cpr_div = p.cpr_div[short_slab], keff_div = p.keff_div[short_slab];
     const uint32_t cpr = cpr_div.d;                     /* chunks a run can touch, any alignment */
     const uint32_t items = n_runs * cpr;
@@ -239,10 +359,11 @@ permute_slab_kernel (const unsigned char *__restrict__ in, unsigned char *__rest
 #undef NNSB_SLAB_NEXT
     }
     __syncthreads ();           /* the buffer is about to be overwritten */
+    }                           /* !LANES */
   }
 }
 
-template <int ES> int
+template <int ES, bool LANES> int
 launch_t (const SlabDev &p, const void *in, void *out, size_t smem, const LaunchCfg &cfg,
     cudaStream_t stream)
 {
@@ -250,16 +371,24 @@ launch_t (const SlabDev &p, const void *in, void *out, size_t smem, const Launch
   int dev = 0;
   cudaGetDevice (&dev);
   if (dev >= 0 && dev < 64 && !configured[dev]) {
-    cudaError_t e = cudaFuncSetAttribute (permute_slab_kernel<ES>,
+    cudaError_t e = cudaFuncSetAttribute (permute_slab_kernel<ES, LANES>,
         cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SLAB_MAX_BYTES + 64));
     if (e != cudaSuccess)
       return (int) e;
     configured[dev] = 1;
   }
-  uint64_t grid = (uint64_t) cfg.sm_count * 2;
+  uint64_t per_sm = (200 * 1024) / (smem + 1024);      /* what the shared memory allows */
+  const uint64_t by_regs = LANES ? 6 : 5;
+  if (per_sm > by_regs)
+    per_sm = by_regs;
+  if (per_sm < 2)
+    per_sm = 2;
+  if (const char *e = getenv ("NNSB_SLAB_CTAS"))
+    per_sm = (uint64_t) atoi (e) > 0 ? (uint64_t) atoi (e) : per_sm;
+  uint64_t grid = (uint64_t) cfg.sm_count * per_sm;
   if (grid > p.n_slabs)
     grid = p.n_slabs;
-  permute_slab_kernel<ES><<<(unsigned int) grid, SLAB_THREADS, smem, stream>>> (
+  permute_slab_kernel<ES, LANES><<<(unsigned int) grid, SLAB_THREADS, smem, stream>>> (
       (const unsigned char *) in, (unsigned char *) out, p);
   return (int) cudaGetLastError ();
 }
@@ -301,7 +430,16 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   if (si < 1)
     return -1;                  /* nothing fits, or the slab dimension would be the innermost */
   const int S = by_in[si];
-  uint64_t k = SLAB_MAX_BYTES / (dims[S].in * es);
+  /* slab height: as tall as fits, but short enough that the grid gets several slabs per CTA slot
+   * (a batch of small frames is only a few hundred 72 KB slabs, and with two resident CTAs per
+   * SM those quantise into 2-3 rounds of which the last is half empty) */
+  uint64_t max_bytes = SLAB_MAX_BYTES;
+  if (const char *e = getenv ("NNSB_SLAB_KB"))
+    if (atoi (e) > 0 && (uint64_t) atoi (e) * 1024 <= SLAB_MAX_BYTES)
+      max_bytes = (uint64_t) atoi (e) * 1024;
+  if (dims[S].in * (uint64_t) es > max_bytes)
+    max_bytes = dims[S].in * (uint64_t) es;
+  uint64_t k = max_bytes / (dims[S].in * es);
   if (k > dims[S].size)
     k = dims[S].size;
   const uint64_t nsl = (dims[S].size + k - 1) / k;
@@ -360,7 +498,14 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
     p.idx_out[p.n_idx] = dims[d].out;
     p.n_idx++;
   }
-  if (p.n_run == 0 || run_elems * es < 128 || run_elems >= (1ull << 28))
+  /* how the store phase works: 16-byte chunks per thread (bytes: fewest stores) or one element
+   * per lane (everything else: fewest instructions, no alignment cases) */
+  p.lanes = es >= 2;
+  if (const char *e = getenv ("NNSB_SLAB_STORE"))
+    p.lanes = strcmp (e, "lanes") == 0 ? 1 : strcmp (e, "chunks") == 0 ? 0 : p.lanes;
+  if (p.n_run == 0 || run_elems >= (1ull << 28))
+    return -1;
+  if (p.lanes ? run_elems < 16 : run_elems * es < 128)
     return -1;                  /* short runs: the tiled kernels do better */
   /* slab-relative input strides: dims inside the slab have in < in[S] * k already */
   p.s_size = (uint32_t) dims[S].size;
@@ -378,22 +523,50 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   {
     const uint64_t k_last = dims[S].size - (nsl - 1) * k;       /* height of the last slab */
     const uint64_t ks[2] = { k, k_last };
+    /* segments: long runs are cut so that the 8 warps of a CTA all find work */
+    p.seg = (uint32_t) ((run_elems + 31) / 32 * 32);
+    if (p.seg > 512)
+      p.seg = 512;
     for (int v = 0; v < 2; v++) {
       uint64_t run_v = run_elems;
       if (p.run_slab >= 0)
         run_v = run_elems / k * ks[v];
       p.cpr_div[v] = make_fastdiv ((uint32_t) ((run_v * es + 15 + 15) / 16));
       p.keff_div[v] = make_fastdiv ((uint32_t) ks[v]);
+      p.nseg_div[v] = make_fastdiv ((uint32_t) ((run_v + p.seg - 1) / p.seg));
+    }
+    /* a step of 32 elements along a run, in the mixed radix (x0, x1) of its dims */
+    if (p.n_run == 1) {
+      p.step_s = 32u * p.run_in[0];
+    } else {
+      const uint32_t x0 = p.run_size[0], x1 = p.run_size[1];
+      p.step_c0 = 32u % x0;
+      uint32_t rest = 32u / x0, top = 0;
+      if (p.n_run > 2) {
+        top = rest / x1;
+        rest = rest % x1;
+      }
+      p.step_c1 = rest;
+      p.step_s = p.step_c0 * p.run_in[0] + p.step_c1 * p.run_in[1] + top * p.run_in[2];
+      p.wrap0_s = p.run_in[1] - x0 * p.run_in[0];
+      p.wrap1_s = p.n_run > 2 ? p.run_in[2] - x1 * p.run_in[1] : 0u;
     }
   }
   const size_t smem = (size_t) (k * dims[S].in * es) + 48;
   if (dry_run)
     return 0;
+  if (p.lanes)
+    switch (es) {
+      case 1: return launch_t<1, true> (p, in, out, smem, cfg, stream);
+      case 2: return launch_t<2, true> (p, in, out, smem, cfg, stream);
+      case 4: return launch_t<4, true> (p, in, out, smem, cfg, stream);
+      default: return launch_t<8, true> (p, in, out, smem, cfg, stream);
+    }
   switch (es) {
-    case 1: return launch_t<1> (p, in, out, smem, cfg, stream);
-    case 2: return launch_t<2> (p, in, out, smem, cfg, stream);
-    case 4: return launch_t<4> (p, in, out, smem, cfg, stream);
-    default: return launch_t<8> (p, in, out, smem, cfg, stream);
+    case 1: return launch_t<1, false> (p, in, out, smem, cfg, stream);
+    case 2: return launch_t<2, false> (p, in, out, smem, cfg, stream);
+    case 4: return launch_t<4, false> (p, in, out, smem, cfg, stream);
+    default: return launch_t<8, false> (p, in, out, smem, cfg, stream);
   }
 }
 

@@ -13,7 +13,10 @@ pytestmark = pytest.mark.gpu
 
 ORDERS = [o for o in itertools.permutations((0, 1, 2)) if o != (0, 1, 2)]
 SHAPES = [("uint16", [3, 225, 113, 1], 5), ("float32", [3, 227, 227, 1], 3), ("uint8", [3, 321, 77, 1], 4),
-          ("float64", [5, 33, 117, 1], 3), ("uint8", [1, 1001, 333, 1], 2), ("int16", [7, 64, 129, 1], 6)]
+          ("float64", [5, 33, 117, 1], 3), ("uint8", [1, 1001, 333, 1], 2), ("int16", [7, 64, 129, 1], 6),
+          # small frames: a slab is a stack of whole frames and all three dims sit inside a run
+          ("uint16", [6, 10, 14, 1], 40), ("float32", [3, 20, 9, 1], 50), ("uint8", [5, 12, 7, 1], 333)]
+STORES = ["lanes", "chunks", None]
 
 
 def np_transpose(x, dim, order, batch):
@@ -23,9 +26,16 @@ def np_transpose(x, dim, order, batch):
     return a.transpose(axes).reshape(-1)
 
 
+@pytest.mark.parametrize("store", STORES, ids=["lanes", "chunks", "auto"])
 @pytest.mark.parametrize("force", [True, False], ids=["forced", "default"])
 @pytest.mark.parametrize("dtype,dim,batch", SHAPES, ids=lambda v: str(v).replace(" ", ""))
-def test_slab_permute_matches_numpy(dev, monkeypatch, dtype, dim, batch, force):
+def test_slab_permute_matches_numpy(dev, monkeypatch, dtype, dim, batch, force, store):
+    """store: the two store phases of the kernel (one element per lane / 16-byte chunks per
+    thread, NNSB_SLAB_STORE) and the default choice between them."""
+    if store:
+        monkeypatch.setenv("NNSB_SLAB_STORE", store)
+    else:
+        monkeypatch.delenv("NNSB_SLAB_STORE", raising=False)
     if force:
         monkeypatch.setenv("NNSB_PERM_SLAB", "2")
     else:
@@ -54,9 +64,11 @@ def test_slab_permute_matches_numpy(dev, monkeypatch, dtype, dim, batch, force):
         assert used > 0, "the slab kernel was never selected for %s %s" % (dtype, dim)
 
 
-def test_slab_leaves_guard_bytes_alone(dev, monkeypatch):
+@pytest.mark.parametrize("store", ["lanes", "chunks"])
+def test_slab_leaves_guard_bytes_alone(dev, monkeypatch, store):
     """Partial head / tail chunks of a run are written element by element: nothing outside."""
     monkeypatch.setenv("NNSB_PERM_SLAB", "2")
+    monkeypatch.setenv("NNSB_SLAB_STORE", store)
     dim, batch, dtype = [3, 225, 113, 1], 3, "uint16"
     n = int(np.prod(dim))
     x = np.random.default_rng(1).integers(0, 65535, n * batch).astype(dtype)
