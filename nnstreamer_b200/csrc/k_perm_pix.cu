@@ -35,6 +35,7 @@ constexpr int PIX_T = 64;               /* tile edge, pixels */
 constexpr int PIX_PITCH = PIX_T + 1;    /* words */
 constexpr int PIX_THREADS = 256;
 
+template <bool STAGE, bool SWZ>
 __global__ void __launch_bounds__ (PIX_THREADS)
 pixel_transpose_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
     uint32_t W, uint32_t H, uint32_t tiles_w, uint32_t tiles_h, uint64_t frame_bytes)
@@ -46,23 +47,51 @@ pixel_transpose_kernel (const unsigned char *__restrict__ in, unsigned char *__r
   const unsigned char *fin = in + (uint64_t) blockIdx.y * frame_bytes;
   unsigned char *fout = out + (uint64_t) blockIdx.y * frame_bytes;
 
+  /* ---- stage: the tile's 64 rows of 192 bytes, global -> shared without passing registers.
+   * Consecutive lanes copy consecutive 16-byte pieces, so a warp's copy touches 4 lines; the
+   * direct loads below (lane stride 48 bytes) touch 12 per instruction, three times. ---- */
+  __shared__ __align__ (16) unsigned char stage[STAGE ? PIX_T * 192 : 16];
+  if constexpr (STAGE) {
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      const uint32_t g = t + PIX_THREADS * i;
+      const uint32_t row = g / 12, pc = g - row * 12;
+      if (h0 + row < H && (w0 * 3 + 16 * pc) < W * 3)
+        asm volatile ("cp.async.cg.shared.global [%0], [%1], 16;"
+            :: "r" ((uint32_t) __cvta_generic_to_shared (stage + row * 192 + pc * 16)),
+               "l" (fin + ((uint64_t) (h0 + row) * W + w0) * 3 + 16 * pc) : "memory");
+    }
+    asm volatile ("cp.async.commit_group;" ::: "memory");
+    asm volatile ("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads ();
+  }
+
   /* ---- load: thread = (input row h, 16-pixel quarter) ---- */
   {
     const uint32_t h = t >> 2, q = t & 3;
     const uint32_t gw = w0 + 16 * q, gh = h0 + h;
     if (gh < H && gw < W) {             /* W % 16 == 0: a quarter is inside or outside as a whole */
-      const uint4 *src = reinterpret_cast<const uint4 *> (fin + ((uint64_t) gh * W + gw) * 3);
+      const uint4 *src = STAGE ? reinterpret_cast<const uint4 *> (stage + h * 192 + q * 48)
+          : reinterpret_cast<const uint4 *> (fin + ((uint64_t) gh * W + gw) * 3);
       /* column of pixel (row 16q + p, h): h with bit 3 flipped in the upper half of the rows, and
        * the upper half of the columns shifted by one word.  The four quarters of a warp's store
        * then fall into four different groups of 8 banks, and the 24 pieces of a row that a warp
        * reads below hit 24 different banks (columns c and c + 32 no longer share one). */
-      const uint32_t hx = h ^ ((q & 2) << 2);
-      const uint32_t hcol = hx + (hx >> 5);
+      const uint32_t hx = SWZ ? h ^ ((q & 2) << 2) : h;
+      const uint32_t hcol = SWZ ? hx + (hx >> 5) : h;
       uint32_t v[12];
 #pragma unroll
       for (int i = 0; i < 3; i++) {
         uint32_t w4[4];
-        ld_stream<16> (w4, src + i);
+        if constexpr (STAGE) {
+          const uint4 v4 = src[i];
+          w4[0] = v4.x;
+          w4[1] = v4.y;
+          w4[2] = v4.z;
+          w4[3] = v4.w;
+        } else {
+          ld_stream<16> (w4, src + i);
+        }
         v[4 * i] = w4[0];
         v[4 * i + 1] = w4[1];
         v[4 * i + 2] = w4[2];
@@ -92,10 +121,20 @@ pixel_transpose_kernel (const unsigned char *__restrict__ in, unsigned char *__r
       /* bytes [8p, 8p + 8) of the row: pixels px0 .. px0 + 3, starting r bytes into px0 */
       const uint32_t px0 = (8 * p) / 3, r = 8 * p - 3 * px0;
       const uint32_t *row = tile_t + w * PIX_PITCH;
-      const uint32_t x = (w & 32) >> 2;          /* the swizzle of the load phase: q & 2 == (w >> 4) & 2 */
-      const uint32_t h0x = px0 ^ x, h1x = (px0 + 1) ^ x, h2x = (px0 + 2) ^ x, h3x = (px0 + 3) ^ x;
-      const uint32_t a = row[h0x + (h0x >> 5)], b = row[h1x + (h1x >> 5)], c = row[h2x + (h2x >> 5)];
-      const uint32_t d = px0 + 3 < (uint32_t) PIX_T ? row[h3x + (h3x >> 5)] : 0u;
+      uint32_t a, b, c, d;
+      if constexpr (SWZ) {
+        const uint32_t x = (w & 32) >> 2;        /* the swizzle of the load phase: q & 2 == (w >> 4) & 2 */
+        const uint32_t h0x = px0 ^ x, h1x = (px0 + 1) ^ x, h2x = (px0 + 2) ^ x, h3x = (px0 + 3) ^ x;
+        a = row[h0x + (h0x >> 5)];
+        b = row[h1x + (h1x >> 5)];
+        c = row[h2x + (h2x >> 5)];
+        d = px0 + 3 < (uint32_t) PIX_T ? row[h3x + (h3x >> 5)] : 0u;
+      } else {
+        a = row[px0];
+        b = row[px0 + 1];
+        c = row[px0 + 2];
+        d = px0 + 3 < (uint32_t) PIX_T ? row[px0 + 3] : 0u;
+      }
       /* re-pack 4 x RGBx to 12 bytes */
       const uint32_t x0 = a | (b << 24);
       const uint32_t x1 = (b >> 8) | (c << 16);
@@ -140,8 +179,19 @@ launch_pixel_transpose (const CDim *dims, int n, int es, const void *in, void *o
   if (dry_run)
     return 0;
   dim3 grid (tiles_w * tiles_h, (unsigned int) batch);
-  pixel_transpose_kernel<<<grid, PIX_THREADS, 0, stream>>> ((const unsigned char *) in,
-      (unsigned char *) out, (uint32_t) W, (uint32_t) H, tiles_w, tiles_h, frame);
+  static const int variant = [] {
+    const char *e = getenv ("NNSB_PIX_STAGE"), *z = getenv ("NNSB_PIX_SWIZZLE");
+    return (e ? atoi (e) != 0 : 1) * 2 + (z ? atoi (z) != 0 : 0);
+  } ();
+  const unsigned char *pi = (const unsigned char *) in;
+  unsigned char *po = (unsigned char *) out;
+  const uint32_t w32 = (uint32_t) W, h32 = (uint32_t) H;
+  switch (variant) {
+    case 0: pixel_transpose_kernel<false, false><<<grid, PIX_THREADS, 0, stream>>> (pi, po, w32, h32, tiles_w, tiles_h, frame); break;
+    case 1: pixel_transpose_kernel<false, true><<<grid, PIX_THREADS, 0, stream>>> (pi, po, w32, h32, tiles_w, tiles_h, frame); break;
+    case 2: pixel_transpose_kernel<true, false><<<grid, PIX_THREADS, 0, stream>>> (pi, po, w32, h32, tiles_w, tiles_h, frame); break;
+    default: pixel_transpose_kernel<true, true><<<grid, PIX_THREADS, 0, stream>>> (pi, po, w32, h32, tiles_w, tiles_h, frame); break;
+  }
   return (int) cudaGetLastError ();
 }
 

@@ -63,12 +63,14 @@ struct SlabDev
   /* divisors that depend on the slab height, for full slabs [0] and for the last, shorter one [1] */
   FastDiv cpr_div[2], keff_div[2];
   /* lane-per-element store (store_lanes): a run is cut into segments of `seg` elements (a multiple
-   * of 32), a warp owns a segment, lane l its elements l, l + 32, ...  The step of 32 elements in
-   * the mixed radix of the run dims, and what it adds to the source offset: */
+   * of lane_w), a group of lane_w lanes (a warp, or a half / quarter of one for short runs) owns a
+   * segment, lane l its elements l, l + lane_w, ...  The step of lane_w elements in the mixed
+   * radix of the run dims, and what it adds to the source offset: */
   int lanes;                            /* use store_lanes */
+  uint32_t lane_w;                      /* 32, 16 or 8 */
   uint32_t seg;
   FastDiv nseg_div[2];                  /* segments per run: full slab, last slab */
-  uint32_t step_c0, step_c1;            /* 32 = (.. * x1 + step_c1) * x0 + step_c0 */
+  uint32_t step_c0, step_c1;            /* lane_w = (.. * x1 + step_c1) * x0 + step_c0 */
   uint32_t step_s;                      /* source elements a step adds when nothing wraps */
   uint32_t wrap0_s, wrap1_s;            /* added (mod 2^32) when c0 / c1 wraps */
 };
@@ -100,9 +102,16 @@ copy_elem (unsigned char *dst, const unsigned char *src)
   } else if constexpr (ES == 4) {
     const uint32_t v = *reinterpret_cast<const uint32_t *> (src);
     asm volatile ("st.global.L1::no_allocate.u32 [%0], %1;" :: "l" (dst), "r" (v) : "memory");
-  } else {
+  } else if constexpr (ES == 8) {
     const uint2 v = *reinterpret_cast<const uint2 *> (src);
     asm volatile ("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" :: "l" (dst), "r" (v.x), "r" (v.y) : "memory");
+  } else {
+    /* 3, 6, 12: a pixel of three 1-, 2- or 4-byte channels that stays together (see the fold in
+     * launch_permute_slab): three accesses of the channel's size, which is all its alignment allows */
+    constexpr int C = ES / 3;
+    copy_elem<C> (dst, src);
+    copy_elem<C> (dst + C, src + C);
+    copy_elem<C> (dst + 2 * C, src + 2 * C);
   }
 }
 
@@ -115,13 +124,33 @@ template <int ES, int NRUN> __device__ __forceinline__ void
 store_lanes (const SlabDev &p, const unsigned char *src0, unsigned char *out, uint64_t out_base,
     uint32_t k_eff, int short_slab, uint32_t L, uint32_t n_runs)
 {
-  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  /* runs shorter than a warp: 2 or 4 of them side by side (lane_w = 16 or 8 lanes each) */
+  const uint32_t W = p.lane_w, G = 32u / W;
+  const uint32_t lane = threadIdx.x & (W - 1);
+  const uint32_t group = (threadIdx.x >> 5) * G + ((threadIdx.x & 31) / W);
   const FastDiv nseg_div = p.nseg_div[short_slab], keff_div = p.keff_div[short_slab];
   const uint32_t x0 = p.run_slab == 0 ? k_eff : p.run_size[0];
   const uint32_t x1 = p.run_slab == 1 ? k_eff : p.run_size[1];
   const uint32_t n0 = p.n_idx > 0 ? (p.idx_slab == 0 ? k_eff : p.idx_div[0].d) : 1;
   const uint32_t n_outer_runs = p.n_idx > 0 ? n_runs / n0 : 1;
   const uint32_t items = n0 * nseg_div.d;
+  const uint32_t stride = (SLAB_THREADS / 32) * G;
+  /* where lane l starts inside a run (element l): the same for every run of the slab */
+  uint32_t c0i = lane, c1i = 0, c2i = 0;
+  if (NRUN > 1) {
+    divmod (lane, p.run_div[0], c1i, c0i);
+    if (NRUN > 2) {
+      const uint32_t t = c1i;
+      divmod (t, p.run_div[1], c2i, c1i);
+    }
+  }
+  uint32_t s_lane = c0i * p.run_in[0];
+  if (NRUN > 1)
+    s_lane += c1i * p.run_in[1];
+  if (NRUN > 2)
+    s_lane += c2i * p.run_in[2];
+  const uint32_t in_step = p.n_idx > 0 ? stride * p.idx_in[0] : 0;
+  const uint64_t out_step = p.n_idx > 0 ? (uint64_t) stride * p.idx_out[0] * ES : 0;
   for (uint32_t o = 0; o < n_outer_runs; o++) {
     /* the run-index dims above the first: the same for every warp */
     uint64_t out_o = out_base;
@@ -138,7 +167,43 @@ store_lanes (const SlabDev &p, const unsigned char *src0, unsigned char *out, ui
         out_o += (uint64_t) c * p.idx_out[d];
         in_o += c * p.idx_in[d];
       }
-    for (uint32_t m = warp; m < items; m += SLAB_THREADS / 32) {
+    if (nseg_div.d == 1) {
+      /* one segment per run (runs of at most `seg` elements): from run to run only the bases
+       * move, by constants */
+      uint32_t sbase = in_o + s_lane;
+      unsigned char *dbase = out + (out_o + lane) * ES;
+      if (p.n_idx > 0) {
+        sbase += group * p.idx_in[0];
+        dbase += (uint64_t) group * p.idx_out[0] * ES;
+      }
+      for (uint32_t m = group; m < n0; m += stride, sbase += in_step, dbase += out_step) {
+        uint32_t sidx = sbase, c0 = c0i, c1 = c1i;
+        unsigned char *dst = dbase;
+        for (uint32_t j = lane; j < L; j += W) {
+          copy_elem<ES> (dst, src0 + (size_t) sidx * ES);
+          dst += W * ES;
+          sidx += p.step_s;
+          if (NRUN > 1) {
+            c0 += p.step_c0;
+            if (c0 >= x0) {
+              c0 -= x0;
+              sidx += p.wrap0_s;
+              if (NRUN > 2)
+                c1 += 1;
+            }
+            if (NRUN > 2) {
+              c1 += p.step_c1;
+              if (c1 >= x1) {
+                c1 -= x1;
+                sidx += p.wrap1_s;
+              }
+            }
+          }
+        }
+      }
+      continue;
+    }
+    for (uint32_t m = group; m < items; m += stride) {
       uint32_t i0, sg;
       divmod (m, nseg_div, i0, sg);
       uint32_t j = sg * p.seg + lane;
@@ -164,9 +229,9 @@ store_lanes (const SlabDev &p, const unsigned char *src0, unsigned char *out, ui
       if (NRUN > 2)
         sidx += c2 * p.run_in[2];
       unsigned char *dst = out + out_r * ES;
-      for (; j < j_end; j += 32) {
+      for (; j < j_end; j += W) {
         copy_elem<ES> (dst, src0 + (size_t) sidx * ES);
-        dst += 32 * ES;
+        dst += W * ES;
         sidx += p.step_s;
         if (NRUN > 1) {
           c0 += p.step_c0;
@@ -404,6 +469,36 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
     return -1;
   if (((uintptr_t) in | (uintptr_t) out) % (uintptr_t) es)
     return -1;
+  /* how the store phase works: 16-byte chunks per thread (bytes: fewest stores) or one element
+   * per lane (everything else: fewest instructions, no alignment cases) */
+  int lanes = es >= 2;
+  bool chunks_forced = false;
+  if (const char *e = getenv ("NNSB_SLAB_STORE")) {
+    chunks_forced = strcmp (e, "chunks") == 0;
+    lanes = strcmp (e, "lanes") == 0 ? 1 : chunks_forced ? 0 : lanes;
+  }
+  /* Three channels that are innermost on both sides (a pixel that moves as a whole: transposing
+   * an RGB image) cannot be folded into a power-of-two element by the canonicaliser; the lane
+   * store does not care, so here the pixel becomes the element (3, 6 or 12 bytes). */
+  CDim folded[2 * SLAB_DIMS];
+  if (n >= 3 && es <= 4 && dims[0].size == 3 && dims[0].in == 1 && dims[0].out == 1
+      && !chunks_forced && !getenv ("NNSB_SLAB_NO_FOLD")) {
+    bool ok = total_elems % 3 == 0;
+    for (int i = 1; i < n && ok; i++)
+      ok = dims[i].in % 3 == 0 && dims[i].out % 3 == 0;
+    if (ok) {
+      for (int i = 1; i < n; i++) {
+        folded[i - 1] = dims[i];
+        folded[i - 1].in /= 3;
+        folded[i - 1].out /= 3;
+      }
+      dims = folded;
+      n--;
+      es *= 3;
+      total_elems /= 3;
+      lanes = 1;
+    }
+  }
   /* dims by input stride; the input must be dense */
   int by_in[2 * SLAB_DIMS];
   for (int i = 0; i < n; i++)
@@ -433,7 +528,7 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   /* slab height: as tall as fits, but short enough that the grid gets several slabs per CTA slot
    * (a batch of small frames is only a few hundred 72 KB slabs, and with two resident CTAs per
    * SM those quantise into 2-3 rounds of which the last is half empty) */
-  uint64_t max_bytes = SLAB_MAX_BYTES;
+  uint64_t max_bytes = 24 * 1024;       /* sweep: profiles/r2_slab_sweep.md */
   if (const char *e = getenv ("NNSB_SLAB_KB"))
     if (atoi (e) > 0 && (uint64_t) atoi (e) * 1024 <= SLAB_MAX_BYTES)
       max_bytes = (uint64_t) atoi (e) * 1024;
@@ -442,8 +537,56 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   uint64_t k = max_bytes / (dims[S].in * es);
   if (k > dims[S].size)
     k = dims[S].size;
+  bool balance = true;          /* equal slabs, unless a height was picked for the lanes */
+  if (lanes && k < dims[S].size) {
+    /* When the slab dimension is part of the output runs, a run is per_k * k elements and lanes
+     * idle where that is not a multiple of the group width: among the heights down to half the
+     * tallest, take the one that fills the lanes best. */
+    bool fixed[2 * SLAB_DIMS];
+    for (int i = 0; i < n; i++)
+      fixed[i] = false;
+    for (int i = si + 1; i < n; i++)
+      fixed[by_in[i]] = true;
+    uint64_t per_k = 0, prod = 1, next_out = 1;
+    int cnt = 0;
+    for (int d = 0; d < n && cnt < 3; d++, cnt++) {
+      if (fixed[d] || dims[d].out != next_out)
+        break;
+      if (d == S) {
+        per_k = prod;
+        break;
+      }
+      prod *= dims[d].size;
+      next_out = dims[d].out * dims[d].size;
+    }
+    if (per_k && per_k * k <= 512) {
+      /* (long runs waste at most one group in many; this runs at every launch, so only the
+       * handful of heights whose runs are whole groups of 8 lanes are looked at) */
+      auto slots = [] (uint64_t L, uint64_t w) { return (L + w - 1) / w * w; };
+      double best = -1.0;
+      uint64_t best_k = k;
+      for (uint64_t kc = k; kc >= 1 && 2 * kc >= k; kc--) {
+        if (kc != k && (per_k * kc) % 8)
+          continue;
+        const uint64_t ns = (dims[S].size + kc - 1) / kc, k_last = dims[S].size - (ns - 1) * kc;
+        const uint64_t Lf = per_k * kc, w = Lf <= 8 ? 8 : Lf <= 16 ? 16 : 32;
+        if (Lf < 8)
+          break;
+        const double eff = (double) (per_k * dims[S].size) / (double) ((ns - 1) * slots (Lf, w) + slots (per_k * k_last, w));
+        if (eff > best + 0.02) {
+          best = eff;
+          best_k = kc;
+        }
+      }
+      if (best_k != k) {
+        k = best_k;
+        balance = false;
+      }
+    }
+  }
   const uint64_t nsl = (dims[S].size + k - 1) / k;
-  k = (dims[S].size + nsl - 1) / nsl;
+  if (balance)
+    k = (dims[S].size + nsl - 1) / nsl;
   if (k * dims[S].in * es >= (1ull << 31))
     return -1;
 
@@ -498,14 +641,29 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
     p.idx_out[p.n_idx] = dims[d].out;
     p.n_idx++;
   }
-  /* how the store phase works: 16-byte chunks per thread (bytes: fewest stores) or one element
-   * per lane (everything else: fewest instructions, no alignment cases) */
-  p.lanes = es >= 2;
-  if (const char *e = getenv ("NNSB_SLAB_STORE"))
-    p.lanes = strcmp (e, "lanes") == 0 ? 1 : strcmp (e, "chunks") == 0 ? 0 : p.lanes;
+  p.lanes = lanes;
   if (p.n_run == 0 || run_elems >= (1ull << 28))
     return -1;
-  if (p.lanes ? run_elems < 16 : run_elems * es < 128)
+  if (lanes && !getenv ("NNSB_SLAB_ANY_STRIDE")) {
+    /* neighbouring lanes read shared memory run_in[0] elements apart: when that stride puts four
+     * or more of them into one bank (1080p RGB rows: 5760 bytes = 45 x 128) the gather serialises
+     * and the tiled kernels, which pad their tiles, do better */
+    const uint64_t stride_b = (uint64_t) p.run_in[0] * es;
+    int per_bank[32] = { 0 };
+    uint64_t words[32];
+    int worst = 0;
+    for (int l = 0; l < 32; l++) {
+      words[l] = l * stride_b / 4;
+      bool seen = false;
+      for (int m = 0; m < l; m++)
+        seen = seen || words[m] == words[l];
+      if (!seen && ++per_bank[words[l] % 32] > worst)
+        worst = per_bank[words[l] % 32];
+    }
+    if (worst >= 4)
+      return -1;
+  }
+  if (p.lanes ? run_elems < 8 : run_elems * es < 128)
     return -1;                  /* short runs: the tiled kernels do better */
   /* slab-relative input strides: dims inside the slab have in < in[S] * k already */
   p.s_size = (uint32_t) dims[S].size;
@@ -524,7 +682,8 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
     const uint64_t k_last = dims[S].size - (nsl - 1) * k;       /* height of the last slab */
     const uint64_t ks[2] = { k, k_last };
     /* segments: long runs are cut so that the 8 warps of a CTA all find work */
-    p.seg = (uint32_t) ((run_elems + 31) / 32 * 32);
+    p.lane_w = (p.lanes && run_elems <= 8) ? 8 : (p.lanes && run_elems <= 16) ? 16 : 32;
+    p.seg = (uint32_t) ((run_elems + p.lane_w - 1) / p.lane_w * p.lane_w);
     if (p.seg > 512)
       p.seg = 512;
     for (int v = 0; v < 2; v++) {
@@ -535,13 +694,13 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
       p.keff_div[v] = make_fastdiv ((uint32_t) ks[v]);
       p.nseg_div[v] = make_fastdiv ((uint32_t) ((run_v + p.seg - 1) / p.seg));
     }
-    /* a step of 32 elements along a run, in the mixed radix (x0, x1) of its dims */
+    /* a step of lane_w elements along a run, in the mixed radix (x0, x1) of its dims */
     if (p.n_run == 1) {
-      p.step_s = 32u * p.run_in[0];
+      p.step_s = p.lane_w * p.run_in[0];
     } else {
       const uint32_t x0 = p.run_size[0], x1 = p.run_size[1];
-      p.step_c0 = 32u % x0;
-      uint32_t rest = 32u / x0, top = 0;
+      p.step_c0 = p.lane_w % x0;
+      uint32_t rest = p.lane_w / x0, top = 0;
       if (p.n_run > 2) {
         top = rest / x1;
         rest = rest % x1;
@@ -557,6 +716,9 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
     return 0;
   if (p.lanes)
     switch (es) {
+      case 3: return launch_t<3, true> (p, in, out, smem, cfg, stream);
+      case 6: return launch_t<6, true> (p, in, out, smem, cfg, stream);
+      case 12: return launch_t<12, true> (p, in, out, smem, cfg, stream);
       case 1: return launch_t<1, true> (p, in, out, smem, cfg, stream);
       case 2: return launch_t<2, true> (p, in, out, smem, cfg, stream);
       case 4: return launch_t<4, true> (p, in, out, smem, cfg, stream);

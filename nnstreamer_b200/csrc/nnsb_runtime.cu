@@ -15,6 +15,7 @@
 #include <cstdio>
 #include <cuda_runtime.h>
 #include <sched.h>
+#include <time.h>
 
 #include <cstdlib>
 #include <cstring>
@@ -555,18 +556,32 @@ nnsb_event_destroy (nnsb_event * e)
 /* Waits for an event without monopolising the core: cudaEventSynchronize spins, and a node
  * that runs 8 ranks x 8 streaming threads on 32 cores (BASELINE configs[4]) then loses a fifth of
  * its throughput to threads spinning against each other.  Query + yield costs nothing when the
- * cores are free. */
+ * cores are free; after a few hundred misses the thread sleeps in 20 us slices (the work it waits
+ * for is then clearly long).  NNSB_WAIT = spin | yield | sleep (default) selects the policy. */
 static void
 host_wait (cudaEvent_t e)
 {
-  for (;;) {
+  static const int policy = [] {
+    const char *v = getenv ("NNSB_WAIT");
+    return !v ? 2 : strcmp (v, "spin") == 0 ? 0 : strcmp (v, "yield") == 0 ? 1 : 2;
+  } ();
+  if (policy == 0) {
+    cudaEventSynchronize (e);
+    return;
+  }
+  for (int misses = 0;; misses++) {
     const cudaError_t r = cudaEventQuery (e);
     if (r != cudaErrorNotReady) {
       if (r != cudaSuccess)
         cudaGetLastError ();
       return;
     }
-    sched_yield ();
+    if (policy == 2 && misses >= 256) {
+      const struct timespec ts = { 0, 20000 };
+      nanosleep (&ts, nullptr);
+    } else {
+      sched_yield ();
+    }
   }
 }
 

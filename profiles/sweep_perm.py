@@ -16,6 +16,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
+KBS = (8, 16, 24, 32, 48, 72)
 CASES = [
     ("transpose", "1:2:0:3", "uint16", "3:225:113:1", 256),
     ("transpose", "0:2:1:3", "uint16", "3:225:113:1", 256),
@@ -62,7 +63,13 @@ def main():
     for case in CASES:
         print("==", case, flush=True)
         combos = [({}, "default"), ({"NNSB_PERM_SLAB": "0", "NNSB_PERM_NO_PIX": "1"}, "vector kernel")]
-        for store, kb, ctas in itertools.product(("lanes", "chunks"), (8, 16, 24, 32, 48, 72), (3, 4, 6)):
+        if case[3].startswith("3:1920:1080") and case[2] == "uint8":
+            for stage, swz in (("1", "0"), ("0", "0")):
+                combos.append(({"NNSB_PIX_STAGE": stage, "NNSB_PIX_SWIZZLE": swz},
+                               "pixel stage=%s swizzle=%s" % (stage, swz)))
+        stores = ("lanes",)
+        combos.append(({"NNSB_SLAB_NO_FOLD": "1"}, "default, no pixel fold"))
+        for store, kb, ctas in itertools.product(stores, KBS, (4, 6)):
             if (kb + 1) * ctas > 220:
                 continue
             combos.append(({"NNSB_PERM_SLAB": "2", "NNSB_PERM_NO_PIX": "1", "NNSB_SLAB_KB": str(kb),
