@@ -324,6 +324,14 @@ def extra_kernels(dev, peak, with_cpu=True):
     run("transpose_2_1_0_227x227x3_f32_b64", "transpose", "2:1:0:3", "float32", [3, 227, 227, 1], 64, 8, f32)
     run("transpose_1_2_0_225x113x3_u16_b256", "transpose", "1:2:0:3", "uint16", [3, 225, 113, 1], 256, 4, u16)
     run("transpose_0_2_1_225x113x3_u16_b256", "transpose", "0:2:1:3", "uint16", [3, 225, 113, 1], 256, 4, u16)
+    # the same shapes in launches long enough to leave the launch / ramp-up cost behind (the
+    # batches above move 79 MB: 17 us at 4.6 TB/s), and an element-wise kernel on those small
+    # batches as a yardstick for what a launch of that size can reach at all
+    run("transpose_2_1_0_227x227x3_f32_b512", "transpose", "2:1:0:3", "float32", [3, 227, 227, 1], 512, 8, f32)
+    run("transpose_1_2_0_225x113x3_u16_b2048", "transpose", "1:2:0:3", "uint16", [3, 225, 113, 1], 2048, 4, u16)
+    run("transpose_0_2_1_225x113x3_u16_b2048", "transpose", "0:2:1:3", "uint16", [3, 225, 113, 1], 2048, 4, u16)
+    run("yardstick_add0_227x227x3_f32_b64", "arithmetic", "add:0", "float32", [3, 227, 227, 1], 64, 8, f32)
+    run("yardstick_add0_225x113x3_u16_b256", "arithmetic", "add:0", "uint16", [3, 225, 113, 1], 256, 4, u16)
     run("transpose_1_0_2_1080p_gray_u8_b32", "transpose", "1:0:2:3", "uint8", [1, 1920, 1080, 1], 32, 2, u8)
     run("clamp_f32_1080p_b64", "clamp", "-33.3:77.7", "float32", DIM, 64, 8, f32,
         lambda c, x, d: c.clamp(x, -33.3, 77.7))

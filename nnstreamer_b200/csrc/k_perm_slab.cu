@@ -62,16 +62,14 @@ struct SlabDev
   uint64_t total_bytes;
   /* divisors that depend on the slab height, for full slabs [0] and for the last, shorter one [1] */
   FastDiv cpr_div[2], keff_div[2];
-  /* lane-per-element store (store_lanes): a run is cut into segments of `seg` elements (a multiple
-   * of lane_w), a group of lane_w lanes (a warp, or a half / quarter of one for short runs) owns a
-   * segment, lane l its elements l, l + lane_w, ...  The step of lane_w elements in the mixed
-   * radix of the run dims, and what it adds to the source offset: */
-  int lanes;                            /* use store_lanes */
-  uint32_t lane_w;                      /* 32, 16 or 8 */
-  uint32_t seg;
-  FastDiv nseg_div[2];                  /* segments per run: full slab, last slab */
-  uint32_t step_c0, step_c1;            /* lane_w = (.. * x1 + step_c1) * x0 + step_c0 */
-  uint32_t step_s;                      /* source elements a step adds when nothing wraps */
+  /* lane-per-element store (slab_lanes_kernel): groups of lane_w lanes step along a run by
+   * lane_w elements, the whole CTA by 256.  A step in the mixed radix of the run dims, and what
+   * it adds to the source offset: */
+  int lanes;                            /* use slab_lanes_kernel */
+  uint32_t lane_w, lane_shift;          /* 32, 16 or 8 lanes = 1 << lane_shift */
+  uint32_t n_above[2];                  /* runs per value of the first run-index dim: full slab, last slab */
+  uint32_t step_c0, step_c1, step_s;    /* lane_w = (.. * x1 + step_c1) * x0 + step_c0 */
+  uint32_t bstep_c0, bstep_c1, bstep_s; /* the same for 256 */
   uint32_t wrap0_s, wrap1_s;            /* added (mod 2^32) when c0 / c1 wraps */
 };
 
@@ -115,147 +113,295 @@ copy_elem (unsigned char *dst, const unsigned char *src)
   }
 }
 
-/* Store phase, one element per lane: consecutive lanes write consecutive elements of a run (a
- * warp store is 32 * ES contiguous bytes, whatever the alignment of the run), and read their
- * sources from shared memory at the stride the permutation gives them.  Nothing here depends on
- * alignment, and a lane spends a handful of instructions per element: its coordinates inside the
- * run advance by 32 with at most one carry per dim.  NRUN = dims inside a run. */
-template <int ES, int NRUN> __device__ __forceinline__ void
-store_lanes (const SlabDev &p, const unsigned char *src0, unsigned char *out, uint64_t out_base,
-    uint32_t k_eff, int short_slab, uint32_t L, uint32_t n_runs)
+/* Which slab, where it starts on both sides, how tall it is; then its bytes -- the 16-byte
+ * aligned superset of them -- go to shared memory (the element at slab byte b sits at
+ * buf[mis + b]) and the CTA waits for them. */
+template <int ES, bool BULK = false> __device__ __forceinline__ void
+slab_begin (const SlabDev &p, uintptr_t in_lo, uintptr_t in_hi, uint32_t slab, unsigned char *buf,
+    uint64_t &out_base, uint32_t &k_eff, uint32_t &mis, uint64_t *bar = nullptr, uint32_t *phase = nullptr)
 {
-  /* runs shorter than a warp: 2 or 4 of them side by side (lane_w = 16 or 8 lanes each) */
-  const uint32_t W = p.lane_w, G = 32u / W;
-  const uint32_t lane = threadIdx.x & (W - 1);
-  const uint32_t group = (threadIdx.x >> 5) * G + ((threadIdx.x & 31) / W);
-  const FastDiv nseg_div = p.nseg_div[short_slab], keff_div = p.keff_div[short_slab];
-  const uint32_t x0 = p.run_slab == 0 ? k_eff : p.run_size[0];
-  const uint32_t x1 = p.run_slab == 1 ? k_eff : p.run_size[1];
-  const uint32_t n0 = p.n_idx > 0 ? (p.idx_slab == 0 ? k_eff : p.idx_div[0].d) : 1;
-  const uint32_t n_outer_runs = p.n_idx > 0 ? n_runs / n0 : 1;
-  const uint32_t items = n0 * nseg_div.d;
-  const uint32_t stride = (SLAB_THREADS / 32) * G;
-  /* where lane l starts inside a run (element l): the same for every run of the slab */
-  uint32_t c0i = lane, c1i = 0, c2i = 0;
-  if (NRUN > 1) {
-    divmod (lane, p.run_div[0], c1i, c0i);
-    if (NRUN > 2) {
-      const uint32_t t = c1i;
-      divmod (t, p.run_div[1], c2i, c1i);
+  uint32_t oi, si;
+  divmod (slab, p.slabs_per_outer, oi, si);
+  uint64_t in_base = 0;         /* elements */
+  out_base = 0;
+#pragma unroll
+  for (int d = 0; d < SLAB_DIMS; d++)
+    if (d < p.n_outer) {
+      uint32_t q, c;
+      divmod (oi, p.outer_div[d], q, c);
+      oi = q;
+      in_base += (uint64_t) c * p.outer_in[d];
+      out_base += (uint64_t) c * p.outer_out[d];
+    }
+  const uint32_t o0 = si * p.k;
+  k_eff = (p.s_size - o0 < p.k) ? p.s_size - o0 : p.k;
+  in_base += (uint64_t) o0 * p.s_in;
+  out_base += (uint64_t) o0 * p.s_out;
+  const uint32_t slab_bytes = (uint32_t) (k_eff * p.s_in) * ES;
+
+  const uintptr_t abs0 = in_lo + in_base * ES;
+  const uintptr_t ga = abs0 & ~(uintptr_t) 15;
+  mis = (uint32_t) (abs0 - ga);
+  const uint32_t n_chunks = (mis + slab_bytes + 15) / 16;
+  if (BULK && ga >= in_lo && ga + (uintptr_t) n_chunks * 16 <= in_hi) {
+    /* one bulk copy (the copy engine of the SM moves it, no thread touches the bytes);
+     * completion is counted on the mbarrier */
+    const uint32_t bar_a = (uint32_t) __cvta_generic_to_shared (bar);
+    if (threadIdx.x == 0) {
+      asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+          :: "r" (bar_a), "r" (n_chunks * 16) : "memory");
+      asm volatile ("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+          :: "r" ((uint32_t) __cvta_generic_to_shared (buf)), "l" (ga), "r" (n_chunks * 16), "r" (bar_a)
+          : "memory");
+    }
+    asm volatile ("{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" :: "r" (bar_a), "r" (*phase) : "memory");
+    *phase ^= 1;
+    return;
+  }
+  for (uint32_t c = threadIdx.x; c < n_chunks; c += SLAB_THREADS) {
+    const uintptr_t g = ga + (uintptr_t) c * 16;
+    if (g >= in_lo && g + 16 <= in_hi) {
+      asm volatile ("cp.async.cg.shared.global [%0], [%1], 16;"
+          :: "r" ((uint32_t) __cvta_generic_to_shared (buf + c * 16)), "l" (g) : "memory");
+    } else {
+      /* first / last bytes of the whole tensor: never touch what is not ours */
+      for (int b = 0; b < 16; b++)
+        if (g + b >= in_lo && g + b < in_hi)
+          buf[c * 16 + b] = *reinterpret_cast<const unsigned char *> (g + b);
     }
   }
-  uint32_t s_lane = c0i * p.run_in[0];
-  if (NRUN > 1)
-    s_lane += c1i * p.run_in[1];
-  if (NRUN > 2)
-    s_lane += c2i * p.run_in[2];
-  const uint32_t in_step = p.n_idx > 0 ? stride * p.idx_in[0] : 0;
-  const uint64_t out_step = p.n_idx > 0 ? (uint64_t) stride * p.idx_out[0] * ES : 0;
-  for (uint32_t o = 0; o < n_outer_runs; o++) {
-    /* the run-index dims above the first: the same for every warp */
-    uint64_t out_o = out_base;
-    uint32_t in_o = 0, r = o;
-#pragma unroll
-    for (int d = 1; d < SLAB_DIMS; d++)
-      if (d < p.n_idx) {
-        uint32_t q, c;
-        if (d == p.idx_slab)
-          divmod (r, keff_div, q, c);
-        else
-          divmod (r, p.idx_div[d], q, c);
-        r = q;
-        out_o += (uint64_t) c * p.idx_out[d];
-        in_o += c * p.idx_in[d];
-      }
-    if (nseg_div.d == 1) {
-      /* one segment per run (runs of at most `seg` elements): from run to run only the bases
-       * move, by constants */
-      uint32_t sbase = in_o + s_lane;
-      unsigned char *dbase = out + (out_o + lane) * ES;
-      if (p.n_idx > 0) {
-        sbase += group * p.idx_in[0];
-        dbase += (uint64_t) group * p.idx_out[0] * ES;
-      }
-      for (uint32_t m = group; m < n0; m += stride, sbase += in_step, dbase += out_step) {
-        uint32_t sidx = sbase, c0 = c0i, c1 = c1i;
-        unsigned char *dst = dbase;
-        for (uint32_t j = lane; j < L; j += W) {
-          copy_elem<ES> (dst, src0 + (size_t) sidx * ES);
-          dst += W * ES;
-          sidx += p.step_s;
-          if (NRUN > 1) {
-            c0 += p.step_c0;
-            if (c0 >= x0) {
-              c0 -= x0;
-              sidx += p.wrap0_s;
-              if (NRUN > 2)
-                c1 += 1;
-            }
-            if (NRUN > 2) {
-              c1 += p.step_c1;
-              if (c1 >= x1) {
-                c1 -= x1;
-                sidx += p.wrap1_s;
-              }
-            }
-          }
-        }
-      }
-      continue;
-    }
-    for (uint32_t m = group; m < items; m += stride) {
-      uint32_t i0, sg;
-      divmod (m, nseg_div, i0, sg);
-      uint32_t j = sg * p.seg + lane;
-      uint32_t j_end = (sg + 1) * p.seg;
-      if (j_end > L)
-        j_end = L;
-      uint32_t c0 = j, c1 = 0, c2 = 0;
-      if (NRUN > 1) {
-        divmod (j, p.run_div[0], c1, c0);
-        if (NRUN > 2) {
-          const uint32_t t = c1;
-          divmod (t, p.run_div[1], c2, c1);
-        }
-      }
-      uint32_t sidx = in_o + c0 * p.run_in[0];
-      uint64_t out_r = out_o + j;
-      if (p.n_idx > 0) {
-        sidx += i0 * p.idx_in[0];
-        out_r += (uint64_t) i0 * p.idx_out[0];
-      }
-      if (NRUN > 1)
-        sidx += c1 * p.run_in[1];
+  asm volatile ("cp.async.commit_group;" ::: "memory");
+  asm volatile ("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads ();
+}
+
+/* One step of `T` elements along a run for a lane that sits at run coordinates (c0, c1, ..):
+ * the source offset moves by a constant plus a correction per carry (at most one per dim). */
+template <int NRUN> __device__ __forceinline__ void
+run_step (uint32_t &sb, uint32_t &c0, uint32_t &c1, uint32_t step_sb, uint32_t step_c0, uint32_t step_c1,
+    uint32_t wrap0_sb, uint32_t wrap1_sb, uint32_t x0, uint32_t x1)
+{
+  sb += step_sb;
+  if (NRUN > 1) {
+    c0 += step_c0;
+    if (c0 >= x0) {
+      c0 -= x0;
+      sb += wrap0_sb;
       if (NRUN > 2)
-        sidx += c2 * p.run_in[2];
-      unsigned char *dst = out + out_r * ES;
-      for (; j < j_end; j += W) {
-        copy_elem<ES> (dst, src0 + (size_t) sidx * ES);
-        dst += W * ES;
-        sidx += p.step_s;
-        if (NRUN > 1) {
-          c0 += p.step_c0;
-          if (c0 >= x0) {
-            c0 -= x0;
-            sidx += p.wrap0_s;
-            if (NRUN > 2)
-              c1 += 1;
-          }
-          if (NRUN > 2) {
-            c1 += p.step_c1;
-            if (c1 >= x1) {
-              c1 -= x1;
-              sidx += p.wrap1_s;
-            }
-          }
-        }
+        c1 += 1;
+    }
+    if (NRUN > 2) {
+      c1 += step_c1;
+      if (c1 >= x1) {
+        c1 -= x1;
+        sb += wrap1_sb;
       }
     }
   }
 }
 
-template <int ES, bool LANES>
-__global__ void __launch_bounds__ (SLAB_THREADS, LANES ? 6 : 5)
+/* The slab kernel with a store phase of one element per lane: consecutive lanes write
+ * consecutive elements of a run (a group of W lanes stores W * ES contiguous bytes, whatever
+ * the alignment of the run) and read their sources from shared memory at the stride the
+ * permutation gives them.  Nothing depends on alignment.  Three shapes of loop:
+ *   runs of at most W elements   a group of W = 8 / 16 / 32 lanes owns a run, takes one element per
+ *                                lane and moves on to the group's next run: bases advance by
+ *                                constants, ~8 instructions per run and lane;
+ *   runs of at most 512          the same with an inner loop along the run (steps of W);
+ *   longer runs                  the whole CTA walks one run after the other in steps of 256.
+ * Coordinates inside a run advance with at most one carry per dim (run_step).  NRUN = dims
+ * inside a run.  ES may be 3, 6 or 12 (a folded RGB pixel, see launch_permute_slab). */
+template <int ES, int NRUN>
+__global__ void __launch_bounds__ (SLAB_THREADS, 6)
+slab_lanes_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
+    const __grid_constant__ SlabDev p)
+{
+  extern __shared__ __align__ (16) unsigned char buf[];
+  const uintptr_t in_lo = (uintptr_t) in, in_hi = in_lo + p.total_bytes;
+  __shared__ __align__ (8) uint64_t bar;
+  const uint32_t tid = threadIdx.x;
+  if (tid == 0) {
+    asm volatile ("mbarrier.init.shared::cta.b64 [%0], 1;"
+        :: "r" ((uint32_t) __cvta_generic_to_shared (&bar)) : "memory");
+    asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads ();
+  uint32_t phase = 0;
+  const uint32_t W = p.lane_w;
+  const uint32_t lane = tid & (W - 1), group = tid >> p.lane_shift, n_groups = SLAB_THREADS >> p.lane_shift;
+  const uint32_t x0 = p.run_size[0], x1 = p.run_size[1];        /* radices: always full dims */
+  /* where lane `lane` (group loops) and thread `tid` (CTA-wide loop) start inside a run */
+  uint32_t lc0 = lane, lc1 = 0, lc2 = 0, tc0 = tid, tc1 = 0, tc2 = 0;
+  if (NRUN > 1) {
+    divmod (lane, p.run_div[0], lc1, lc0);
+    divmod (tid, p.run_div[0], tc1, tc0);
+    if (NRUN > 2) {
+      uint32_t t = lc1;
+      divmod (t, p.run_div[1], lc2, lc1);
+      t = tc1;
+      divmod (t, p.run_div[1], tc2, tc1);
+    }
+  }
+  uint32_t ls = lc0 * p.run_in[0], ts = tc0 * p.run_in[0];
+  if (NRUN > 1) {
+    ls += lc1 * p.run_in[1];
+    ts += tc1 * p.run_in[1];
+  }
+  if (NRUN > 2) {
+    ls += lc2 * p.run_in[2];
+    ts += tc2 * p.run_in[2];
+  }
+  const uint32_t in0_b = p.n_idx > 0 ? p.idx_in[0] * ES : 0;
+  const uint64_t out0_b = p.n_idx > 0 ? p.idx_out[0] * ES : 0;
+  const uint32_t g_in_b = n_groups * in0_b;
+  const uint64_t g_out_b = n_groups * out0_b;
+  const uint32_t wstep_sb = p.step_s * ES, wwrap0 = p.wrap0_s * ES, wwrap1 = p.wrap1_s * ES;
+  const uint32_t bstep_sb = p.bstep_s * ES;
+
+  for (uint32_t slab = blockIdx.x; slab < p.n_slabs; slab += gridDim.x) {
+    uint64_t out_base;
+    uint32_t k_eff, mis;
+    slab_begin<ES, true> (p, in_lo, in_hi, slab, buf, out_base, k_eff, mis, &bar, &phase);
+    const unsigned char *src0 = buf + mis;
+
+    uint32_t L = 1;
+#pragma unroll
+    for (int d = 0; d < NRUN; d++)
+      L *= (d == p.run_slab) ? k_eff : p.run_size[d];
+    uint32_t n_runs = 1;
+#pragma unroll
+    for (int d = 0; d < SLAB_DIMS; d++)
+      if (d < p.n_idx)
+        n_runs *= (d == p.idx_slab) ? k_eff : p.idx_div[d].d;
+    const FastDiv keff_div = p.keff_div[k_eff != p.k];
+
+    if (L <= 512) {
+      /* groups of W lanes, a run each; from run to run along the first run-index dim only the
+       * bases move */
+      const uint32_t n0 = p.n_idx > 0 ? (p.idx_slab == 0 ? k_eff : p.idx_div[0].d) : 1;
+      const uint32_t n_above = p.n_above[k_eff != p.k];
+      const uint32_t mine = n0 > group ? (n0 - group + n_groups - 1) >> (8 - p.lane_shift) : 0;
+      if (L <= W && n_above <= 4) {
+        /* one element per lane and run, and so few values of the upper run-index dims (the three
+         * channel planes of a CHW output) that their offsets stay in registers: the loop over
+         * the first run-index dim carries all of them */
+        uint32_t in_ob[4];
+        uint64_t out_ob[4];
+#pragma unroll
+        for (int o = 0; o < 4; o++) {
+          uint64_t out_o = 0;
+          uint32_t in_o = 0, r = o;
+#pragma unroll
+          for (int d = 1; d < SLAB_DIMS; d++)
+            if (d < p.n_idx) {
+              uint32_t q, c;
+              if (d == p.idx_slab)
+                divmod (r, keff_div, q, c);
+              else
+                divmod (r, p.idx_div[d], q, c);
+              r = q;
+              out_o += (uint64_t) c * p.idx_out[d];
+              in_o += c * p.idx_in[d];
+            }
+          in_ob[o] = in_o * ES;
+          out_ob[o] = out_o * ES;
+        }
+        if (lane < L) {
+          uint32_t sb = ls * ES + group * in0_b;
+          unsigned char *dp = out + (out_base + lane) * ES + group * out0_b;
+#pragma unroll 2
+          for (uint32_t i = 0; i < mine; i++) {
+#pragma unroll
+            for (int o = 0; o < 4; o++)
+              if ((uint32_t) o < n_above)
+                copy_elem<ES> (dp + out_ob[o], src0 + sb + in_ob[o]);
+            sb += g_in_b;
+            dp += g_out_b;
+          }
+        }
+      } else
+      for (uint32_t o = 0; o < n_above; o++) {
+        uint64_t out_o = out_base;
+        uint32_t in_o = 0, r = o;
+#pragma unroll
+        for (int d = 1; d < SLAB_DIMS; d++)
+          if (d < p.n_idx) {
+            uint32_t q, c;
+            if (d == p.idx_slab)
+              divmod (r, keff_div, q, c);
+            else
+              divmod (r, p.idx_div[d], q, c);
+            r = q;
+            out_o += (uint64_t) c * p.idx_out[d];
+            in_o += c * p.idx_in[d];
+          }
+        uint32_t sb = (in_o + ls) * ES + group * in0_b;
+        unsigned char *dp = out + (out_o + lane) * ES + group * out0_b;
+        if (L <= W) {
+          if (lane < L) {
+#pragma unroll 4
+            for (uint32_t i = 0; i < mine; i++) {
+              copy_elem<ES> (dp, src0 + sb);
+              sb += g_in_b;
+              dp += g_out_b;
+            }
+          }
+        } else {
+          for (uint32_t i = 0; i < mine; i++, sb += g_in_b, dp += g_out_b) {
+            uint32_t s = sb, c0 = lc0, c1 = lc1;
+            unsigned char *d = dp;
+            for (uint32_t j = lane; j < L; j += W) {
+              copy_elem<ES> (d, src0 + s);
+              d += W * ES;
+              run_step<NRUN> (s, c0, c1, wstep_sb, p.step_c0, p.step_c1, wwrap0, wwrap1, x0, x1);
+            }
+          }
+        }
+      }
+    } else {
+      /* long runs: the CTA walks each of them in steps of 256 elements */
+      for (uint32_t run = 0; run < n_runs; run++) {
+        uint64_t out_r = out_base;
+        uint32_t in_r = 0, r = run;
+        if (p.n_idx == 1) {
+          out_r += (uint64_t) run * p.idx_out[0];
+          in_r = run * p.idx_in[0];
+        } else
+#pragma unroll
+        for (int d = 0; d < SLAB_DIMS; d++)
+          if (d < p.n_idx) {
+            uint32_t q, c;
+            if (d == p.idx_slab)
+              divmod (r, keff_div, q, c);
+            else
+              divmod (r, p.idx_div[d], q, c);
+            r = q;
+            out_r += (uint64_t) c * p.idx_out[d];
+            in_r += c * p.idx_in[d];
+          }
+        uint32_t s = (in_r + ts) * ES, c0 = tc0, c1 = tc1;
+        unsigned char *d = out + (out_r + tid) * ES;
+#pragma unroll 4
+        for (uint32_t j = tid; j < L; j += SLAB_THREADS) {
+          copy_elem<ES> (d, src0 + s);
+          d += SLAB_THREADS * ES;
+          run_step<NRUN> (s, c0, c1, bstep_sb, p.bstep_c0, p.bstep_c1, wwrap0, wwrap1, x0, x1);
+        }
+      }
+    }
+    __syncthreads ();           /* the buffer is about to be overwritten */
+  }
+}
+
+template <int ES>
+__global__ void __launch_bounds__ (SLAB_THREADS, 5)
 permute_slab_kernel (const unsigned char *__restrict__ in, unsigned char *__restrict__ out,
     const __grid_constant__ SlabDev p)
 {
@@ -263,45 +409,9 @@ permute_slab_kernel (const unsigned char *__restrict__ in, unsigned char *__rest
   const uintptr_t in_lo = (uintptr_t) in, in_hi = in_lo + p.total_bytes;
 
   for (uint32_t slab = blockIdx.x; slab < p.n_slabs; slab += gridDim.x) {
-    /* which slab: (outer coordinates, position along the slab dimension) */
-    uint32_t oi, si;
-    divmod (slab, p.slabs_per_outer, oi, si);
-    uint64_t in_base = 0, out_base = 0;         /* elements */
-#pragma unroll
-    for (int d = 0; d < SLAB_DIMS; d++)
-      if (d < p.n_outer) {
-        uint32_t q, c;
-        divmod (oi, p.outer_div[d], q, c);
-        oi = q;
-        in_base += (uint64_t) c * p.outer_in[d];
-        out_base += (uint64_t) c * p.outer_out[d];
-      }
-    const uint32_t o0 = si * p.k;
-    const uint32_t k_eff = (p.s_size - o0 < p.k) ? p.s_size - o0 : p.k;
-    in_base += (uint64_t) o0 * p.s_in;
-    out_base += (uint64_t) o0 * p.s_out;
-    const uint32_t slab_bytes = (uint32_t) (k_eff * p.s_in) * ES;
-
-    /* ---- load: the aligned superset of [abs0, abs0 + slab_bytes) ---- */
-    const uintptr_t abs0 = in_lo + in_base * ES;
-    const uintptr_t ga = abs0 & ~(uintptr_t) 15;
-    const uint32_t mis = (uint32_t) (abs0 - ga);
-    const uint32_t n_chunks = (mis + slab_bytes + 15) / 16;
-    for (uint32_t c = threadIdx.x; c < n_chunks; c += SLAB_THREADS) {
-      const uintptr_t g = ga + (uintptr_t) c * 16;
-      if (g >= in_lo && g + 16 <= in_hi) {
-        asm volatile ("cp.async.cg.shared.global [%0], [%1], 16;"
-            :: "r" ((uint32_t) __cvta_generic_to_shared (buf + c * 16)), "l" (g) : "memory");
-      } else {
-        /* first / last bytes of the whole tensor: never touch what is not ours */
-        for (int b = 0; b < 16; b++)
-          if (g + b >= in_lo && g + b < in_hi)
-            buf[c * 16 + b] = *reinterpret_cast<const unsigned char *> (g + b);
-      }
-    }
-    asm volatile ("cp.async.commit_group;" ::: "memory");
-    asm volatile ("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads ();
+    uint64_t out_base;
+    uint32_t k_eff, mis;
+    slab_begin<ES> (p, in_lo, in_hi, slab, buf, out_base, k_eff, mis);
 
     /* ---- store: runs of L elements, 16-byte chunks ---- */
     uint32_t L = 1;
@@ -316,16 +426,7 @@ permute_slab_kernel (const unsigned char *__restrict__ in, unsigned char *__rest
         n_runs *= (d == p.idx_slab) ? k_eff : p.idx_div[d].d;
     const uint32_t run_bytes = L * ES;
     const int short_slab = k_eff != p.k;
-    if constexpr (LANES) {
-      if (p.n_run == 1)
-        store_lanes<ES, 1> (p, buf + mis, out, out_base, k_eff, short_slab, L, n_runs);
-      else if (p.n_run == 2)
-        store_lanes<ES, 2> (p, buf + mis, out, out_base, k_eff, short_slab, L, n_runs);
-      else
-        store_lanes<ES, 3> (p, buf + mis, out, out_base, k_eff, short_slab, L, n_runs);
-      __syncthreads ();         /* the buffer is about to be overwritten */
-      continue;
-    } else {
+    {
     const FastDiv cpr_div = p.cpr_div[short_slab], keff_div = p.keff_div[short_slab];
     const uint32_t cpr = cpr_div.d;                     /* chunks a run can touch, any alignment */
     const uint32_t items = n_runs * cpr;
@@ -424,41 +525,93 @@ permute_slab_kernel (const unsigned char *__restrict__ in, unsigned char *__rest
 #undef NNSB_SLAB_NEXT
     }
     __syncthreads ();           /* the buffer is about to be overwritten */
-    }                           /* !LANES */
+    }
   }
 }
 
-template <int ES, bool LANES> int
-launch_t (const SlabDev &p, const void *in, void *out, size_t smem, const LaunchCfg &cfg,
-    cudaStream_t stream)
+static uint64_t
+slab_grid (size_t smem, uint64_t by_regs, const SlabDev &p, const LaunchCfg &cfg)
 {
-  static int configured[64];
-  int dev = 0;
-  cudaGetDevice (&dev);
-  if (dev >= 0 && dev < 64 && !configured[dev]) {
-    cudaError_t e = cudaFuncSetAttribute (permute_slab_kernel<ES, LANES>,
-        cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (SLAB_MAX_BYTES + 64));
-    if (e != cudaSuccess)
-      return (int) e;
-    configured[dev] = 1;
-  }
   uint64_t per_sm = (200 * 1024) / (smem + 1024);      /* what the shared memory allows */
-  const uint64_t by_regs = LANES ? 6 : 5;
   if (per_sm > by_regs)
     per_sm = by_regs;
   if (per_sm < 2)
     per_sm = 2;
   if (const char *e = getenv ("NNSB_SLAB_CTAS"))
     per_sm = (uint64_t) atoi (e) > 0 ? (uint64_t) atoi (e) : per_sm;
-  uint64_t grid = (uint64_t) cfg.sm_count * per_sm;
-  if (grid > p.n_slabs)
-    grid = p.n_slabs;
-  permute_slab_kernel<ES, LANES><<<(unsigned int) grid, SLAB_THREADS, smem, stream>>> (
+  const uint64_t grid = (uint64_t) cfg.sm_count * per_sm;
+  return grid > p.n_slabs ? p.n_slabs : grid;
+}
+
+template <typename K> static int
+slab_configure (K kernel, int *configured)
+{
+  int dev = 0;
+  cudaGetDevice (&dev);
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute (kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int) (SLAB_MAX_BYTES + 64));
+    if (e != cudaSuccess)
+      return (int) e;
+    configured[dev] = 1;
+  }
+  return 0;
+}
+
+template <int ES> int
+launch_chunks (const SlabDev &p, const void *in, void *out, size_t smem, const LaunchCfg &cfg,
+    cudaStream_t stream)
+{
+  static int configured[64];
+  if (int r = slab_configure (permute_slab_kernel<ES>, configured))
+    return r;
+  permute_slab_kernel<ES><<<(unsigned int) slab_grid (smem, 5, p, cfg), SLAB_THREADS, smem, stream>>> (
       (const unsigned char *) in, (unsigned char *) out, p);
   return (int) cudaGetLastError ();
 }
 
+template <int ES, int NRUN> int
+launch_lanes_n (const SlabDev &p, const void *in, void *out, size_t smem, const LaunchCfg &cfg,
+    cudaStream_t stream)
+{
+  static int configured[64];
+  if (int r = slab_configure (slab_lanes_kernel<ES, NRUN>, configured))
+    return r;
+  slab_lanes_kernel<ES, NRUN><<<(unsigned int) slab_grid (smem, 6, p, cfg), SLAB_THREADS, smem, stream>>> (
+      (const unsigned char *) in, (unsigned char *) out, p);
+  return (int) cudaGetLastError ();
+}
+
+template <int ES> int
+launch_lanes (const SlabDev &p, const void *in, void *out, size_t smem, const LaunchCfg &cfg,
+    cudaStream_t stream)
+{
+  switch (p.n_run) {
+    case 1: return launch_lanes_n<ES, 1> (p, in, out, smem, cfg, stream);
+    case 2: return launch_lanes_n<ES, 2> (p, in, out, smem, cfg, stream);
+    default: return launch_lanes_n<ES, 3> (p, in, out, smem, cfg, stream);
+  }
+}
+
 }  // namespace
+
+/* lanes that share a run of L elements: a warp, or a half / quarter of one when that fills them
+ * better (short runs, or runs that are whole multiples of 16 / 8 only) */
+static uint32_t
+lane_width (uint64_t L)
+{
+  if (L <= 8)
+    return 8;
+  if (L <= 16)
+    return 16;
+  if (L % 32 == 0 || L > 128)
+    return 32;
+  if (L % 16 == 0)
+    return 16;
+  if (L <= 64 && L % 8 == 0)
+    return 8;
+  return 32;
+}
 
 /* -1: this permutation does not suit the slab kernel; else the launch result */
 int
@@ -479,10 +632,12 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   }
   /* Three channels that are innermost on both sides (a pixel that moves as a whole: transposing
    * an RGB image) cannot be folded into a power-of-two element by the canonicaliser; the lane
-   * store does not care, so here the pixel becomes the element (3, 6 or 12 bytes). */
+   * store does not care, so here the pixel can become the element (3, 6 or 12 bytes).  Measured
+   * on u16 225x113x3 0:2:1:3 this is slower than leaving the channels as the innermost run dim
+   * (three strided 2-byte stores per lane: 1.9 against 2.3 TB/s), so it is opt-in: NNSB_SLAB_FOLD. */
   CDim folded[2 * SLAB_DIMS];
   if (n >= 3 && es <= 4 && dims[0].size == 3 && dims[0].in == 1 && dims[0].out == 1
-      && !chunks_forced && !getenv ("NNSB_SLAB_NO_FOLD")) {
+      && !chunks_forced && getenv ("NNSB_SLAB_FOLD")) {
     bool ok = total_elems % 3 == 0;
     for (int i = 1; i < n && ok; i++)
       ok = dims[i].in % 3 == 0 && dims[i].out % 3 == 0;
@@ -569,7 +724,7 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
         if (kc != k && (per_k * kc) % 8)
           continue;
         const uint64_t ns = (dims[S].size + kc - 1) / kc, k_last = dims[S].size - (ns - 1) * kc;
-        const uint64_t Lf = per_k * kc, w = Lf <= 8 ? 8 : Lf <= 16 ? 16 : 32;
+        const uint64_t Lf = per_k * kc, w = lane_width (Lf);
         if (Lf < 8)
           break;
         const double eff = (double) (per_k * dims[S].size) / (double) ((ns - 1) * slots (Lf, w) + slots (per_k * k_last, w));
@@ -681,34 +836,43 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   {
     const uint64_t k_last = dims[S].size - (nsl - 1) * k;       /* height of the last slab */
     const uint64_t ks[2] = { k, k_last };
-    /* segments: long runs are cut so that the 8 warps of a CTA all find work */
-    p.lane_w = (p.lanes && run_elems <= 8) ? 8 : (p.lanes && run_elems <= 16) ? 16 : 32;
-    p.seg = (uint32_t) ((run_elems + p.lane_w - 1) / p.lane_w * p.lane_w);
-    if (p.seg > 512)
-      p.seg = 512;
+    p.lane_w = p.lanes ? lane_width (run_elems) : 32;
+    p.lane_shift = p.lane_w == 8 ? 3 : p.lane_w == 16 ? 4 : 5;
+    for (int v = 0; v < 2; v++) {
+      uint64_t above = 1;
+      for (int d = 1; d < p.n_idx; d++)
+        above *= (d == p.idx_slab) ? ks[v] : p.idx_div[d].d;
+      p.n_above[v] = (uint32_t) above;
+    }
     for (int v = 0; v < 2; v++) {
       uint64_t run_v = run_elems;
       if (p.run_slab >= 0)
         run_v = run_elems / k * ks[v];
       p.cpr_div[v] = make_fastdiv ((uint32_t) ((run_v * es + 15 + 15) / 16));
       p.keff_div[v] = make_fastdiv ((uint32_t) ks[v]);
-      p.nseg_div[v] = make_fastdiv ((uint32_t) ((run_v + p.seg - 1) / p.seg));
     }
-    /* a step of lane_w elements along a run, in the mixed radix (x0, x1) of its dims */
-    if (p.n_run == 1) {
-      p.step_s = p.lane_w * p.run_in[0];
-    } else {
+    /* a step of T elements along a run, in the mixed radix (x0, x1) of its dims */
+    auto steps = [&p] (uint32_t T, uint32_t &c0, uint32_t &c1, uint32_t &sv) {
+      if (p.n_run == 1) {
+        c0 = c1 = 0;
+        sv = T * p.run_in[0];
+        return;
+      }
       const uint32_t x0 = p.run_size[0], x1 = p.run_size[1];
-      p.step_c0 = p.lane_w % x0;
-      uint32_t rest = p.lane_w / x0, top = 0;
+      c0 = T % x0;
+      uint32_t rest = T / x0, top = 0;
       if (p.n_run > 2) {
         top = rest / x1;
         rest = rest % x1;
       }
-      p.step_c1 = rest;
-      p.step_s = p.step_c0 * p.run_in[0] + p.step_c1 * p.run_in[1] + top * p.run_in[2];
-      p.wrap0_s = p.run_in[1] - x0 * p.run_in[0];
-      p.wrap1_s = p.n_run > 2 ? p.run_in[2] - x1 * p.run_in[1] : 0u;
+      c1 = rest;
+      sv = c0 * p.run_in[0] + c1 * p.run_in[1] + top * p.run_in[2];
+    };
+    steps (p.lane_w, p.step_c0, p.step_c1, p.step_s);
+    steps (SLAB_THREADS, p.bstep_c0, p.bstep_c1, p.bstep_s);
+    if (p.n_run > 1) {
+      p.wrap0_s = p.run_in[1] - p.run_size[0] * p.run_in[0];
+      p.wrap1_s = p.n_run > 2 ? p.run_in[2] - p.run_size[1] * p.run_in[1] : 0u;
     }
   }
   const size_t smem = (size_t) (k * dims[S].in * es) + 48;
@@ -716,19 +880,19 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
     return 0;
   if (p.lanes)
     switch (es) {
-      case 3: return launch_t<3, true> (p, in, out, smem, cfg, stream);
-      case 6: return launch_t<6, true> (p, in, out, smem, cfg, stream);
-      case 12: return launch_t<12, true> (p, in, out, smem, cfg, stream);
-      case 1: return launch_t<1, true> (p, in, out, smem, cfg, stream);
-      case 2: return launch_t<2, true> (p, in, out, smem, cfg, stream);
-      case 4: return launch_t<4, true> (p, in, out, smem, cfg, stream);
-      default: return launch_t<8, true> (p, in, out, smem, cfg, stream);
+      case 3: return launch_lanes<3> (p, in, out, smem, cfg, stream);
+      case 6: return launch_lanes<6> (p, in, out, smem, cfg, stream);
+      case 12: return launch_lanes<12> (p, in, out, smem, cfg, stream);
+      case 1: return launch_lanes<1> (p, in, out, smem, cfg, stream);
+      case 2: return launch_lanes<2> (p, in, out, smem, cfg, stream);
+      case 4: return launch_lanes<4> (p, in, out, smem, cfg, stream);
+      default: return launch_lanes<8> (p, in, out, smem, cfg, stream);
     }
   switch (es) {
-    case 1: return launch_t<1, false> (p, in, out, smem, cfg, stream);
-    case 2: return launch_t<2, false> (p, in, out, smem, cfg, stream);
-    case 4: return launch_t<4, false> (p, in, out, smem, cfg, stream);
-    default: return launch_t<8, false> (p, in, out, smem, cfg, stream);
+    case 1: return launch_chunks<1> (p, in, out, smem, cfg, stream);
+    case 2: return launch_chunks<2> (p, in, out, smem, cfg, stream);
+    case 4: return launch_chunks<4> (p, in, out, smem, cfg, stream);
+    default: return launch_chunks<8> (p, in, out, smem, cfg, stream);
   }
 }
 

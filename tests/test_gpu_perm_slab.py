@@ -26,12 +26,16 @@ def np_transpose(x, dim, order, batch):
     return a.transpose(axes).reshape(-1)
 
 
-@pytest.mark.parametrize("store", STORES, ids=["lanes", "chunks", "auto"])
+@pytest.mark.parametrize("store", STORES + ["fold"], ids=["lanes", "chunks", "auto", "fold"])
 @pytest.mark.parametrize("force", [True, False], ids=["forced", "default"])
 @pytest.mark.parametrize("dtype,dim,batch", SHAPES, ids=lambda v: str(v).replace(" ", ""))
 def test_slab_permute_matches_numpy(dev, monkeypatch, dtype, dim, batch, force, store):
     """store: the two store phases of the kernel (one element per lane / 16-byte chunks per
     thread, NNSB_SLAB_STORE) and the default choice between them."""
+    monkeypatch.delenv("NNSB_SLAB_FOLD", raising=False)
+    if store == "fold":                            # RGB pixels as 3 / 6 / 12-byte elements
+        monkeypatch.setenv("NNSB_SLAB_FOLD", "1")
+        store = "lanes"
     if store:
         monkeypatch.setenv("NNSB_SLAB_STORE", store)
     else:
