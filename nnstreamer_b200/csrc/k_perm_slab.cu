@@ -32,7 +32,7 @@ namespace nnsb {
 namespace {
 
 constexpr int SLAB_THREADS = 256;
-constexpr uint32_t SLAB_MAX_BYTES = 72 * 1024;        /* three CTAs per SM overlap their load and store phases */
+constexpr uint32_t SLAB_MAX_BYTES = 96 * 1024;        /* two CTAs per SM still overlap their load and store phases */
 constexpr int SLAB_DIMS = 4;
 
 struct SlabDev
@@ -683,26 +683,16 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   /* slab height: as tall as fits, but short enough that the grid gets several slabs per CTA slot
    * (a batch of small frames is only a few hundred 72 KB slabs, and with two resident CTAs per
    * SM those quantise into 2-3 rounds of which the last is half empty) */
-  uint64_t max_bytes = 24 * 1024;       /* sweep: profiles/r2_slab_sweep.md */
-  if (const char *e = getenv ("NNSB_SLAB_KB"))
-    if (atoi (e) > 0 && (uint64_t) atoi (e) * 1024 <= SLAB_MAX_BYTES)
-      max_bytes = (uint64_t) atoi (e) * 1024;
-  if (dims[S].in * (uint64_t) es > max_bytes)
-    max_bytes = dims[S].in * (uint64_t) es;
-  uint64_t k = max_bytes / (dims[S].in * es);
-  if (k > dims[S].size)
-    k = dims[S].size;
-  bool balance = true;          /* equal slabs, unless a height was picked for the lanes */
-  if (lanes && k < dims[S].size) {
-    /* When the slab dimension is part of the output runs, a run is per_k * k elements and lanes
-     * idle where that is not a multiple of the group width: among the heights down to half the
-     * tallest, take the one that fills the lanes best. */
+  /* elements of an output run per slice of the slab dimension (0: the slab dimension is not part
+   * of the runs) */
+  uint64_t per_k = 0;
+  {
     bool fixed[2 * SLAB_DIMS];
     for (int i = 0; i < n; i++)
       fixed[i] = false;
     for (int i = si + 1; i < n; i++)
       fixed[by_in[i]] = true;
-    uint64_t per_k = 0, prod = 1, next_out = 1;
+    uint64_t prod = 1, next_out = 1;
     int cnt = 0;
     for (int d = 0; d < n && cnt < 3; d++, cnt++) {
       if (fixed[d] || dims[d].out != next_out)
@@ -714,6 +704,32 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
       prod *= dims[d].size;
       next_out = dims[d].out * dims[d].size;
     }
+  }
+  const uint64_t slice_bytes = dims[S].in * (uint64_t) es;
+  uint64_t max_bytes = 24 * 1024;       /* sweep: profiles/r2_slab_sweep.md */
+  /* ... unless the runs would then be shorter than a 128-byte line: every 32-byte sector of the
+   * output is then written in pieces by different slabs, which is harmless while the output
+   * stays in the L2 and halves the rate once it does not (f32 227x227x3 2:1:0:3, 8-row slabs:
+   * 3.4 TB/s on 64 frames, 1.9 on 512; 16-row slabs: 3.5 and 2.8) */
+  if (lanes && per_k && per_k * (max_bytes / slice_bytes) * es < 128) {
+    const uint64_t k_line = (128 + per_k * es - 1) / (per_k * es);
+    max_bytes = k_line * slice_bytes;
+    if (max_bytes > 48 * 1024)          /* 16 rows of 227 floats: 22.4 us / 226 us (64 / 512 frames); 32 rows: 25.3 / 237 */
+      max_bytes = 48 * 1024;
+  }
+  if (const char *e = getenv ("NNSB_SLAB_KB"))
+    if (atoi (e) > 0 && (uint64_t) atoi (e) * 1024 <= SLAB_MAX_BYTES)
+      max_bytes = (uint64_t) atoi (e) * 1024;
+  if (slice_bytes > max_bytes)
+    max_bytes = slice_bytes;
+  uint64_t k = max_bytes / slice_bytes;
+  if (k > dims[S].size)
+    k = dims[S].size;
+  bool balance = true;          /* equal slabs, unless a height was picked for the lanes */
+  if (lanes && k < dims[S].size) {
+    /* When the slab dimension is part of the output runs, a run is per_k * k elements and lanes
+     * idle where that is not a multiple of the group width: among the heights down to half the
+     * tallest, take the one that fills the lanes best. */
     if (per_k && per_k * k <= 512) {
       /* (long runs waste at most one group in many; this runs at every launch, so only the
        * handful of heights whose runs are whole groups of 8 lanes are looked at) */
