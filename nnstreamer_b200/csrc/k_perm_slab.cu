@@ -66,6 +66,7 @@ struct SlabDev
    * lane_w elements, the whole CTA by 256.  A step in the mixed radix of the run dims, and what
    * it adds to the source offset: */
   int lanes;                            /* use slab_lanes_kernel */
+  uint32_t piece;                       /* bytes per bulk copy of the slab load (a multiple of 16) */
   uint32_t lane_w, lane_shift;          /* 32, 16 or 8 lanes = 1 << lane_shift */
   uint32_t n_above[2];                  /* runs per value of the first run-index dim: full slab, last slab */
   uint32_t step_c0, step_c1, step_s;    /* lane_w = (.. * x1 + step_c1) * x0 + step_c0 */
@@ -147,12 +148,19 @@ slab_begin (const SlabDev &p, uintptr_t in_lo, uintptr_t in_hi, uint32_t slab, u
     /* one bulk copy (the copy engine of the SM moves it, no thread touches the bytes);
      * completion is counted on the mbarrier */
     const uint32_t bar_a = (uint32_t) __cvta_generic_to_shared (bar);
-    if (threadIdx.x == 0) {
-      asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
-          :: "r" (bar_a), "r" (n_chunks * 16) : "memory");
-      asm volatile ("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-          :: "r" ((uint32_t) __cvta_generic_to_shared (buf)), "l" (ga), "r" (n_chunks * 16), "r" (bar_a)
-          : "memory");
+    if (threadIdx.x < 32) {
+      /* the slab in pieces, one bulk copy per lane and round: several requests in flight */
+      const uint32_t total = n_chunks * 16, piece = p.piece;
+      if (threadIdx.x == 0)
+        asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+            :: "r" (bar_a), "r" (total) : "memory");
+      __syncwarp ();
+      for (uint32_t off = threadIdx.x * piece; off < total; off += 32 * piece) {
+        const uint32_t len = total - off < piece ? total - off : piece;
+        asm volatile ("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+            :: "r" ((uint32_t) __cvta_generic_to_shared (buf + off)), "l" (ga + off), "r" (len), "r" (bar_a)
+            : "memory");
+      }
     }
     asm volatile ("{\n"
         ".reg .pred p;\n"
@@ -852,6 +860,10 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   {
     const uint64_t k_last = dims[S].size - (nsl - 1) * k;       /* height of the last slab */
     const uint64_t ks[2] = { k, k_last };
+    p.piece = 4096;
+    if (const char *e = getenv ("NNSB_SLAB_PIECE"))
+      if (atoi (e) >= 16)
+        p.piece = (uint32_t) atoi (e) / 16 * 16;
     p.lane_w = p.lanes ? lane_width (run_elems) : 32;
     p.lane_shift = p.lane_w == 8 ? 3 : p.lane_w == 16 ? 4 : 5;
     for (int v = 0; v < 2; v++) {
