@@ -149,7 +149,7 @@ slab_begin (const SlabDev &p, uintptr_t in_lo, uintptr_t in_hi, uint32_t slab, u
      * completion is counted on the mbarrier */
     const uint32_t bar_a = (uint32_t) __cvta_generic_to_shared (bar);
     if (threadIdx.x < 32) {
-      /* the slab in pieces, one bulk copy per lane and round: several requests in flight */
+      /* one bulk copy, or (NNSB_SLAB_PIECE) pieces issued by the lanes of the first warp */
       const uint32_t total = n_chunks * 16, piece = p.piece;
       if (threadIdx.x == 0)
         asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
@@ -860,7 +860,7 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   {
     const uint64_t k_last = dims[S].size - (nsl - 1) * k;       /* height of the last slab */
     const uint64_t ks[2] = { k, k_last };
-    p.piece = 4096;
+    p.piece = 1u << 20;         /* one copy: pieces of 1-16 KB were measured 0-5 % slower (profiles/r2_slab_sweep.md) */
     if (const char *e = getenv ("NNSB_SLAB_PIECE"))
       if (atoi (e) >= 16)
         p.piece = (uint32_t) atoi (e) / 16 * 16;
