@@ -20,7 +20,10 @@ Workload (BASELINE.json configs[1], the configuration the metric is quoted on):
   cpu_baseline: the reference's own C code (oracle/_ref) or the C port timed on the host cores.
   kernels: configs[4] (`chain_64_streams_*`: 8 streams per GPU through converter -> typecast ->
            arithmetic -> transpose, resident / H2D / H2D+D2H, 1920 and 1918 wide) on EVERY N;
-           at N=1 also the other modes at their BASELINE configs.
+           at N=1 also the other modes at their BASELINE configs, the narrow-row permutes (with
+           `yardstick_*` = an element-wise kernel on the same small batches), the aggregator
+           (Python calls and `*_native_thread` = tools/agg_bench), the 8-stream chain from
+           Python threads (one call per element, and `*_linked` = one nnsb_branch_push per frame).
 
 Multi-GPU (--gpus N under torchrun): streams are independent, so each rank runs its own
 32-frame batch (and its own 8 streams) on its own GPU ("weak" scaling); NCCL is used only for the
