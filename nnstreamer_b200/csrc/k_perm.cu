@@ -321,8 +321,12 @@ launch_permute_t (const PermDev &p, const void *in, void *out, const LaunchCfg &
 {
   const size_t smem = (size_t) (ASYNC ? PERM_STAGES : 1) * (PERM_TILE_MAX + PERM_TILE_MAX / 32 + 1)
       * sizeof (E);
-  static int resident = 0;
-  if (resident == 0) {
+  /* per device: the attribute and the occupancy answer belong to a device's context */
+  static int resident_of[64];
+  int dev_id = 0;
+  cudaGetDevice (&dev_id);
+  int &resident = resident_of[(dev_id >= 0 && dev_id < 64) ? dev_id : 0];
+  if (resident == 0 || dev_id >= 64) {
     if (smem > 48 * 1024) {
       cudaError_t e = cudaFuncSetAttribute (permute_kernel<E, ASYNC>,
           cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);

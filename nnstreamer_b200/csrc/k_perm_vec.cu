@@ -894,8 +894,12 @@ launch_permute_vec_t (const PermVecDev &p, const void *d_table, const void *in, 
     const LaunchCfg &cfg, cudaStream_t stream)
 {
   const size_t smem = (size_t) PV_STAGES * PV_NVT * VB;
-  static int resident = 0;
-  if (resident == 0) {
+  /* per device: the attribute and the occupancy answer belong to a device's context */
+  static int resident_of[64];
+  int dev_id = 0;
+  cudaGetDevice (&dev_id);
+  int &resident = resident_of[(dev_id >= 0 && dev_id < 64) ? dev_id : 0];
+  if (resident == 0 || dev_id >= 64) {
     cudaError_t e = cudaFuncSetAttribute (permute_vec_kernel<ES, VB, MICRO>,
         cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
     if (e != cudaSuccess)

@@ -324,8 +324,12 @@ launch_plane_t (const PlaneDev &p, const void *in, void *out, const LaunchCfg &c
     cudaStream_t stream)
 {
   typedef PlaneGeom<C, ES> Gm;
-  static int resident = 0;
-  if (resident == 0) {
+  /* per device: the attribute and the occupancy answer belong to a device's context */
+  static int resident_of[64];
+  int dev_id = 0;
+  cudaGetDevice (&dev_id);
+  int &resident = resident_of[(dev_id >= 0 && dev_id < 64) ? dev_id : 0];
+  if (resident == 0 || dev_id >= 64) {
     cudaError_t e = cudaFuncSetAttribute (plane_kernel<C, ES, TO_PLANAR>,
         cudaFuncAttributeMaxDynamicSharedMemorySize, (int) Gm::SMEM);
     if (e != cudaSuccess)
