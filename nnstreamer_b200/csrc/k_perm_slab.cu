@@ -62,13 +62,25 @@ struct SlabDev
   uint64_t total_bytes;
   /* divisors that depend on the slab height, for full slabs [0] and for the last, shorter one [1] */
   FastDiv cpr_div[2], keff_div[2];
+  /* window (lane kernel only): a slab takes only wt slices of the dimension just below the slab
+   * dimension on the input side, so that it can be taller -- k row segments instead of one
+   * contiguous range.  Row r of the slab sits in shared memory at r * pitch_b (+ the
+   * misalignment of row 0): pitch_b = row stride modulo 16, so every row's 16-byte aligned
+   * superset lands 16-byte aligned. */
+  int win;
+  int idx_win;                          /* index of the window dimension among the run-index dims */
+  uint32_t w_size, wt;                  /* its extent, slices per window */
+  uint64_t w_in, w_out;                 /* its strides, elements */
+  FastDiv nwin_div;                     /* windows per slab position */
+  FastDiv weff_div[2];                  /* wt, and the width of the last window */
+  uint32_t pitch_b, seg_b;              /* bytes between rows in shared memory; bytes of a full row segment */
   /* lane-per-element store (slab_lanes_kernel): groups of lane_w lanes step along a run by
    * lane_w elements, the whole CTA by 256.  A step in the mixed radix of the run dims, and what
    * it adds to the source offset: */
   int lanes;                            /* use slab_lanes_kernel */
   uint32_t piece;                       /* bytes per bulk copy of the slab load (a multiple of 16) */
   uint32_t lane_w, lane_shift;          /* 32, 16 or 8 lanes = 1 << lane_shift */
-  uint32_t n_above[2];                  /* runs per value of the first run-index dim: full slab, last slab */
+  uint32_t n_above[2][2];               /* runs per value of the first run-index dim: [last slab][last window] */
   uint32_t step_c0, step_c1, step_s;    /* lane_w = (.. * x1 + step_c1) * x0 + step_c0 */
   uint32_t bstep_c0, bstep_c1, bstep_s; /* the same for 256 */
   uint32_t wrap0_s, wrap1_s;            /* added (mod 2^32) when c0 / c1 wraps */
@@ -119,12 +131,20 @@ copy_elem (unsigned char *dst, const unsigned char *src)
  * buf[mis + b]) and the CTA waits for them. */
 template <int ES, bool BULK = false> __device__ __forceinline__ void
 slab_begin (const SlabDev &p, uintptr_t in_lo, uintptr_t in_hi, uint32_t slab, unsigned char *buf,
-    uint64_t &out_base, uint32_t &k_eff, uint32_t &mis, uint64_t *bar = nullptr, uint32_t *phase = nullptr)
+    uint64_t &out_base, uint32_t &k_eff, uint32_t &mis, uint64_t *bar = nullptr, uint32_t *phase = nullptr,
+    uint32_t *wt_eff = nullptr)
 {
-  uint32_t oi, si;
+  uint32_t oi, si, w0 = 0;
+  if (BULK && p.win) {
+    uint32_t rest, wi;
+    divmod (slab, p.nwin_div, rest, wi);
+    slab = rest;
+    w0 = wi * p.wt;
+    *wt_eff = (p.w_size - w0 < p.wt) ? p.w_size - w0 : p.wt;
+  }
   divmod (slab, p.slabs_per_outer, oi, si);
-  uint64_t in_base = 0;         /* elements */
-  out_base = 0;
+  uint64_t in_base = (uint64_t) w0 * p.w_in;    /* elements */
+  out_base = (uint64_t) w0 * p.w_out;
 #pragma unroll
   for (int d = 0; d < SLAB_DIMS; d++)
     if (d < p.n_outer) {
@@ -138,28 +158,60 @@ slab_begin (const SlabDev &p, uintptr_t in_lo, uintptr_t in_hi, uint32_t slab, u
   k_eff = (p.s_size - o0 < p.k) ? p.s_size - o0 : p.k;
   in_base += (uint64_t) o0 * p.s_in;
   out_base += (uint64_t) o0 * p.s_out;
-  const uint32_t slab_bytes = (uint32_t) (k_eff * p.s_in) * ES;
-
   const uintptr_t abs0 = in_lo + in_base * ES;
-  const uintptr_t ga = abs0 & ~(uintptr_t) 15;
-  mis = (uint32_t) (abs0 - ga);
-  const uint32_t n_chunks = (mis + slab_bytes + 15) / 16;
-  if (BULK && ga >= in_lo && ga + (uintptr_t) n_chunks * 16 <= in_hi) {
-    /* one bulk copy (the copy engine of the SM moves it, no thread touches the bytes);
-     * completion is counted on the mbarrier */
+  mis = (uint32_t) (abs0 & 15);
+
+  if (BULK) {
     const uint32_t bar_a = (uint32_t) __cvta_generic_to_shared (bar);
     if (threadIdx.x < 32) {
-      /* one bulk copy, or (NNSB_SLAB_PIECE) pieces issued by the lanes of the first warp */
-      const uint32_t total = n_chunks * 16, piece = p.piece;
-      if (threadIdx.x == 0)
-        asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
-            :: "r" (bar_a), "r" (total) : "memory");
-      __syncwarp ();
-      for (uint32_t off = threadIdx.x * piece; off < total; off += 32 * piece) {
-        const uint32_t len = total - off < piece ? total - off : piece;
-        asm volatile ("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-            :: "r" ((uint32_t) __cvta_generic_to_shared (buf + off)), "l" (ga + off), "r" (len), "r" (bar_a)
-            : "memory");
+      /* every lane of the first warp arrives once with the bytes of the bulk copies it issues
+       * (the copy engine moves them, no thread touches the bytes); what cannot be copied in
+       * bulk -- a 16-byte piece that would reach outside the tensor -- the lane moves itself
+       * before it arrives */
+      const uint32_t rows = p.win ? k_eff : 1u;
+      const uint64_t row_b = (uint64_t) p.s_in * ES;
+      const uint32_t seg = p.win ? (uint32_t) ((uint64_t) (*wt_eff) * p.w_in * ES) : (uint32_t) (k_eff * p.s_in) * ES;
+      uint32_t tx = 0;
+      for (int pass = 0; pass < 2; pass++) {
+        for (uint32_t r = threadIdx.x; r < rows; r += 32) {
+          const uintptr_t a = abs0 + r * row_b;
+          uintptr_t g = a & ~(uintptr_t) 15;
+          uint32_t len = ((uint32_t) (a - g) + seg + 15) & ~15u;
+          /* row r: element 0 at buf[mis + r * pitch_b], so its aligned superset starts here: */
+          unsigned char *dst = buf + mis + r * p.pitch_b - (uint32_t) (a - g);
+          /* the first / last 16-byte piece may reach outside the tensor (its very first and last
+           * bytes only): those pieces are moved byte by byte, never touching what is not ours */
+          if (g < in_lo) {
+            if (pass == 0)
+              for (uint32_t b = 0; b < 16; b++)
+                if (g + b >= in_lo && g + b < in_hi)
+                  dst[b] = *reinterpret_cast<const unsigned char *> (g + b);
+            g += 16;
+            dst += 16;
+            len -= 16;
+          }
+          if (len && g + len > in_hi) {
+            if (pass == 0)
+              for (uint32_t b = len - 16; b < len; b++)
+                if (g + b >= in_lo && g + b < in_hi)
+                  dst[b] = *reinterpret_cast<const unsigned char *> (g + b);
+            len -= 16;
+          }
+          if (pass == 0) {
+            tx += len;
+          } else {
+            const uint32_t piece = p.piece;
+            for (uint32_t off = 0; off < len; off += piece) {
+              const uint32_t n = len - off < piece ? len - off : piece;
+              asm volatile ("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                  :: "r" ((uint32_t) __cvta_generic_to_shared (dst + off)), "l" (g + off), "r" (n), "r" (bar_a)
+                  : "memory");
+            }
+          }
+        }
+        if (pass == 0)
+          asm volatile ("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+              :: "r" (bar_a), "r" (tx) : "memory");
       }
     }
     asm volatile ("{\n"
@@ -173,6 +225,11 @@ slab_begin (const SlabDev &p, uintptr_t in_lo, uintptr_t in_hi, uint32_t slab, u
     *phase ^= 1;
     return;
   }
+
+  /* cp.async by all threads: the 16-byte aligned superset of the slab */
+  const uint32_t slab_bytes = (uint32_t) (k_eff * p.s_in) * ES;
+  const uintptr_t ga = abs0 & ~(uintptr_t) 15;
+  const uint32_t n_chunks = (mis + slab_bytes + 15) / 16;
   for (uint32_t c = threadIdx.x; c < n_chunks; c += SLAB_THREADS) {
     const uintptr_t g = ga + (uintptr_t) c * 16;
     if (g >= in_lo && g + 16 <= in_hi) {
@@ -236,7 +293,7 @@ slab_lanes_kernel (const unsigned char *__restrict__ in, unsigned char *__restri
   __shared__ __align__ (8) uint64_t bar;
   const uint32_t tid = threadIdx.x;
   if (tid == 0) {
-    asm volatile ("mbarrier.init.shared::cta.b64 [%0], 1;"
+    asm volatile ("mbarrier.init.shared::cta.b64 [%0], 32;"      /* the lanes of the first warp, slab_begin */
         :: "r" ((uint32_t) __cvta_generic_to_shared (&bar)) : "memory");
     asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -275,8 +332,8 @@ slab_lanes_kernel (const unsigned char *__restrict__ in, unsigned char *__restri
 
   for (uint32_t slab = blockIdx.x; slab < p.n_slabs; slab += gridDim.x) {
     uint64_t out_base;
-    uint32_t k_eff, mis;
-    slab_begin<ES, true> (p, in_lo, in_hi, slab, buf, out_base, k_eff, mis, &bar, &phase);
+    uint32_t k_eff, mis, wt_eff = 0;
+    slab_begin<ES, true> (p, in_lo, in_hi, slab, buf, out_base, k_eff, mis, &bar, &phase, &wt_eff);
     const unsigned char *src0 = buf + mis;
 
     uint32_t L = 1;
@@ -287,14 +344,16 @@ slab_lanes_kernel (const unsigned char *__restrict__ in, unsigned char *__restri
 #pragma unroll
     for (int d = 0; d < SLAB_DIMS; d++)
       if (d < p.n_idx)
-        n_runs *= (d == p.idx_slab) ? k_eff : p.idx_div[d].d;
+        n_runs *= (d == p.idx_slab) ? k_eff : (p.win && d == p.idx_win) ? wt_eff : p.idx_div[d].d;
     const FastDiv keff_div = p.keff_div[k_eff != p.k];
+    const int short_w = p.win && wt_eff != p.wt;
+    const FastDiv weff_div = p.weff_div[short_w];
 
     if (L <= 512) {
       /* groups of W lanes, a run each; from run to run along the first run-index dim only the
        * bases move */
-      const uint32_t n0 = p.n_idx > 0 ? (p.idx_slab == 0 ? k_eff : p.idx_div[0].d) : 1;
-      const uint32_t n_above = p.n_above[k_eff != p.k];
+      const uint32_t n0 = p.n_idx > 0 ? (p.idx_slab == 0 ? k_eff : (p.win && p.idx_win == 0) ? wt_eff : p.idx_div[0].d) : 1;
+      const uint32_t n_above = p.n_above[k_eff != p.k][short_w];
       const uint32_t mine = n0 > group ? (n0 - group + n_groups - 1) >> (8 - p.lane_shift) : 0;
       if (L <= W && n_above <= 4) {
         /* one element per lane and run, and so few values of the upper run-index dims (the three
@@ -312,6 +371,8 @@ slab_lanes_kernel (const unsigned char *__restrict__ in, unsigned char *__restri
               uint32_t q, c;
               if (d == p.idx_slab)
                 divmod (r, keff_div, q, c);
+              else if (p.win && d == p.idx_win)
+                divmod (r, weff_div, q, c);
               else
                 divmod (r, p.idx_div[d], q, c);
               r = q;
@@ -344,6 +405,8 @@ slab_lanes_kernel (const unsigned char *__restrict__ in, unsigned char *__restri
             uint32_t q, c;
             if (d == p.idx_slab)
               divmod (r, keff_div, q, c);
+            else if (p.win && d == p.idx_win)
+              divmod (r, weff_div, q, c);
             else
               divmod (r, p.idx_div[d], q, c);
             r = q;
@@ -388,6 +451,8 @@ slab_lanes_kernel (const unsigned char *__restrict__ in, unsigned char *__restri
             uint32_t q, c;
             if (d == p.idx_slab)
               divmod (r, keff_div, q, c);
+            else if (p.win && d == p.idx_win)
+              divmod (r, weff_div, q, c);
             else
               divmod (r, p.idx_div[d], q, c);
             r = q;
@@ -694,6 +759,9 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   /* elements of an output run per slice of the slab dimension (0: the slab dimension is not part
    * of the runs) */
   uint64_t per_k = 0;
+  bool pre_run[2 * SLAB_DIMS];          /* dims the output runs cover below the slab dimension */
+  for (int i = 0; i < n; i++)
+    pre_run[i] = false;
   {
     bool fixed[2 * SLAB_DIMS];
     for (int i = 0; i < n; i++)
@@ -709,6 +777,7 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
         per_k = prod;
         break;
       }
+      pre_run[d] = true;
       prod *= dims[d].size;
       next_out = dims[d].out * dims[d].size;
     }
@@ -734,7 +803,54 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   if (k > dims[S].size)
     k = dims[S].size;
   bool balance = true;          /* equal slabs, unless a height was picked for the lanes */
-  if (lanes && k < dims[S].size) {
+  /* Window: when the slab dimension is what the output runs run along and a slab of whole slices
+   * is only a few of them tall (f32 227x227x3 2:1:0:3: 16 rows = 64-byte runs), take only a part
+   * of the dimension below it instead and make the slab taller: runs of >= 512 bytes (or the
+   * whole dimension), row segments of >= 256 bytes, about 32 KB per slab. */
+  int Wd = -1;
+  uint64_t wt = 0, nwin = 1, pitch_b = 0;
+  {
+    /* measured (profiles/r2_slab_sweep.md): f32 227x227x3 2:1:0:3 on 512 frames 221 -> 167-173 us,
+     * u16 225x113x3 0:2:1:3 on 2048 frames 263 -> 207 us; on 64 / 256 frames, whose output stays in
+     * the L2, the many small row copies cost more than the longer runs give (24 -> 30 us), hence
+     * only for outputs that do not fit the L2 */
+    const char *e = getenv ("NNSB_SLAB_WINDOW");
+    const bool allowed = e ? atoi (e) != 0 : total_elems * (uint64_t) es >= 100ull * 1000 * 1000;
+    const int cand = by_in[si - 1];
+    if (allowed && lanes && per_k && es <= 8 && k < dims[S].size && per_k * k * es < 512
+        && !pre_run[cand] && dims[cand].size > 1 && !getenv ("NNSB_SLAB_KB")) {
+      const uint64_t unit_b = dims[cand].in * (uint64_t) es;    /* one slice of the window dim inside a row */
+      const uint64_t k_need = (512 + per_k * es - 1) / (per_k * es), budget = 32 * 1024;
+      uint64_t kk = dims[S].size <= 2 * k_need ? dims[S].size : k_need;
+      if (const char *r = getenv ("NNSB_SLAB_WIN_ROWS"))
+        if (atoi (r) > 0 && (uint64_t) atoi (r) <= dims[S].size)
+          kk = (uint64_t) atoi (r);
+      uint64_t w = budget / (kk * unit_b);
+      const uint64_t w_min = (256 + unit_b - 1) / unit_b;       /* (144-byte segments: 234 us where 264-byte ones take 173) */
+      if (w < w_min) {
+        w = w_min;
+        kk = budget / (w * unit_b + 46);
+      }
+      if (kk > dims[S].size)
+        kk = dims[S].size;
+      if (w >= 1 && w < dims[cand].size && kk >= 2 * k) {
+        nwin = (dims[cand].size + w - 1) / w;
+        w = (dims[cand].size + nwin - 1) / nwin;
+        nwin = (dims[cand].size + w - 1) / w;
+        const uint64_t ns = (dims[S].size + kk - 1) / kk;
+        kk = (dims[S].size + ns - 1) / ns;
+        const uint64_t p0 = w * unit_b + 30;
+        pitch_b = p0 + ((slice_bytes % 16) + 16 - (p0 % 16)) % 16;      /* = row stride modulo 16 */
+        if (kk * pitch_b + 64 <= SLAB_MAX_BYTES) {
+          Wd = cand;
+          wt = w;
+          k = kk;
+          balance = false;
+        }
+      }
+    }
+  }
+  if (lanes && k < dims[S].size && Wd < 0) {
     /* When the slab dimension is part of the output runs, a run is per_k * k elements and lanes
      * idle where that is not a multiple of the group width: among the heights down to half the
      * tallest, take the one that fills the lanes best. */
@@ -774,6 +890,7 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   p.es = es;
   p.idx_slab = -1;
   p.run_slab = -1;
+  p.idx_win = -1;
   bool outer[2 * SLAB_DIMS];
   for (int i = 0; i < n; i++)
     outer[i] = false;
@@ -799,14 +916,14 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
     if (in_run && dims[d].out == next_out && p.n_run < 3) {
       p.run_size[p.n_run] = (uint32_t) (d == S ? k : dims[d].size);
       p.run_div[p.n_run] = make_fastdiv (p.run_size[p.n_run]);
-      p.run_in[p.n_run] = (uint32_t) dims[d].in;
+      p.run_in[p.n_run] = (uint32_t) ((d == S && Wd >= 0) ? pitch_b / es : dims[d].in);
       p.n_run++;
       run_elems *= (d == S ? k : dims[d].size);
       next_out = dims[d].out * dims[d].size;
       if (d == S) {
         p.run_slab = p.n_run - 1;
-        if (k < dims[S].size)
-          in_run = false;
+        if (k < dims[S].size || Wd >= 0)
+          in_run = false;       /* (with a window the dim above may not join the run: its extent varies) */
       }
       continue;
     }
@@ -815,8 +932,10 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
       return -1;
     if (d == S)
       p.idx_slab = p.n_idx;
-    p.idx_div[p.n_idx] = make_fastdiv ((uint32_t) (d == S ? k : dims[d].size));
-    p.idx_in[p.n_idx] = (uint32_t) dims[d].in;
+    if (d == Wd)
+      p.idx_win = p.n_idx;
+    p.idx_div[p.n_idx] = make_fastdiv ((uint32_t) (d == S ? k : d == Wd ? wt : dims[d].size));
+    p.idx_in[p.n_idx] = (uint32_t) ((d == S && Wd >= 0) ? pitch_b / es : dims[d].in);
     p.idx_out[p.n_idx] = dims[d].out;
     p.n_idx++;
   }
@@ -850,9 +969,23 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
   p.s_in = dims[S].in;
   p.s_out = dims[S].out;
   p.slabs_per_outer = make_fastdiv ((uint32_t) nsl);
-  uint64_t n_slabs = nsl;
+  uint64_t n_slabs = nsl * nwin;
   for (int i = 0; i < p.n_outer; i++)
     n_slabs *= p.outer_div[i].d;
+  if (Wd >= 0) {
+    if (p.idx_win < 0 || p.idx_slab >= 0 || p.run_slab < 0)
+      return -1;                /* (the window dimension must enumerate runs, the slab dimension be inside them) */
+    p.win = 1;
+    p.w_size = (uint32_t) dims[Wd].size;
+    p.wt = (uint32_t) wt;
+    p.w_in = dims[Wd].in;
+    p.w_out = dims[Wd].out;
+    p.nwin_div = make_fastdiv ((uint32_t) nwin);
+    p.weff_div[0] = make_fastdiv ((uint32_t) wt);
+    p.weff_div[1] = make_fastdiv ((uint32_t) (dims[Wd].size - (nwin - 1) * wt));
+    p.pitch_b = (uint32_t) pitch_b;
+    p.seg_b = (uint32_t) (wt * dims[Wd].in * es);
+  }
   if (n_slabs >= (1ull << 31))
     return -1;
   p.n_slabs = (uint32_t) n_slabs;
@@ -866,12 +999,13 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
         p.piece = (uint32_t) atoi (e) / 16 * 16;
     p.lane_w = p.lanes ? lane_width (run_elems) : 32;
     p.lane_shift = p.lane_w == 8 ? 3 : p.lane_w == 16 ? 4 : 5;
-    for (int v = 0; v < 2; v++) {
-      uint64_t above = 1;
-      for (int d = 1; d < p.n_idx; d++)
-        above *= (d == p.idx_slab) ? ks[v] : p.idx_div[d].d;
-      p.n_above[v] = (uint32_t) above;
-    }
+    for (int v = 0; v < 2; v++)
+      for (int u = 0; u < 2; u++) {
+        uint64_t above = 1;
+        for (int d = 1; d < p.n_idx; d++)
+          above *= (d == p.idx_slab) ? ks[v] : (p.win && d == p.idx_win) ? p.weff_div[u].d : p.idx_div[d].d;
+        p.n_above[v][u] = (uint32_t) above;
+      }
     for (int v = 0; v < 2; v++) {
       uint64_t run_v = run_elems;
       if (p.run_slab >= 0)
@@ -903,7 +1037,7 @@ launch_permute_slab (const CDim *dims, int n, int es, const void *in, void *out,
       p.wrap1_s = p.n_run > 2 ? p.run_in[2] - p.run_size[1] * p.run_in[1] : 0u;
     }
   }
-  const size_t smem = (size_t) (k * dims[S].in * es) + 48;
+  const size_t smem = (Wd >= 0 ? (size_t) (k * pitch_b) : (size_t) (k * dims[S].in * es)) + 48;
   if (dry_run)
     return 0;
   if (p.lanes)

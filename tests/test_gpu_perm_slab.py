@@ -26,13 +26,17 @@ def np_transpose(x, dim, order, batch):
     return a.transpose(axes).reshape(-1)
 
 
-@pytest.mark.parametrize("store", STORES + ["fold"], ids=["lanes", "chunks", "auto", "fold"])
+@pytest.mark.parametrize("store", STORES + ["fold", "window"], ids=["lanes", "chunks", "auto", "fold", "window"])
 @pytest.mark.parametrize("force", [True, False], ids=["forced", "default"])
 @pytest.mark.parametrize("dtype,dim,batch", SHAPES, ids=lambda v: str(v).replace(" ", ""))
 def test_slab_permute_matches_numpy(dev, monkeypatch, dtype, dim, batch, force, store):
     """store: the two store phases of the kernel (one element per lane / 16-byte chunks per
     thread, NNSB_SLAB_STORE) and the default choice between them."""
     monkeypatch.delenv("NNSB_SLAB_FOLD", raising=False)
+    monkeypatch.delenv("NNSB_SLAB_WINDOW", raising=False)
+    if store == "window":                          # taller slabs of row segments (k_perm_slab.cu, window)
+        monkeypatch.setenv("NNSB_SLAB_WINDOW", "1")
+        store = "lanes"
     if store == "fold":                            # RGB pixels as 3 / 6 / 12-byte elements
         monkeypatch.setenv("NNSB_SLAB_FOLD", "1")
         store = "lanes"
@@ -68,15 +72,17 @@ def test_slab_permute_matches_numpy(dev, monkeypatch, dtype, dim, batch, force, 
         assert used > 0, "the slab kernel was never selected for %s %s" % (dtype, dim)
 
 
-@pytest.mark.parametrize("store", ["lanes", "chunks"])
-def test_slab_leaves_guard_bytes_alone(dev, monkeypatch, store):
+@pytest.mark.parametrize("order", [(1, 2, 0), (0, 2, 1), (2, 1, 0)])
+@pytest.mark.parametrize("store", ["lanes", "chunks", "window"])
+def test_slab_leaves_guard_bytes_alone(dev, monkeypatch, store, order):
     """Partial head / tail chunks of a run are written element by element: nothing outside."""
     monkeypatch.setenv("NNSB_PERM_SLAB", "2")
-    monkeypatch.setenv("NNSB_SLAB_STORE", store)
+    monkeypatch.setenv("NNSB_SLAB_WINDOW", "1" if store == "window" else "0")
+    monkeypatch.setenv("NNSB_SLAB_STORE", "lanes" if store == "window" else store)
     dim, batch, dtype = [3, 225, 113, 1], 3, "uint16"
     n = int(np.prod(dim))
     x = np.random.default_rng(1).integers(0, 65535, n * batch).astype(dtype)
-    plan = dev.plan("transpose", "1:2:0:3", dtype, dim)
+    plan = dev.plan("transpose", "%d:%d:%d:3" % order, dtype, dim)
     guard = 256
     d_in = dev.upload(x)
     host = np.full(x.nbytes + 2 * guard + 6, 0xA5, dtype=np.uint8)
@@ -85,7 +91,7 @@ def test_slab_leaves_guard_bytes_alone(dev, monkeypatch, store):
     back = dev.download(d_out, host.size, np.uint8)
     plan.close()
     assert np.all(back[:guard + 6] == 0xA5) and np.all(back[guard + 6 + x.nbytes:] == 0xA5)
-    assert back[guard + 6:guard + 6 + x.nbytes].tobytes() == np_transpose(x, dim, (1, 2, 0), batch).tobytes()
+    assert back[guard + 6:guard + 6 + x.nbytes].tobytes() == np_transpose(x, dim, order, batch).tobytes()
     dev.free(d_in)
     dev.free(d_out)
 
