@@ -425,14 +425,20 @@ slab_lanes_kernel (const unsigned char *__restrict__ in, unsigned char *__restri
             }
           }
         } else {
-          for (uint32_t i = 0; i < mine; i++, sb += g_in_b, dp += g_out_b) {
-            uint32_t s = sb, c0 = lc0, c1 = lc1;
-            unsigned char *d = dp;
-            for (uint32_t j = lane; j < L; j += W) {
-              copy_elem<ES> (d, src0 + s);
-              d += W * ES;
-              run_step<NRUN> (s, c0, c1, wstep_sb, p.step_c0, p.step_c1, wwrap0, wwrap1, x0, x1);
+          /* the lane's position inside a run on the outside, the group's runs on the inside: for
+           * one position only the bases move from run to run (the same tight loop as above), and
+           * the carry arithmetic along the run is done once per position, not once per element */
+          uint32_t s = 0, c0 = lc0, c1 = lc1;
+          for (uint32_t j = lane; j < L; j += W) {
+            uint32_t sbt = sb + s;
+            unsigned char *d = dp + (j - lane) * ES;
+#pragma unroll 4
+            for (uint32_t i = 0; i < mine; i++) {
+              copy_elem<ES> (d, src0 + sbt);
+              sbt += g_in_b;
+              d += g_out_b;
             }
+            run_step<NRUN> (s, c0, c1, wstep_sb, p.step_c0, p.step_c1, wwrap0, wwrap1, x0, x1);
           }
         }
       }
